@@ -1,0 +1,317 @@
+// C ABI of the rasterizer library (see include/das3r_raster.h). Host-side orchestration only: layout of the three
+// state blobs, stage sequencing, error reporting. Replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (reference cuda_rasterizer/rasterizer_impl.cu:141-434) and SimpleKNN::knn (simple-knn/simple_knn.cu:186-222).
+#include "../../include/das3r_raster.h"
+#include "kernels.cuh"
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+
+using namespace das3r;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* where, cudaError_t e) {
+    char buf[512];
+    snprintf(buf, sizeof(buf), "[das3r_raster] %s: %s", where, e == cudaSuccess ? "failed" : cudaGetErrorString(e));
+    g_err = buf;
+    return code;
+}
+int fail_msg(int code, const char* msg) {
+    g_err = std::string("[das3r_raster] ") + msg;
+    return code;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Cursor {
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        size_t o = off;
+        off += align_up(bytes, 256);
+        return o;
+    }
+};
+
+void geom_layout(int P, das3r_raster_state_layout* L) {
+    Cursor c;
+    const size_t n = (size_t)P;
+    L->g_recA = c.take(n * sizeof(GaussRec));  // AoS: A at +0, B at +16, C at +32 of each 48-byte record
+    L->g_recB = L->g_recA + 16;
+    L->g_recC = L->g_recA + 32;
+    L->g_tiles_touched = c.take(n * 4);
+    L->g_clamped = c.take(n);
+    L->geom_bytes = c.off;
+}
+
+void image_layout(int W, int H, das3r_raster_state_layout* L) {
+    Cursor c;
+    const size_t N = (size_t)W * H;
+    const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    L->i_final_T = c.take(N * 4);
+    L->i_n_contrib = c.take(N * 4);
+    L->i_ranges = c.take(T * 8);
+    L->i_tile_counts = c.take(T * 4);
+    L->i_cursors = c.take(T * 4);
+    L->i_totals = c.take(16);
+    L->image_bytes = c.off;
+}
+
+// Tail of the binning blob used only by the large-tile fallback starts at b_fallback.
+struct BinExtra {
+    size_t b_fallback, fallback_bytes;
+};
+
+void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_raster_state_layout* L, BinExtra* X) {
+    Cursor c;
+    const size_t n = (size_t)R;
+    L->b_unsorted = c.take(n * 8);
+    L->b_point_list = c.take(n * 4);
+    L->b_sA = c.take(n * sizeof(GaussRec));
+    L->b_sB = L->b_sA + 16;
+    L->b_sC = L->b_sA + 32;
+    L->b_keys_sorted = with_keys ? c.take(n * 8) : (size_t)0;
+    X->fallback_bytes = with_fallback ? tile_sort_fallback_bytes(R, T) : 0;
+    X->b_fallback = with_fallback ? c.take(X->fallback_bytes) : 0;
+    L->binning_bytes = c.off;
+}
+
+bool check_params(const das3r_raster_params* p) {
+    return p && p->P >= 0 && p->width > 0 && p->height > 0 && p->D >= 0 && p->D <= 3 && p->M >= 0;
+}
+
+#define STAGE(call, name)                                                   \
+    do {                                                                    \
+        cudaError_t e_ = (call);                                            \
+        if (e_ != cudaSuccess) return fail(DAS3R_ECUDA, name, e_);          \
+        if (params->debug) {                                                \
+            e_ = cudaStreamSynchronize(stream);                             \
+            if (e_ == cudaSuccess) e_ = cudaGetLastError();                 \
+            if (e_ != cudaSuccess) return fail(DAS3R_ECUDA, name, e_);      \
+        }                                                                   \
+    } while (0)
+
+}  // namespace
+
+extern "C" {
+
+int das3r_abi_version(void) { return DAS3R_ABI_VERSION; }
+
+const char* das3r_last_error(void) { return g_err.c_str(); }
+
+int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
+                                    das3r_raster_state_layout* out) {
+    if (!out || P < 0 || width <= 0 || height <= 0 || num_rendered < 0) return fail_msg(DAS3R_EINVAL, "bad layout query");
+    memset(out, 0, sizeof(*out));
+    geom_layout(P, out);
+    image_layout(width, height, out);
+    BinExtra x;
+    const int T = ((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
+    binning_layout(num_rendered, T, true, false, out, &x);
+    return DAS3R_OK;
+}
+
+int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_inputs* in,
+                         const das3r_raster_outputs* out, das3r_alloc_fn geom_alloc, void* geom_ctx,
+                         das3r_alloc_fn binning_alloc, void* binning_ctx, das3r_alloc_fn image_alloc, void* image_ctx,
+                         das3r_raster_state* state, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!check_params(params) || !in || !out || !state || !geom_alloc || !binning_alloc || !image_alloc)
+        return fail_msg(DAS3R_EINVAL, "forward: null or invalid argument");
+    if (!out->out_color || (params->P > 0 && !out->radii)) return fail_msg(DAS3R_EINVAL, "forward: null output");
+    const int P = params->P, W = params->width, H = params->height;
+    memset(state, 0, sizeof(*state));
+    if (P == 0) {
+        // rasterize_points.cu:68,:81 — the image stays all-zero (no background) when there are no Gaussians
+        cudaError_t e = cudaMemsetAsync(out->out_color, 0, (size_t)3 * W * H * 4, stream);
+        if (e == cudaSuccess && out->out_depth) e = cudaMemsetAsync(out->out_depth, 0, (size_t)W * H * 4, stream);
+        if (e == cudaSuccess && out->out_alpha) e = cudaMemsetAsync(out->out_alpha, 0, (size_t)W * H * 4, stream);
+        if (e != cudaSuccess) return fail(DAS3R_ECUDA, "memset(out_color)", e);
+        return 0;
+    }
+    if (!in->means3D || !in->opacities || !params->background || !params->viewmatrix || !params->projmatrix ||
+        !params->campos)
+        return fail_msg(DAS3R_EINVAL, "forward: means3D/opacities/background/matrices/campos must be non-null");
+    if ((in->shs == nullptr) == (in->colors_precomp == nullptr))
+        return fail_msg(DAS3R_EINVAL, "forward: provide exactly one of shs / colors_precomp");
+    const bool has_sr = in->scales != nullptr && in->rotations != nullptr;
+    if (has_sr == (in->cov3D_precomp != nullptr) || ((in->scales != nullptr) != (in->rotations != nullptr)))
+        return fail_msg(DAS3R_EINVAL, "forward: provide exactly one of (scales, rotations) / cov3D_precomp");
+    if (in->shs && (params->M < (params->D + 1) * (params->D + 1) || params->M > 16))
+        return fail_msg(DAS3R_EINVAL, "forward: M must satisfy (D+1)^2 <= M <= 16");
+
+    const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const int T = (int)(gx * gy);
+    das3r_raster_state_layout L;
+    memset(&L, 0, sizeof(L));
+    geom_layout(P, &L);
+    image_layout(W, H, &L);
+
+    char* geom = geom_alloc(L.geom_bytes, geom_ctx);
+    char* img = image_alloc(L.image_bytes, image_ctx);
+    if (!geom || !img) return fail_msg(DAS3R_ENOMEM, "forward: allocator returned NULL");
+    state->geom = geom;
+    state->geom_bytes = L.geom_bytes;
+    state->image = img;
+    state->image_bytes = L.image_bytes;
+
+    GaussRec* rec = reinterpret_cast<GaussRec*>(geom + L.g_recA);
+    uint32_t* tiles_touched = reinterpret_cast<uint32_t*>(geom + L.g_tiles_touched);
+    uint8_t* clamped = reinterpret_cast<uint8_t*>(geom + L.g_clamped);
+    float* final_T = reinterpret_cast<float*>(img + L.i_final_T);
+    uint32_t* n_contrib = reinterpret_cast<uint32_t*>(img + L.i_n_contrib);
+    uint2* ranges = reinterpret_cast<uint2*>(img + L.i_ranges);
+    uint32_t* tile_counts = reinterpret_cast<uint32_t*>(img + L.i_tile_counts);
+    uint32_t* cursors = reinterpret_cast<uint32_t*>(img + L.i_cursors);
+    uint32_t* totals = reinterpret_cast<uint32_t*>(img + L.i_totals);
+
+    STAGE(cudaMemsetAsync(tile_counts, 0, (size_t)T * 4, stream), "memset(tile_counts)");
+
+    PreFwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.P = P; a.D = params->D; a.M = params->M; a.W = W; a.H = H;
+    a.gx = gx; a.gy = gy;
+    a.tan_fovx = params->tan_fovx; a.tan_fovy = params->tan_fovy;
+    a.focal_y = H / (2.0f * params->tan_fovy);  // rasterizer_impl.cu:222-223
+    a.focal_x = W / (2.0f * params->tan_fovx);
+    a.scale_mod = params->scale_modifier;
+    a.prefiltered = params->prefiltered;
+    a.means = in->means3D; a.shs = in->shs; a.colors_precomp = in->colors_precomp; a.opac = in->opacities;
+    a.scales = in->scales; a.rots = in->rotations; a.cov3D_precomp = in->cov3D_precomp;
+    a.view = params->viewmatrix; a.proj = params->projmatrix; a.campos = params->campos;
+    a.radii = out->radii; a.rec = rec; a.tiles_touched = tiles_touched; a.clamped = clamped;
+    a.tile_counts = tile_counts;
+    static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
+    STAGE(launch_preprocess_fwd(a, stage_sh, stream), "preprocess_fwd");
+    STAGE(launch_tile_scan(tile_counts, T, ranges, cursors, totals, stream), "tile_scan");
+
+    // The one host round trip of the forward (the reference has the same one, rasterizer_impl.cu:281).
+    uint32_t host_totals[4] = {0, 0, 0, 0};
+    cudaError_t e = cudaMemcpyAsync(host_totals, totals, sizeof(host_totals), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "read-back of num_rendered", e);
+    if (host_totals[0] > 0x7fffffffu) return fail_msg(DAS3R_ELIMIT, "forward: more than 2^31-1 tile instances");
+    const int R = (int)host_totals[0];
+    const uint32_t max_count = host_totals[1];
+    state->num_rendered = R;
+
+    const bool fallback = max_count > (uint32_t)tile_sort_capacity();
+    BinExtra X;
+    binning_layout(R, T, params->debug != 0, fallback, &L, &X);
+    char* bin = binning_alloc(L.binning_bytes, binning_ctx);
+    if (!bin && L.binning_bytes > 0) return fail_msg(DAS3R_ENOMEM, "forward: binning allocator returned NULL");
+    state->binning = bin;
+    state->binning_bytes = L.binning_bytes;
+    uint64_t* unsorted = reinterpret_cast<uint64_t*>(bin + L.b_unsorted);
+    uint32_t* point_list = reinterpret_cast<uint32_t*>(bin + L.b_point_list);
+    GaussRec* sorted_rec = reinterpret_cast<GaussRec*>(bin + L.b_sA);
+    uint64_t* keys_sorted = params->debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
+
+    if (R > 0) {
+        STAGE(launch_scatter(P, gx, gy, rec, out->radii, tiles_touched, cursors, unsorted, stream), "scatter");
+        if (!fallback)
+            STAGE(launch_tile_sort(T, max_count, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, stream),
+                  "tile_sort");
+        else
+            STAGE(launch_tile_sort_fallback(R, T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted,
+                                            bin + X.b_fallback, X.fallback_bytes, stream),
+                  "tile_sort_fallback");
+    }
+    STAGE(launch_blend_fwd(gx, gy, ranges, sorted_rec, W, H, params->background, final_T, n_contrib, out->out_color,
+                           out->out_depth, out->out_alpha, stream),
+          "blend_fwd");
+    return R;
+}
+
+size_t das3r_raster_backward_scratch_bytes(int32_t P) {
+    return align_up((size_t)(P > 0 ? P : 0) * ACC_STRIDE * sizeof(float), 256);
+}
+
+int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in, const int32_t* radii,
+                          const das3r_raster_state* state, const float* dL_dpix, const das3r_raster_grads* g,
+                          void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!check_params(params) || !in || !state || !g) return fail_msg(DAS3R_EINVAL, "backward: null or invalid argument");
+    const int P = params->P, W = params->width, H = params->height;
+    if (P == 0) return DAS3R_OK;
+    if (!radii || !dL_dpix || !state->geom || !state->image || !g->dL_dmeans2D || !g->dL_dcolors || !g->dL_dopacity ||
+        !g->dL_dmeans3D || !g->dL_dcov3D || !g->dL_dscales || !g->dL_drotations || !g->scratch)
+        return fail_msg(DAS3R_EINVAL, "backward: null buffer");
+    if (in->shs && !g->dL_dsh) return fail_msg(DAS3R_EINVAL, "backward: dL_dsh is null although shs is given");
+    const int R = state->num_rendered;
+    if (R > 0 && !state->binning) return fail_msg(DAS3R_EINVAL, "backward: binning blob is null");
+
+    const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const int T = (int)(gx * gy);
+    das3r_raster_state_layout L;
+    memset(&L, 0, sizeof(L));
+    geom_layout(P, &L);
+    image_layout(W, H, &L);
+    BinExtra X;
+    binning_layout(R, T, params->debug != 0, false, &L, &X);
+    if (state->geom_bytes < L.geom_bytes || state->image_bytes < L.image_bytes)
+        return fail_msg(DAS3R_EINVAL, "backward: state blobs are smaller than the forward's layout");
+
+    const uint8_t* clamped = reinterpret_cast<const uint8_t*>(state->geom + L.g_clamped);
+    const float* final_T = reinterpret_cast<const float*>(state->image + L.i_final_T);
+    const uint32_t* n_contrib = reinterpret_cast<const uint32_t*>(state->image + L.i_n_contrib);
+    const uint2* ranges = reinterpret_cast<const uint2*>(state->image + L.i_ranges);
+
+    STAGE(cudaMemsetAsync(g->scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)");
+    if (R > 0) {
+        const uint32_t* point_list = reinterpret_cast<const uint32_t*>(state->binning + L.b_point_list);
+        const GaussRec* sorted_rec = reinterpret_cast<const GaussRec*>(state->binning + L.b_sA);
+        STAGE(launch_blend_bwd(gx, gy, ranges, point_list, sorted_rec, W, H, params->background, final_T, n_contrib,
+                               dL_dpix, g->scratch, stream),
+              "blend_bwd");
+    }
+    PreBwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.P = P; a.D = params->D; a.M = in->shs ? params->M : 0; a.W = W; a.H = H;
+    a.tan_fovx = params->tan_fovx; a.tan_fovy = params->tan_fovy;
+    a.focal_y = H / (2.0f * params->tan_fovy);
+    a.focal_x = W / (2.0f * params->tan_fovx);
+    a.scale_mod = params->scale_modifier;
+    a.means = in->means3D; a.shs = in->shs; a.scales = in->scales; a.rots = in->rotations;
+    a.cov3D_precomp = in->cov3D_precomp;
+    a.view = params->viewmatrix; a.proj = params->projmatrix; a.campos = params->campos;
+    a.radii = radii; a.clamped = clamped; a.acc = g->scratch;
+    a.dL_dmeans2D = g->dL_dmeans2D; a.dL_dcolors = g->dL_dcolors; a.dL_dopacity = g->dL_dopacity;
+    a.dL_dmeans3D = g->dL_dmeans3D; a.dL_dcov3D = g->dL_dcov3D; a.dL_dsh = in->shs ? g->dL_dsh : nullptr;
+    a.dL_dscales = g->dL_dscales; a.dL_drots = g->dL_drotations;
+    STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd");
+    return DAS3R_OK;
+}
+
+int das3r_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present, void* stream_v) {
+    g_err.clear();
+    if (P < 0) return fail_msg(DAS3R_EINVAL, "mark_visible: P < 0");
+    if (P == 0) return DAS3R_OK;
+    if (!means3D || !viewmatrix || !projmatrix || !present) return fail_msg(DAS3R_EINVAL, "mark_visible: null pointer");
+    cudaError_t e =
+        launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, static_cast<cudaStream_t>(stream_v));
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "mark_visible", e);
+    return DAS3R_OK;
+}
+
+size_t das3r_knn_scratch_bytes(int32_t P) { return knn_scratch_bytes(P); }
+
+int das3r_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes,
+                    void* stream_v) {
+    g_err.clear();
+    if (P < 0) return fail_msg(DAS3R_EINVAL, "knn: P < 0");
+    if (P == 0) return DAS3R_OK;
+    if (!points || !mean_dist2 || !scratch) return fail_msg(DAS3R_EINVAL, "knn: null pointer");
+    if (scratch_bytes < knn_scratch_bytes(P)) return fail_msg(DAS3R_EINVAL, "knn: scratch too small");
+    cudaError_t e = knn_dist2(P, points, mean_dist2, scratch, scratch_bytes, static_cast<cudaStream_t>(stream_v));
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "knn", e);
+    return DAS3R_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,533 @@
+// Backward path of the sm_100a Gaussian-splat rasterizer:
+//   blend_bwd       -> back-to-front replay per 16x16 tile (replaces renderCUDA, reference
+//                      cuda_rasterizer/backward.cu:399-557). Per-Gaussian partials are reduced across the warp with
+//                      shuffles, accumulated per tile batch in shared memory, and flushed with ONE global atomic per
+//                      (tile instance, component) instead of one per (pixel, Gaussian) pair (backward.cu:523-554).
+//   preprocess_bwd  -> computeCov2DCUDA (backward.cu:144-274) + preprocessCUDA (:346-396) + SH backward (:20-139) +
+//                      cov3D backward (:278-341) fused into one pass that also writes the zeros the reference gets from
+//                      nine torch::zeros fills (rasterize_points.cu:151-159).
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace das3r {
+
+constexpr int BLEND_BATCH = 256;
+constexpr int NACC = 9;
+
+struct BlendBwdSmem {
+    GaussRec rec[2][BLEND_BATCH];
+    float acc[NACC][BLEND_BATCH];
+    uint64_t bar[2];
+    uint32_t warp_max[8];
+};
+
+__global__ void __launch_bounds__(256) blend_bwd_kernel(const uint2* __restrict__ ranges,
+                                                        const uint32_t* __restrict__ point_list,
+                                                        const GaussRec* __restrict__ sorted_rec, int W, int H,
+                                                        const float* __restrict__ bg,
+                                                        const float* __restrict__ final_Ts,
+                                                        const uint32_t* __restrict__ n_contrib,
+                                                        const float* __restrict__ dL_dpixels,
+                                                        float* __restrict__ acc_out) {
+    __shared__ __align__(128) BlendBwdSmem sm;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int n = (int)(range.y - range.x);
+    if (n == 0) return;
+
+    const int wx0 = blockIdx.x * TILE_X + (warp & 1) * 8;
+    const int wy0 = blockIdx.y * TILE_Y + (warp >> 1) * 4;
+    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const int pix_id = W * py + px;
+    const float2 pixf = {(float)px, (float)py};
+    const float rx0 = (float)wx0, rx1 = (float)(wx0 + 7), ry0 = (float)wy0, ry1 = (float)(wy0 + 3);
+
+    // backward.cu:431-458
+    const float T_final = inside ? final_Ts[pix_id] : 0;
+    float T = T_final;
+    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0;
+    float accum_rec[3] = {0.f, 0.f, 0.f};
+    float dL_dpixel[3] = {0.f, 0.f, 0.f};
+    if (inside)
+#pragma unroll
+        for (int i = 0; i < 3; i++) dL_dpixel[i] = dL_dpixels[i * H * W + pix_id];
+    float last_alpha = 0;
+    float last_color[3] = {0.f, 0.f, 0.f};
+    const float ddelx_dx = 0.5 * W;
+    const float ddely_dy = 0.5 * H;
+    float bg_dot_dpixel = 0;
+#pragma unroll
+    for (int i = 0; i < 3; i++) bg_dot_dpixel += bg[i] * dL_dpixel[i];
+
+    // Highest list position any pixel of this warp / block still needs.
+    uint32_t wmax = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    if (lane == 0) sm.warp_max[warp] = wmax;
+    if (tid == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        mbar_fence_init();
+    }
+    for (int i = tid; i < NACC * BLEND_BATCH; i += 256) (&sm.acc[0][0])[i] = 0.f;
+    __syncthreads();
+    uint32_t bmax = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) bmax = max(bmax, sm.warp_max[w]);
+    if (bmax == 0) return;  // nothing contributed anywhere in this tile
+    const int bstart = (int)((bmax - 1) / BLEND_BATCH);
+    const int nsteps = bstart + 1;
+
+    auto batch_count = [&](int b) { return min(BLEND_BATCH, n - b * BLEND_BATCH); };
+    if (tid == 0) {
+        for (int i = 0; i < min(nsteps, 2); i++) {
+            int b = bstart - i;
+            uint32_t bytes = (uint32_t)batch_count(b) * (uint32_t)sizeof(GaussRec);
+            mbar_expect_tx(&sm.bar[i], bytes);
+            tma_load_1d(&sm.rec[i][0], sorted_rec + range.x + (size_t)b * BLEND_BATCH, bytes, &sm.bar[i]);
+        }
+    }
+
+    for (int i = 0; i < nsteps; i++) {
+        const int b = bstart - i;
+        const int st = i & 1;
+        const int cnt = batch_count(b);
+        mbar_wait(&sm.bar[st], (uint32_t)((i >> 1) & 1));
+        const GaussRec* rec = sm.rec[st];
+        const int base_pos = b * BLEND_BATCH;
+
+        if ((uint32_t)base_pos < wmax) {
+            // chunks of 32 list entries, highest first
+            for (int c0 = ((min(cnt, (int)wmax - base_pos) - 1) / 32) * 32; c0 >= 0; c0 -= 32) {
+                const int g = c0 + lane;
+                bool ov = false;
+                if (g < cnt) {
+                    float4 A = rec[g].A;
+                    ov = (A.z >= 0.f) && (A.x + A.z >= rx0) && (A.x - A.z <= rx1) && (A.y + A.w >= ry0) &&
+                         (A.y - A.w <= ry1);
+                }
+                unsigned m = __ballot_sync(0xffffffffu, ov);
+                while (m) {
+                    const int j = 31 - __clz(m);
+                    m &= ~(1u << j);
+                    const int gi = c0 + j;
+                    const uint32_t pos = (uint32_t)(base_pos + gi);
+                    float gr[NACC];
+#pragma unroll
+                    for (int k = 0; k < NACC; k++) gr[k] = 0.f;
+                    bool contrib = false;
+                    if (pos < last_contributor) {
+                        // backward.cu:490-554
+                        const float4 A = rec[gi].A;
+                        const float4 con_o = rec[gi].B;
+                        const float2 d = {A.x - pixf.x, A.y - pixf.y};
+                        const float power =
+                            -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                        if (!(power > 0.0f)) {
+                            const float G = expf(power);
+                            const float alpha = min(0.99f, con_o.w * G);
+                            if (!(alpha < 1.0f / 255.0f)) {
+                                contrib = true;
+                                const float4 col4 = rec[gi].C;
+                                const float col[3] = {col4.x, col4.y, col4.z};
+                                T = T / (1.f - alpha);
+                                const float dchannel_dcolor = alpha * T;
+                                float dL_dalpha = 0.0f;
+#pragma unroll
+                                for (int ch = 0; ch < 3; ch++) {
+                                    const float c = col[ch];
+                                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                                    last_color[ch] = c;
+                                    const float dL_dchannel = dL_dpixel[ch];
+                                    dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
+                                    gr[6 + ch] = dchannel_dcolor * dL_dchannel;
+                                }
+                                dL_dalpha *= T;
+                                last_alpha = alpha;
+                                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                                const float dL_dG = con_o.w * dL_dalpha;
+                                const float gdx = G * d.x;
+                                const float gdy = G * d.y;
+                                const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
+                                const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
+                                gr[0] = dL_dG * dG_ddelx * ddelx_dx;
+                                gr[1] = dL_dG * dG_ddely * ddely_dy;
+                                gr[2] = -0.5f * gdx * d.x * dL_dG;
+                                gr[3] = -0.5f * gdx * d.y * dL_dG;
+                                gr[4] = -0.5f * gdy * d.y * dL_dG;
+                                gr[5] = G * dL_dalpha;
+                            }
+                        }
+                    }
+                    if (__ballot_sync(0xffffffffu, contrib) != 0) {
+#pragma unroll
+                        for (int k = 0; k < NACC; k++) {
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) gr[k] += __shfl_xor_sync(0xffffffffu, gr[k], o);
+                        }
+                        // lane k adds component k: pick it without dynamic register indexing
+                        float v = gr[0];
+#pragma unroll
+                        for (int k = 1; k < NACC; k++) v = (lane == k) ? gr[k] : v;
+                        if (lane < NACC) atomicAdd(&sm.acc[lane][gi], v);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        // flush this batch's accumulators: one global atomic per (tile instance, component)
+        if (tid < cnt) {
+            float v[NACC];
+            bool any = false;
+#pragma unroll
+            for (int k = 0; k < NACC; k++) {
+                v[k] = sm.acc[k][tid];
+                any = any || (v[k] != 0.f);
+                sm.acc[k][tid] = 0.f;
+            }
+            if (any) {
+                const uint32_t gid = point_list[range.x + base_pos + tid];
+                float* dst = acc_out + (size_t)gid * ACC_STRIDE;
+#pragma unroll
+                for (int k = 0; k < NACC; k++)
+                    if (v[k] != 0.f) atomicAdd(dst + k, v[k]);
+            }
+        }
+        __syncthreads();
+        if (tid == 0 && i + 2 < nsteps) {
+            int b2 = b - 2;
+            uint32_t bytes = (uint32_t)batch_count(b2) * (uint32_t)sizeof(GaussRec);
+            mbar_expect_tx(&sm.bar[st], bytes);
+            tma_load_1d(&sm.rec[st][0], sorted_rec + range.x + (size_t)b2 * BLEND_BATCH, bytes, &sm.bar[st]);
+        }
+    }
+}
+
+cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* point_list,
+                             const GaussRec* sorted_rec, int W, int H, const float* bg, const float* final_T,
+                             const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t s) {
+    dim3 grid(gx, gy, 1);
+    blend_bwd_kernel<<<grid, 256, 0, s>>>(ranges, point_list, sorted_rec, W, H, bg, final_T, n_contrib, dL_dpix, acc);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// preprocess_bwd
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float3 dnormvdv3(float3 v, float3 dv) {  // auxiliary.h:107-117
+    float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+    float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    float3 r;
+    r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+    r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+    r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+    return r;
+}
+
+struct V3 {
+    float x, y, z;
+};
+__device__ __forceinline__ V3 operator*(float s, V3 v) { return {s * v.x, s * v.y, s * v.z}; }
+__device__ __forceinline__ V3 operator*(V3 v, float s) { return {v.x * s, v.y * s, v.z * s}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ V3& operator+=(V3& a, V3 b) {
+    a.x += b.x; a.y += b.y; a.z += b.z;
+    return a;
+}
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+// SH backward (backward.cu:20-139). sh[k] / out[k] are rows of 3 floats. Writes the first (deg+1)^2 rows of `out`
+// (the caller zero-fills the rest) and returns the view-direction part of dL_dmean.
+__device__ __forceinline__ float3 sh_backward(int deg, const float* f, float3 pos, float3 campos, uint8_t clamped,
+                                              float3 dL_dcolor, float* out) {
+    float3 dir_orig = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
+    float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+    float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+    V3 dL_dRGB = {dL_dcolor.x, dL_dcolor.y, dL_dcolor.z};
+    dL_dRGB.x *= (clamped & 1) ? 0 : 1;
+    dL_dRGB.y *= (clamped & 2) ? 0 : 1;
+    dL_dRGB.z *= (clamped & 4) ? 0 : 1;
+    auto sh = [&](int k) -> V3 { return {f[3 * k], f[3 * k + 1], f[3 * k + 2]}; };
+    auto put = [&](int k, float w) {
+        out[3 * k] = w * dL_dRGB.x;
+        out[3 * k + 1] = w * dL_dRGB.y;
+        out[3 * k + 2] = w * dL_dRGB.z;
+    };
+    V3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
+    put(0, kSH0);
+    if (deg > 0) {
+        put(1, -kSH1 * y);
+        put(2, kSH1 * z);
+        put(3, -kSH1 * x);
+        dRGBdx = -kSH1 * sh(3);
+        dRGBdy = -kSH1 * sh(1);
+        dRGBdz = kSH1 * sh(2);
+        if (deg > 1) {
+            float xx = x * x, yy = y * y, zz = z * z;
+            float xy = x * y, yz = y * z, xz = x * z;
+            put(4, kSH2[0] * xy);
+            put(5, kSH2[1] * yz);
+            put(6, kSH2[2] * (2.f * zz - xx - yy));
+            put(7, kSH2[3] * xz);
+            put(8, kSH2[4] * (xx - yy));
+            dRGBdx += kSH2[0] * y * sh(4) + kSH2[2] * 2.f * -x * sh(6) + kSH2[3] * z * sh(7) + kSH2[4] * 2.f * x * sh(8);
+            dRGBdy += kSH2[0] * x * sh(4) + kSH2[1] * z * sh(5) + kSH2[2] * 2.f * -y * sh(6) + kSH2[4] * 2.f * -y * sh(8);
+            dRGBdz += kSH2[1] * y * sh(5) + kSH2[2] * 2.f * 2.f * z * sh(6) + kSH2[3] * x * sh(7);
+            if (deg > 2) {
+                put(9, kSH3[0] * y * (3.f * xx - yy));
+                put(10, kSH3[1] * xy * z);
+                put(11, kSH3[2] * y * (4.f * zz - xx - yy));
+                put(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+                put(13, kSH3[4] * x * (4.f * zz - xx - yy));
+                put(14, kSH3[5] * z * (xx - yy));
+                put(15, kSH3[6] * x * (xx - 3.f * yy));
+                dRGBdx += (kSH3[0] * sh(9) * 3.f * 2.f * xy + kSH3[1] * sh(10) * yz + kSH3[2] * sh(11) * -2.f * xy +
+                           kSH3[3] * sh(12) * -3.f * 2.f * xz + kSH3[4] * sh(13) * (-3.f * xx + 4.f * zz - yy) +
+                           kSH3[5] * sh(14) * 2.f * xz + kSH3[6] * sh(15) * 3.f * (xx - yy));
+                dRGBdy += (kSH3[0] * sh(9) * 3.f * (xx - yy) + kSH3[1] * sh(10) * xz +
+                           kSH3[2] * sh(11) * (-3.f * yy + 4.f * zz - xx) + kSH3[3] * sh(12) * -3.f * 2.f * yz +
+                           kSH3[4] * sh(13) * -2.f * xy + kSH3[5] * sh(14) * -2.f * yz +
+                           kSH3[6] * sh(15) * -3.f * 2.f * xy);
+                dRGBdz += (kSH3[1] * sh(10) * xy + kSH3[2] * sh(11) * 4.f * 2.f * yz +
+                           kSH3[3] * sh(12) * 3.f * (2.f * zz - xx - yy) + kSH3[4] * sh(13) * 4.f * 2.f * xz +
+                           kSH3[5] * sh(14) * (xx - yy));
+            }
+        }
+    }
+    float3 dL_ddir = {dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB)};
+    return dnormvdv3(dir_orig, dL_ddir);
+}
+
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P) return;
+    const int nsh = 3 * a.M;  // floats per dL_dsh row
+    float* sh_out = a.dL_dsh ? a.dL_dsh + (size_t)idx * nsh : nullptr;
+    const bool sh_aligned = ((a.M & 3) == 0);
+
+    if (!(a.radii[idx] > 0)) {
+        // invisible: every gradient is zero (the reference relies on torch::zeros for this)
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            a.dL_dmeans2D[3 * idx + k] = 0.f;
+            a.dL_dcolors[3 * idx + k] = 0.f;
+            a.dL_dmeans3D[3 * idx + k] = 0.f;
+            a.dL_dscales[3 * idx + k] = 0.f;
+        }
+        a.dL_dopacity[idx] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = 0.f;
+        reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (sh_out) {
+            if (sh_aligned && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
+                float4* o4 = reinterpret_cast<float4*>(sh_out);
+                for (int j = 0; j < nsh / 4; j++) o4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+                for (int j = 0; j < nsh; j++) sh_out[j] = 0.f;
+            }
+        }
+        return;
+    }
+
+    const float4* acc4 = reinterpret_cast<const float4*>(a.acc + (size_t)idx * ACC_STRIDE);
+    const float4 q0 = acc4[0], q1 = acc4[1], q2 = acc4[2];
+    const float dL_dmean2D_x = q0.x, dL_dmean2D_y = q0.y;
+    const float3 dL_dconic = {q0.z, q0.w, q1.x};  // (x, y, w) of the reference's float4
+    const float dL_dopac = q1.y;
+    const float3 dL_dcol = {q1.z, q1.w, q2.x};
+
+    a.dL_dmeans2D[3 * idx + 0] = dL_dmean2D_x;
+    a.dL_dmeans2D[3 * idx + 1] = dL_dmean2D_y;
+    a.dL_dmeans2D[3 * idx + 2] = 0.f;
+    a.dL_dcolors[3 * idx + 0] = dL_dcol.x;
+    a.dL_dcolors[3 * idx + 1] = dL_dcol.y;
+    a.dL_dcolors[3 * idx + 2] = dL_dcol.z;
+    a.dL_dopacity[idx] = dL_dopac;
+
+    const float3 mean = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
+    float cov3D[6];
+    float3 sc = {0.f, 0.f, 0.f};
+    float4 rq = {0.f, 0.f, 0.f, 0.f};
+    if (a.cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D_precomp[6 * idx + k];
+    } else {
+        sc = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
+        rq = __ldg(reinterpret_cast<const float4*>(a.rots) + idx);
+        cov3d_from_scale_rot(sc, a.scale_mod, rq, cov3D);  // recomputed instead of stored (same code as forward)
+    }
+
+    // ---- computeCov2DCUDA, backward.cu:162-273 ----
+    const float h_x = a.focal_x, h_y = a.focal_y;
+    Ewa e = ewa_project(mean, h_x, h_y, a.tan_fovx, a.tan_fovy, cov3D, a.view);
+    const float3 t = e.t;
+    const float x_grad_mul = e.txtz < -e.limx || e.txtz > e.limx ? 0 : 1;
+    const float y_grad_mul = e.tytz < -e.limy || e.tytz > e.limy ? 0 : 1;
+    const Mat3& T = e.T;
+    const Mat3& Vrk = e.Vrk;
+    const float ca = e.a, cb = e.b, cc = e.c;
+    float denom = ca * cc - cb * cb;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float dL_dcov[6];
+    if (denom2inv != 0) {
+        dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
+        dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
+        dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
+        dL_dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+        dL_dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+        dL_dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+        dL_dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+                     2 * T.m[1][0] * T.m[1][1] * dL_dc;
+        dL_dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+                     2 * T.m[1][0] * T.m[1][2] * dL_dc;
+        dL_dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+                     2 * T.m[1][1] * T.m[1][2] * dL_dc;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 6; i++) dL_dcov[i] = 0;
+    }
+#pragma unroll
+    for (int i = 0; i < 6; i++) a.dL_dcov3D[6 * idx + i] = dL_dcov[i];
+
+    float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
+                    (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
+    float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
+                    (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
+    float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
+                    (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
+    float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
+                    (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
+    float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
+                    (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
+    float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
+                    (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
+
+    // W as built in ewa_project: W.m[c][r] = view[4*r + c]  (glm::mat3(view[0], view[4], view[8], ...))
+    const float* vm = a.view;
+    const float W00 = vm[0], W01 = vm[4], W02 = vm[8];
+    const float W10 = vm[1], W11 = vm[5], W12 = vm[9];
+    const float W20 = vm[2], W21 = vm[6], W22 = vm[10];
+    float dL_dJ00 = W00 * dL_dT00 + W01 * dL_dT01 + W02 * dL_dT02;
+    float dL_dJ02 = W20 * dL_dT00 + W21 * dL_dT01 + W22 * dL_dT02;
+    float dL_dJ11 = W10 * dL_dT10 + W11 * dL_dT11 + W12 * dL_dT12;
+    float dL_dJ12 = W20 * dL_dT10 + W21 * dL_dT11 + W22 * dL_dT12;
+
+    float tz = 1.f / t.z;
+    float tz2 = tz * tz;
+    float tz3 = tz2 * tz;
+    float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                   (2 * h_y * t.y) * tz3 * dL_dJ12;
+    float3 dL_dmean_acc = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, a.view);
+
+    // ---- preprocessCUDA (backward.cu:366-395) ----
+    const float* proj = a.proj;
+    float4 m_hom = xform_point_4x4(mean, proj);
+    float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+    float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+    float3 dL_dmean;
+    dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D_y;
+    dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D_y;
+    dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D_y;
+    dL_dmean_acc.x += dL_dmean.x;
+    dL_dmean_acc.y += dL_dmean.y;
+    dL_dmean_acc.z += dL_dmean.z;
+
+    if (a.shs != nullptr && sh_out != nullptr) {
+        float f[48];
+        float o[48];
+        const float* row = a.shs + (size_t)idx * nsh;
+        const bool al = sh_aligned && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+        load_sh_row(row, a.D, al, f);
+        float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
+        float3 dm = sh_backward(a.D, f, mean, cam, a.clamped[idx], dL_dcol, o);
+        dL_dmean_acc.x += dm.x;
+        dL_dmean_acc.y += dm.y;
+        dL_dmean_acc.z += dm.z;
+        const int nw = 3 * (a.D + 1) * (a.D + 1);
+        if (a.M == 16 && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
+            float4* o4 = reinterpret_cast<float4*>(sh_out);
+#pragma unroll
+            for (int j = 0; j < 12; j++) {
+                float4 v;
+                v.x = (4 * j + 0 < nw) ? o[4 * j + 0] : 0.f;
+                v.y = (4 * j + 1 < nw) ? o[4 * j + 1] : 0.f;
+                v.z = (4 * j + 2 < nw) ? o[4 * j + 2] : 0.f;
+                v.w = (4 * j + 3 < nw) ? o[4 * j + 3] : 0.f;
+                o4[j] = v;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 48; j++)
+                if (j < nsh) sh_out[j] = (j < nw) ? o[j] : 0.f;
+        }
+    }
+    a.dL_dmeans3D[3 * idx + 0] = dL_dmean_acc.x;
+    a.dL_dmeans3D[3 * idx + 1] = dL_dmean_acc.y;
+    a.dL_dmeans3D[3 * idx + 2] = dL_dmean_acc.z;
+
+    // ---- computeCov3D backward (backward.cu:278-341) ----
+    if (a.scales != nullptr) {
+        float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
+        Mat3 R = mat3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                      2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                      2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+        Mat3 S = mat3(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+        float3 s = {a.scale_mod * sc.x, a.scale_mod * sc.y, a.scale_mod * sc.z};
+        S.m[0][0] = s.x;
+        S.m[1][1] = s.y;
+        S.m[2][2] = s.z;
+        Mat3 M = mul(S, R);
+        Mat3 dL_dSigma = mat3(dL_dcov[0], 0.5f * dL_dcov[1], 0.5f * dL_dcov[2], 0.5f * dL_dcov[1], dL_dcov[3],
+                              0.5f * dL_dcov[4], 0.5f * dL_dcov[2], 0.5f * dL_dcov[4], dL_dcov[5]);
+        // dL_dM = 2.0f * M * dL_dSigma  (glm: scalar*mat first, then the product)
+        Mat3 M2;
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int rr = 0; rr < 3; rr++) M2.m[c][rr] = 2.0f * M.m[c][rr];
+        Mat3 dL_dM = mul(M2, dL_dSigma);
+        Mat3 Rt = transpose(R);
+        Mat3 dL_dMt = transpose(dL_dM);
+        float3 dsc;
+        dsc.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+        dsc.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+        dsc.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+        a.dL_dscales[3 * idx + 0] = dsc.x;
+        a.dL_dscales[3 * idx + 1] = dsc.y;
+        a.dL_dscales[3 * idx + 2] = dsc.z;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            dL_dMt.m[0][k] *= s.x;
+            dL_dMt.m[1][k] *= s.y;
+            dL_dMt.m[2][k] *= s.z;
+        }
+        float4 dq;
+        dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+               2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
+        dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+               2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
+        dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+               2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
+        dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+               2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
+        reinterpret_cast<float4*>(a.dL_drots)[idx] = dq;
+    } else {
+        a.dL_dscales[3 * idx + 0] = 0.f;
+        a.dL_dscales[3 * idx + 1] = 0.f;
+        a.dL_dscales[3 * idx + 2] = 0.f;
+        reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s) {
+    preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace das3r

@@ -1,0 +1,685 @@
+// Forward path of the sm_100a Gaussian-splat rasterizer:
+//   preprocess_fwd  -> per-Gaussian projection / EWA covariance / SH colour / tile rectangle  (replaces
+//                      preprocessCUDA, reference cuda_rasterizer/forward.cu:155-256) + per-tile histogram
+//   tile_scan       -> exclusive scan of the T tile counts = tile ranges (replaces the P-sized InclusiveSum,
+//                      rasterizer_impl.cu:277, and identifyTileRanges, :116-138)
+//   scatter         -> one (depth|index) entry per (Gaussian, tile) pair into its tile bucket (replaces
+//                      duplicateWithKeys, rasterizer_impl.cu:70-111)
+//   tile_sort       -> per-tile bitonic sort in registers/shuffles/shared memory (replaces the global 64-bit
+//                      cub::DeviceRadixSort, rasterizer_impl.cu:303-308) + gather of tile-ordered records
+//   blend_fwd       -> front-to-back alpha blend per 16x16 tile (replaces renderCUDA, forward.cu:261-374)
+//
+// The result of scatter+tile_sort is bit-identical to the reference's stable LSD radix sort of (tile<<32|depth)
+// keys: equal keys keep emission order there, i.e. ascending Gaussian index, so the total order is
+// (tile, depth bits, Gaussian index) and any correct sort on that triple reproduces point_list exactly.
+#include "common.cuh"
+#include "kernels.cuh"
+#include <cub/device/device_segmented_radix_sort.cuh>
+#include <stdio.h>
+
+namespace das3r {
+
+// ---------------------------------------------------------------------------------------------------------------
+// SH evaluation (forward.cu:20-71). f[] holds the row as 3*k+c floats; only the first 3*(deg+1)^2 are defined.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float3 sh_to_rgb(int deg, const float* f, float3 pos, float3 campos, uint8_t& clamped) {
+    float3 dir = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
+    float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+    dir.x = dir.x / len;
+    dir.y = dir.y / len;
+    dir.z = dir.z / len;
+    float res[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) res[c] = kSH0 * f[c];
+    if (deg > 0) {
+        float x = dir.x, y = dir.y, z = dir.z;
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+            res[c] = res[c] - kSH1 * y * f[3 + c] + kSH1 * z * f[6 + c] - kSH1 * x * f[9 + c];
+        if (deg > 1) {
+            float xx = x * x, yy = y * y, zz = z * z;
+            float xy = x * y, yz = y * z, xz = x * z;
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                res[c] = res[c] + kSH2[0] * xy * f[12 + c] + kSH2[1] * yz * f[15 + c] +
+                         kSH2[2] * (2.0f * zz - xx - yy) * f[18 + c] + kSH2[3] * xz * f[21 + c] +
+                         kSH2[4] * (xx - yy) * f[24 + c];
+            if (deg > 2) {
+#pragma unroll
+                for (int c = 0; c < 3; c++)
+                    res[c] = res[c] + kSH3[0] * y * (3.0f * xx - yy) * f[27 + c] + kSH3[1] * xy * z * f[30 + c] +
+                             kSH3[2] * y * (4.0f * zz - xx - yy) * f[33 + c] +
+                             kSH3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * f[36 + c] +
+                             kSH3[4] * x * (4.0f * zz - xx - yy) * f[39 + c] + kSH3[5] * z * (xx - yy) * f[42 + c] +
+                             kSH3[6] * x * (xx - 3.0f * yy) * f[45 + c];
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; c++) res[c] += 0.5f;
+    clamped = (uint8_t)((res[0] < 0 ? 1 : 0) | (res[1] < 0 ? 2 : 0) | (res[2] < 0 ? 4 : 0));
+    return make_float3(res[0] < 0.0f ? 0.0f : res[0], res[1] < 0.0f ? 0.0f : res[1], res[2] < 0.0f ? 0.0f : res[2]);
+}
+
+constexpr int PRE_THREADS = 256;
+constexpr int SH_ROW_F4 = 12;      // 48 floats = 12 float4 per degree-3 row
+constexpr int SH_ROW_PAD_F4 = 13;  // padded row pitch in shared memory: 13 float4 (odd) -> conflict-free LDS.128
+
+// ---------------------------------------------------------------------------------------------------------------
+// preprocess_fwd. STAGE_SH: the block's 256 degree-3 SH rows (48 KB contiguous) are brought into shared memory with
+// coalesced 16-byte cp.async while the geometry is computed, then read back row-wise without bank conflicts.
+// ---------------------------------------------------------------------------------------------------------------
+template <bool STAGE_SH>
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFwdArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* sh_stage = reinterpret_cast<float4*>(smem_raw);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + (STAGE_SH ? PRE_THREADS * SH_ROW_PAD_F4 * 16 : 0));
+
+    const int tid = threadIdx.x;
+    const int base = blockIdx.x * PRE_THREADS;
+    const int idx = base + tid;
+    const int T = (int)(a.gx * a.gy);
+
+    if (a.smem_hist)
+        for (int i = tid; i < T; i += PRE_THREADS) hist[i] = 0;
+
+    if (STAGE_SH) {
+        const int nvalid = min(PRE_THREADS, a.P - base);
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)base * SH_ROW_F4;
+        const int total = nvalid * SH_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < SH_ROW_F4; k++) {
+            int e = tid + k * PRE_THREADS;
+            if (e < total) {
+                int g = e / SH_ROW_F4, j = e - g * SH_ROW_F4;
+                cp_async_16(&sh_stage[g * SH_ROW_PAD_F4 + j], src + e);
+            }
+        }
+        cp_async_commit();
+    }
+
+    bool vis = false;
+    float my_radius = 0.f;
+    uint2 rmin = {0, 0}, rmax = {0, 0};
+    float2 point_image = {0.f, 0.f};
+    float3 p_orig = {0.f, 0.f, 0.f};
+    float3 conic = {0.f, 0.f, 0.f};
+    float depth = 0.f, opacity = 0.f, hx = -1.f, hy = -1.f;
+
+    if (idx < a.P) {
+        p_orig = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
+        // in_frustum (auxiliary.h:139-164) with the 0.001 near plane.
+        float4 p_hom = xform_point_4x4(p_orig, a.proj);
+        float p_w = 1.0f / (p_hom.w + 0.0000001f);
+        float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+        float3 p_view = xform_point_4x3(p_orig, a.view);
+        if (p_view.z <= NEAR_Z) {
+            if (a.prefiltered) {
+                printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+                __trap();
+            }
+        } else {
+            float cov3D[6];
+            if (a.cov3D_precomp != nullptr) {
+#pragma unroll
+                for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D_precomp[6 * idx + k];
+            } else {
+                float3 sc = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
+                float4 rq = __ldg(reinterpret_cast<const float4*>(a.rots) + idx);
+                cov3d_from_scale_rot(sc, a.scale_mod, rq, cov3D);
+            }
+            Ewa e = ewa_project(p_orig, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, cov3D, a.view);
+            float3 cov = {e.a, e.b, e.c};
+            // forward.cu:218-237
+            float det = (cov.x * cov.z - cov.y * cov.y);
+            if (det != 0.0f) {
+                float det_inv = 1.f / det;
+                conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+                float mid = 0.5f * (cov.x + cov.z);
+                float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
+                float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
+                my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+                point_image = {ndc_to_pix(p_proj.x, a.W), ndc_to_pix(p_proj.y, a.H)};
+                tile_rect(point_image, (int)my_radius, rmin, rmax, a.gx, a.gy);
+                if ((rmax.x - rmin.x) * (rmax.y - rmin.y) != 0) {
+                    vis = true;
+                    depth = p_view.z;
+                    opacity = a.opac[idx];
+                    // Conservative half-extent of {alpha >= 1/255}: 0.5*d^T Q d <= tau with tau = ln(255*opacity),
+                    // bounding box of that ellipse = sqrt(2*tau*inv(Q)_xx). Computed in double from the ROUNDED conic
+                    // the blend will use, with a relative and an absolute margin, so a pair skipped by the warp-level
+                    // test is always one the reference would have skipped by `alpha < 1/255` (forward.cu:340).
+                    float o255 = 255.f * opacity;
+                    if (o255 > 1.0f) {
+                        double tau = (double)logf(o255) * 1.0001 + 1e-4;
+                        double qa = conic.x, qb = conic.y, qc = conic.z;
+                        double qdet = qa * qc - qb * qb;
+                        if (qdet > 0.0 && qa > 0.0 && qc > 0.0) {
+                            hx = (float)(sqrt(2.0 * tau * qc / qdet) * 1.0001 + 0.01);
+                            hy = (float)(sqrt(2.0 * tau * qa / qdet) * 1.0001 + 0.01);
+                        } else {
+                            hx = hy = 3.0e38f;  // degenerate conic: never cull
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    if (STAGE_SH) cp_async_wait_all();
+    __syncthreads();
+
+    if (idx < a.P) {
+        a.radii[idx] = vis ? (int)my_radius : 0;
+        a.tiles_touched[idx] = vis ? (rmax.y - rmin.y) * (rmax.x - rmin.x) : 0u;
+    }
+    if (vis) {
+        float3 rgb;
+        uint8_t cl = 0;
+        if (a.colors_precomp == nullptr) {
+            float f[48];
+            if (STAGE_SH) {
+#pragma unroll
+                for (int j = 0; j < SH_ROW_F4; j++) {
+                    float4 v = sh_stage[tid * SH_ROW_PAD_F4 + j];
+                    f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
+                }
+            } else {
+                const float* row = a.shs + (size_t)idx * 3 * a.M;
+                bool aligned = ((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+                load_sh_row(row, a.D, aligned, f);
+            }
+            float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
+            rgb = sh_to_rgb(a.D, f, p_orig, cam, cl);
+        } else {
+            rgb = {a.colors_precomp[3 * idx], a.colors_precomp[3 * idx + 1], a.colors_precomp[3 * idx + 2]};
+        }
+        GaussRec r;
+        r.A = make_float4(point_image.x, point_image.y, hx, hy);
+        r.B = make_float4(conic.x, conic.y, conic.z, opacity);
+        r.C = make_float4(rgb.x, rgb.y, rgb.z, depth);
+        a.rec[idx] = r;
+        a.clamped[idx] = cl;
+        // Tile histogram (this replaces the prefix sum over all P Gaussians of the reference).
+        for (unsigned y = rmin.y; y < rmax.y; y++)
+            for (unsigned x = rmin.x; x < rmax.x; x++) {
+                if (a.smem_hist)
+                    atomicAdd(&hist[y * a.gx + x], 1u);
+                else
+                    atomicAdd(&a.tile_counts[y * a.gx + x], 1u);
+            }
+    }
+    if (a.smem_hist) {
+        __syncthreads();
+        for (int i = tid; i < T; i += PRE_THREADS) {
+            uint32_t v = hist[i];
+            if (v) atomicAdd(&a.tile_counts[i], v);
+        }
+    }
+}
+
+constexpr int SMEM_HIST_MAX_TILES = 8192;
+
+cudaError_t launch_preprocess_fwd(const PreFwdArgs& a_in, bool stage_sh, cudaStream_t s) {
+    PreFwdArgs a = a_in;
+    const int T = (int)(a.gx * a.gy);
+    a.smem_hist = (T <= SMEM_HIST_MAX_TILES) ? 1 : 0;
+    const size_t hist_bytes = a.smem_hist ? (size_t)T * 4 : 0;
+    const int blocks = (a.P + PRE_THREADS - 1) / PRE_THREADS;
+    stage_sh = stage_sh && a.shs != nullptr && a.colors_precomp == nullptr && a.D == 3 && a.M == 16 &&
+               ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+    if (stage_sh) {
+        size_t smem = (size_t)PRE_THREADS * SH_ROW_PAD_F4 * 16 + hist_bytes;
+        cudaError_t e =
+            cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        preprocess_fwd_kernel<true><<<blocks, PRE_THREADS, smem, s>>>(a);
+    } else {
+        preprocess_fwd_kernel<false><<<blocks, PRE_THREADS, hist_bytes, s>>>(a);
+    }
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// tile_scan: one block. ranges[t] = (start, end) for non-empty tiles and (0,0) for empty ones, exactly what the
+// reference's memset + identifyTileRanges leave behind (rasterizer_impl.cu:310-318).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(SCAN_THREADS) tile_scan_kernel(const uint32_t* __restrict__ counts, int T,
+                                                                 uint2* __restrict__ ranges,
+                                                                 uint32_t* __restrict__ cursors,
+                                                                 uint32_t* __restrict__ totals) {
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t warp_max[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (T + SCAN_THREADS - 1) / SCAN_THREADS;
+    const int beg = tid * per, end = min(T, beg + per);
+    uint32_t sum = 0, mx = 0;
+    for (int i = beg; i < end; i++) {
+        uint32_t c = counts[i];
+        sum += c;
+        mx = max(mx, c);
+    }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 31) warp_sum[warp] = incl;
+    if (lane == 0) warp_max[warp] = mx;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = warp_sum[lane];
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        warp_sum[lane] = wi - w;  // exclusive
+        uint32_t m = warp_max[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 31) totals[0] = wi;
+        if (lane == 0) {
+            totals[1] = m;
+            totals[2] = 0;
+            totals[3] = 0;
+        }
+    }
+    __syncthreads();
+    uint32_t run = warp_sum[warp] + incl - sum;
+    for (int i = beg; i < end; i++) {
+        uint32_t c = counts[i];
+        ranges[i] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+        cursors[i] = run;
+        run += c;
+    }
+}
+
+cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,
+                             cudaStream_t s) {
+    tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(counts, T, ranges, cursors, totals);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// scatter: (Gaussian, tile) pairs into tile buckets. Entry = depth_bits << 32 | gaussian index. The slot order
+// inside a bucket is arbitrary (atomic cursor); the tile sort makes the final order deterministic.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) scatter_kernel(int P, unsigned gx, unsigned gy, const GaussRec* __restrict__ rec,
+                                                      const int* __restrict__ radii,
+                                                      const uint32_t* __restrict__ tiles_touched,
+                                                      uint32_t* __restrict__ cursors,
+                                                      uint64_t* __restrict__ unsorted) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    if (tiles_touched[idx] == 0) return;
+    float4 A = rec[idx].A;
+    float depth = rec[idx].C.w;
+    uint2 rmin, rmax;
+    tile_rect(make_float2(A.x, A.y), radii[idx], rmin, rmax, gx, gy);
+    uint64_t entry = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
+    for (unsigned y = rmin.y; y < rmax.y; y++)
+        for (unsigned x = rmin.x; x < rmax.x; x++) {
+            uint32_t slot = atomicAdd(&cursors[y * gx + x], 1u);
+            unsorted[slot] = entry;
+        }
+}
+
+cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,
+                           const uint32_t* tiles_touched, uint32_t* cursors, uint64_t* unsorted, cudaStream_t s) {
+    scatter_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, rec, radii, tiles_touched, cursors, unsorted);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// tile_sort: one block of 512 threads per tile, bitonic network over N = 512*E keys held E per thread (blocked):
+// strides < E in registers, E..16E by warp shuffles, >= 32E through shared memory.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_MAX_E = 32;
+
+__device__ __forceinline__ void cmpx(uint64_t& a, uint64_t& b, bool up) {
+    bool sw = (a > b) == up;
+    uint64_t lo = sw ? b : a, hi = sw ? a : b;
+    a = lo;
+    b = hi;
+}
+
+template <int E>
+__device__ __forceinline__ void bitonic_sort_tile(uint64_t* sm, const uint64_t* __restrict__ in, int n) {
+    constexpr int N = SORT_THREADS * E;
+    const int t = threadIdx.x;
+    uint64_t v[E];
+    // striped (coalesced) global read into shared, then blocked read-out
+    for (int i = t; i < N; i += SORT_THREADS) sm[i] = (i < n) ? in[i] : ~0ull;
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < E; r++) v[r] = sm[t * E + r];
+    __syncthreads();
+
+#pragma unroll 1
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll 1
+        for (int j = k >> 1; j >= 32 * E; j >>= 1) {
+            // cross-warp stride: exchange through shared memory, layout [r][t] (conflict-free both ways)
+            const int pt = t ^ (j / E);
+#pragma unroll
+            for (int r = 0; r < E; r++) sm[r * SORT_THREADS + t] = v[r];
+            __syncthreads();
+            const bool up = (((t * E) & k) == 0);
+            const bool keep_min = (((t * E) & j) == 0) == up;
+#pragma unroll
+            for (int r = 0; r < E; r++) {
+                uint64_t o = sm[r * SORT_THREADS + pt];
+                v[r] = keep_min ? min(v[r], o) : max(v[r], o);
+            }
+            __syncthreads();
+        }
+        {
+            int j = min(k >> 1, 16 * E);
+#pragma unroll 1
+            for (; j >= E; j >>= 1) {
+                const int mask = j / E;
+                const bool up = (((t * E) & k) == 0) || (k == N);  // (i & N) is always 0 for i < N
+                const bool keep_min = (((t * E) & j) == 0) == up;
+#pragma unroll
+                for (int r = 0; r < E; r++) {
+                    uint64_t o = __shfl_xor_sync(0xffffffffu, v[r], mask);
+                    v[r] = keep_min ? min(v[r], o) : max(v[r], o);
+                }
+            }
+        }
+        if (E > 1) {
+#pragma unroll
+            for (int j = E >> 1; j >= 1; j >>= 1) {
+                if (j < k) {
+#pragma unroll
+                    for (int r = 0; r < E; r++) {
+                        if ((r & j) == 0) {
+                            const int i = t * E + r;
+                            const bool up = ((i & k) == 0);
+                            cmpx(v[r], v[r | j], up);
+                        }
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < E; r++) sm[t * E + r] = v[r];
+    __syncthreads();
+}
+
+// MAXE bounds the per-thread key count the instantiation supports, so the common small-tile variants keep a low
+// register count (2 blocks/SM) and only the rare huge-tile variant pays for 32 keys per thread.
+template <int MAXE>
+__global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
+    tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ unsorted,
+                     const GaussRec* __restrict__ rec, uint32_t* __restrict__ point_list,
+                     GaussRec* __restrict__ sorted_rec, uint64_t* __restrict__ keys_sorted) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* sm = reinterpret_cast<uint64_t*>(smem_raw);
+    const uint32_t tile = blockIdx.x;
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+    if (n == 0) return;
+    const uint64_t* in = unsorted + range.x;
+    if (n <= SORT_THREADS * 1) bitonic_sort_tile<1>(sm, in, n);
+    else if (MAXE >= 2 && n <= SORT_THREADS * 2) bitonic_sort_tile<(MAXE >= 2 ? 2 : 1)>(sm, in, n);
+    else if (MAXE >= 4 && n <= SORT_THREADS * 4) bitonic_sort_tile<(MAXE >= 4 ? 4 : 1)>(sm, in, n);
+    else if (MAXE >= 8 && n <= SORT_THREADS * 8) bitonic_sort_tile<(MAXE >= 8 ? 8 : 1)>(sm, in, n);
+    else if (MAXE >= 16 && n <= SORT_THREADS * 16) bitonic_sort_tile<(MAXE >= 16 ? 16 : 1)>(sm, in, n);
+    else if (MAXE >= 32 && n <= SORT_THREADS * 32) bitonic_sort_tile<(MAXE >= 32 ? 32 : 1)>(sm, in, n);
+    else return;  // host never launches this variant when a tile exceeds its capacity
+    for (int i = threadIdx.x; i < n; i += SORT_THREADS) {
+        uint64_t key = sm[i];
+        uint32_t g = (uint32_t)key;
+        point_list[range.x + i] = g;
+        sorted_rec[range.x + i] = rec[g];
+        if (keys_sorted) keys_sorted[range.x + i] = ((uint64_t)tile << 32) | (key >> 32);
+    }
+}
+
+int tile_sort_capacity() { return SORT_THREADS * SORT_MAX_E; }
+
+template <int MAXE>
+static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const uint64_t* unsorted, const GaussRec* rec,
+                                            uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted,
+                                            cudaStream_t s) {
+    const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t);
+    if (smem > 48 * 1024) {
+        cudaError_t err =
+            cudaFuncSetAttribute(tile_sort_kernel<MAXE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return err;
+    }
+    tile_sort_kernel<MAXE><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sorted_rec, keys_sorted);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tile_sort(int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
+                             const GaussRec* rec, uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted,
+                             cudaStream_t s) {
+    if (max_count > (uint32_t)tile_sort_capacity()) return cudaErrorInvalidValue;
+    if (max_count <= SORT_THREADS * 4)
+        return launch_tile_sort_variant<4>(T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, s);
+    if (max_count <= SORT_THREADS * 8)
+        return launch_tile_sort_variant<8>(T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, s);
+    return launch_tile_sort_variant<32>(T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, s);
+}
+
+// Fallback for tiles larger than the in-shared-memory capacity: library segmented radix sort of the
+// (depth|index) entries, segment = tile, then the same gather.
+__global__ void gather_sorted_kernel(int R, int T, const uint2* __restrict__ ranges,
+                                     const uint64_t* __restrict__ sorted_entries, const GaussRec* __restrict__ rec,
+                                     uint32_t* __restrict__ point_list, GaussRec* __restrict__ sorted_rec,
+                                     uint64_t* __restrict__ keys_sorted) {
+    // one block per tile so the tile id is known without a search
+    const uint32_t tile = blockIdx.x;
+    const uint2 range = ranges[tile];
+    for (uint32_t i = range.x + threadIdx.x; i < range.y; i += blockDim.x) {
+        uint64_t key = sorted_entries[i];
+        uint32_t g = (uint32_t)key;
+        point_list[i] = g;
+        sorted_rec[i] = rec[g];
+        if (keys_sorted) keys_sorted[i] = ((uint64_t)tile << 32) | (key >> 32);
+    }
+}
+
+__global__ void ranges_to_offsets_kernel(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ beg,
+                                         uint32_t* __restrict__ end) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < T) {
+        beg[i] = ranges[i].x;
+        end[i] = ranges[i].y;
+    }
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+size_t tile_sort_fallback_bytes(int R, int T) {
+    size_t cub_bytes = 0;
+    cub::DeviceSegmentedRadixSort::SortKeys((void*)nullptr, cub_bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr, R,
+                                            T, (const uint32_t*)nullptr, (const uint32_t*)nullptr);
+    return align_up((size_t)R * 8, 256) + 2 * align_up((size_t)T * 4, 256) + align_up(cub_bytes, 256);
+}
+
+cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
+                                      uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted, void* temp,
+                                      size_t temp_bytes, cudaStream_t s) {
+    char* p = static_cast<char*>(temp);
+    uint64_t* sorted_entries = reinterpret_cast<uint64_t*>(p);
+    p += align_up((size_t)R * 8, 256);
+    uint32_t* beg = reinterpret_cast<uint32_t*>(p);
+    p += align_up((size_t)T * 4, 256);
+    uint32_t* end = reinterpret_cast<uint32_t*>(p);
+    p += align_up((size_t)T * 4, 256);
+    size_t cub_bytes = temp_bytes - (size_t)(p - static_cast<char*>(temp));
+    ranges_to_offsets_kernel<<<(T + 255) / 256, 256, 0, s>>>(T, ranges, beg, end);
+    cudaError_t e = cub::DeviceSegmentedRadixSort::SortKeys(p, cub_bytes, unsorted, sorted_entries, R, T, beg, end, 0,
+                                                            64, s);
+    if (e != cudaSuccess) return e;
+    gather_sorted_kernel<<<T, 256, 0, s>>>(R, T, ranges, sorted_entries, rec, point_list, sorted_rec, keys_sorted);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// blend_fwd: one block per 16x16 tile, 8 warps, each warp owns an 8x4 pixel rectangle. Batches of 256 tile-ordered
+// records are staged by one TMA bulk copy per batch (double buffered, mbarrier completion). Each warp first tests
+// 32 Gaussians at a time (one per lane) against its rectangle with the conservative extent, then walks only the
+// survivors in list order, so the front-to-back recurrence and `n_contrib` are identical to the reference
+// (forward.cu:306-361) while most (pixel, Gaussian) pairs are never evaluated.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int BLEND_BATCH = 256;
+
+struct BlendSmem {
+    GaussRec rec[2][BLEND_BATCH];
+    uint64_t bar[2];
+};
+
+__global__ void __launch_bounds__(256) blend_fwd_kernel(const uint2* __restrict__ ranges,
+                                                        const GaussRec* __restrict__ sorted_rec, int W, int H,
+                                                        const float* __restrict__ bg, float* __restrict__ final_T,
+                                                        uint32_t* __restrict__ n_contrib,
+                                                        float* __restrict__ out_color, float* __restrict__ out_depth,
+                                                        float* __restrict__ out_alpha) {
+    __shared__ __align__(128) BlendSmem sm;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int n = (int)(range.y - range.x);
+    const int nb = (n + BLEND_BATCH - 1) / BLEND_BATCH;
+
+    const int wx0 = blockIdx.x * TILE_X + (warp & 1) * 8;
+    const int wy0 = blockIdx.y * TILE_Y + (warp >> 1) * 4;
+    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const float2 pixf = {(float)px, (float)py};
+    const float rx0 = (float)wx0, rx1 = (float)(wx0 + 7), ry0 = (float)wy0, ry1 = (float)(wy0 + 3);
+
+    if (tid == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int b = 0; b < min(nb, 2); b++) {
+            uint32_t cnt = (uint32_t)min(BLEND_BATCH, n - b * BLEND_BATCH);
+            mbar_expect_tx(&sm.bar[b], cnt * (uint32_t)sizeof(GaussRec));
+            tma_load_1d(&sm.rec[b][0], sorted_rec + range.x + (size_t)b * BLEND_BATCH, cnt * (uint32_t)sizeof(GaussRec),
+                        &sm.bar[b]);
+        }
+    }
+
+    bool done = !inside;
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C[3] = {0.f, 0.f, 0.f};
+    float Dz = 0.f;
+
+    for (int b = 0; b < nb; b++) {
+        const int st = b & 1;
+        const int cnt = min(BLEND_BATCH, n - b * BLEND_BATCH);
+        mbar_wait(&sm.bar[st], (uint32_t)((b >> 1) & 1));
+        const GaussRec* rec = sm.rec[st];
+        if (__ballot_sync(0xffffffffu, !done) != 0) {
+            for (int c0 = 0; c0 < cnt; c0 += 32) {
+                const int g = c0 + lane;
+                bool ov = false;
+                if (g < cnt) {
+                    float4 A = rec[g].A;
+                    ov = (A.z >= 0.f) && (A.x + A.z >= rx0) && (A.x - A.z <= rx1) && (A.y + A.w >= ry0) &&
+                         (A.y - A.w <= ry1);
+                }
+                unsigned m = __ballot_sync(0xffffffffu, ov);
+                while (m) {
+                    const int j = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int gi = c0 + j;
+                    if (!done) {
+                        // forward.cu:330-361
+                        const float4 A = rec[gi].A;
+                        const float4 con_o = rec[gi].B;
+                        float2 d = {A.x - pixf.x, A.y - pixf.y};
+                        float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                        if (!(power > 0.0f)) {
+                            float alpha = min(0.99f, con_o.w * expf(power));
+                            if (alpha >= 1.0f / 255.0f) {
+                                float test_T = T * (1 - alpha);
+                                if (test_T < 0.0001f) {
+                                    done = true;
+                                } else {
+                                    const float4 col = rec[gi].C;
+                                    C[0] += col.x * alpha * T;
+                                    C[1] += col.y * alpha * T;
+                                    C[2] += col.z * alpha * T;
+                                    Dz += col.w * alpha * T;
+                                    T = test_T;
+                                    last_contributor = (uint32_t)(b * BLEND_BATCH + gi + 1);
+                                }
+                            }
+                        }
+                    }
+                }
+                if (__ballot_sync(0xffffffffu, !done) == 0) break;
+            }
+        }
+        // All threads are finished with this stage; refill it with batch b+2 (or stop if every pixel is done,
+        // forward.cu:309-311).
+        int num_done = __syncthreads_count(done);
+        if (num_done == TILE_PIX) {
+            // a bulk copy for batch b+1 may still be in flight: it must land before this block's shared memory is freed
+            if (b + 1 < nb) mbar_wait(&sm.bar[st ^ 1], (uint32_t)(((b + 1) >> 1) & 1));
+            break;
+        }
+        if (tid == 0 && b + 2 < nb) {
+            uint32_t cnt2 = (uint32_t)min(BLEND_BATCH, n - (b + 2) * BLEND_BATCH);
+            mbar_expect_tx(&sm.bar[st], cnt2 * (uint32_t)sizeof(GaussRec));
+            tma_load_1d(&sm.rec[st][0], sorted_rec + range.x + (size_t)(b + 2) * BLEND_BATCH,
+                        cnt2 * (uint32_t)sizeof(GaussRec), &sm.bar[st]);
+        }
+    }
+
+    if (inside) {
+        const int pix_id = W * py + px;
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) out_color[ch * H * W + pix_id] = C[ch] + T * bg[ch];
+        if (out_depth) out_depth[pix_id] = Dz;
+        if (out_alpha) out_alpha[pix_id] = 1.0f - T;
+    }
+}
+
+cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const GaussRec* sorted_rec, int W, int H,
+                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
+                             float* out_alpha, cudaStream_t s) {
+    dim3 grid(gx, gy, 1);
+    blend_fwd_kernel<<<grid, 256, 0, s>>>(ranges, sorted_rec, W, H, bg, final_T, n_contrib, out_color, out_depth,
+                                          out_alpha);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// mark_visible (checkFrustum, rasterizer_impl.cu:54-66): present = view-space z > near.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view,
+                                    const float* __restrict__ proj, uint8_t* __restrict__ present) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    float3 p = {means[3 * idx], means[3 * idx + 1], means[3 * idx + 2]};
+    float3 p_view = xform_point_4x3(p, view);
+    present[idx] = (p_view.z <= NEAR_Z) ? 0 : 1;
+}
+
+cudaError_t launch_mark_visible(int P, const float* means, const float* view, const float* proj, uint8_t* present,
+                                cudaStream_t s) {
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means, view, proj, present);
+    return cudaGetLastError();
+}
+
+}  // namespace das3r

@@ -1,0 +1,85 @@
+// Launch-side declarations shared between forward.cu, backward.cu, knn.cu and api.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+namespace das3r {
+
+constexpr int TILE_X = 16;  // reference config.h:16-17 (BLOCK_X, BLOCK_Y)
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// Per-Gaussian record, 48 bytes, written by the forward preprocess and gathered (in tile/depth order) by the tile
+// sort so that the blend kernels can stage contiguous batches with one TMA bulk copy.
+//   A = {x, y, hx, hy}      pixel-space mean and a conservative half-extent of the alpha >= 1/255 region
+//   B = {conic a, b, c, opacity}   (reference: conic_opacity, forward.cu:253)
+//   C = {r, g, b, depth}
+struct __align__(16) GaussRec {
+    float4 A, B, C;
+};
+static_assert(sizeof(GaussRec) == 48, "GaussRec must be 48 bytes");
+
+// Screen-space gradient accumulator, 48 bytes per Gaussian (replaces the reference's four zero-filled tensors
+// dL_dmean2D/dL_dconic/dL_dopacity/dL_dcolors, rasterize_points.cu:151-155).
+//   f[0..1] dL_dmean2D.xy   f[2..4] dL_dconic (x, y, w)   f[5] dL_dopacity   f[6..8] dL_dcolor   f[9..11] pad
+constexpr int ACC_STRIDE = 12;
+
+struct PreFwdArgs {
+    int P, D, M, W, H;
+    unsigned gx, gy;
+    float tan_fovx, tan_fovy, focal_x, focal_y, scale_mod;
+    int prefiltered;
+    const float *means, *shs, *colors_precomp, *opac, *scales, *rots, *cov3D_precomp, *view, *proj, *campos;
+    int* radii;
+    GaussRec* rec;
+    uint32_t* tiles_touched;
+    uint8_t* clamped;
+    uint32_t* tile_counts;
+    int smem_hist;  // 1: per-block shared-memory histogram of tile counts, 0: direct global atomics
+};
+
+struct PreBwdArgs {
+    int P, D, M, W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y, scale_mod;
+    const float *means, *shs, *scales, *rots, *cov3D_precomp, *view, *proj, *campos;
+    const int* radii;
+    const uint8_t* clamped;
+    const float* acc;  // [P][ACC_STRIDE]
+    float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drots;
+};
+
+// forward.cu
+cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
+cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,
+                             cudaStream_t s);
+cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,
+                           const uint32_t* tiles_touched, uint32_t* cursors, uint64_t* unsorted, cudaStream_t s);
+// Sorts every tile whose entry count is <= tile_sort_capacity(); returns cudaErrorInvalidValue if max_count is larger
+// (the caller then uses the segmented fallback).
+int tile_sort_capacity();
+cudaError_t launch_tile_sort(int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
+                             const GaussRec* rec, uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted,
+                             cudaStream_t s);
+// Fallback for tiles beyond the shared-memory capacity: library segmented radix sort + gather.
+size_t tile_sort_fallback_bytes(int R, int T);
+cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
+                                      uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted, void* temp,
+                                      size_t temp_bytes, cudaStream_t s);
+cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const GaussRec* sorted_rec, int W, int H,
+                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
+                             float* out_alpha, cudaStream_t s);
+cudaError_t launch_mark_visible(int P, const float* means, const float* view, const float* proj, uint8_t* present,
+                                cudaStream_t s);
+
+// backward.cu
+cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* point_list,
+                             const GaussRec* sorted_rec, int W, int H, const float* bg, const float* final_T,
+                             const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t s);
+cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
+
+// knn.cu
+size_t knn_scratch_bytes(int P);
+cudaError_t knn_dist2(int P, const float* points, float* out, void* scratch, size_t scratch_bytes, cudaStream_t s);
+
+}  // namespace das3r

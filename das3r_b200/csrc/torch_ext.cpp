@@ -1,0 +1,284 @@
+// Thin PyTorch binding over the C ABI (include/das3r_raster.h). The exported functions have exactly the signatures of
+// the reference's pybind module (submodules/diff-gaussian-rasterization/ext.cpp:15-18, rasterize_points.h:18-67) and
+// of simple_knn._C.distCUDA2 (submodules/simple-knn/ext.cpp:15-16, spatial.h:14), so the reference's Python package
+// code paths work unchanged on top of them. torch is used for memory and streams only.
+#include <torch/extension.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <tuple>
+#include <string>
+#include "../../include/das3r_raster.h"
+
+namespace {
+
+const float* fptr(const torch::Tensor& t) {
+    // empty tensor (the reference passes torch.Tensor([]) for absent inputs) -> NULL
+    return t.defined() && t.numel() > 0 ? t.data_ptr<float>() : nullptr;
+}
+
+torch::Tensor prep(const torch::Tensor& t, const char* name, const torch::Device& dev) {
+    if (!t.defined() || t.numel() == 0) return t;
+    TORCH_CHECK(t.scalar_type() == torch::kFloat32, name, " must be float32");
+    TORCH_CHECK(t.device() == dev, name, " must be on ", dev);
+    return t.contiguous();
+}
+
+struct BlobAlloc {
+    torch::Tensor t;
+    torch::TensorOptions opts;
+    static char* fn(size_t bytes, void* ctx) {
+        auto* self = static_cast<BlobAlloc*>(ctx);
+        self->t = torch::empty({(long long)bytes}, self->opts);
+        return reinterpret_cast<char*>(self->t.data_ptr());
+    }
+};
+
+void check(int rc, const char* what) {
+    if (rc < 0) throw std::runtime_error(std::string(what) + ": " + das3r_last_error());
+}
+
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+rasterize_impl(const torch::Tensor& background, const torch::Tensor& means3D_, const torch::Tensor& colors_,
+               const torch::Tensor& opacity_, const torch::Tensor& scales_, const torch::Tensor& rotations_,
+               const float scale_modifier, const torch::Tensor& cov3D_precomp_, const torch::Tensor& viewmatrix_,
+               const torch::Tensor& projmatrix_, const float tan_fovx, const float tan_fovy, const int image_height,
+               const int image_width, const torch::Tensor& sh_, const int degree, const torch::Tensor& campos_,
+               const bool prefiltered, const bool debug, const bool extras) {
+    if (means3D_.ndimension() != 2 || means3D_.size(1) != 3) {
+        AT_ERROR("means3D must have dimensions (num_points, 3)");  // rasterize_points.cu:57-59
+    }
+    TORCH_CHECK(means3D_.is_cuda(), "means3D must be a CUDA tensor: this rasterizer has no CPU path");
+    const auto dev = means3D_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    const int P = means3D_.size(0), H = image_height, W = image_width;
+
+    auto means3D = prep(means3D_, "means3D", dev);
+    auto colors = prep(colors_, "colors_precomp", dev);
+    auto opacity = prep(opacity_, "opacities", dev);
+    auto scales = prep(scales_, "scales", dev);
+    auto rotations = prep(rotations_, "rotations", dev);
+    auto cov3D = prep(cov3D_precomp_, "cov3D_precomp", dev);
+    auto view = prep(viewmatrix_, "viewmatrix", dev);
+    auto proj = prep(projmatrix_, "projmatrix", dev);
+    auto sh = prep(sh_, "shs", dev);
+    auto campos = prep(campos_, "campos", dev);
+    auto bg = prep(background, "bg", dev);
+
+    auto float_opts = means3D.options().dtype(torch::kFloat32);
+    torch::Tensor out_color = torch::empty({3, H, W}, float_opts);
+    torch::Tensor radii = torch::empty({P}, means3D.options().dtype(torch::kInt32));
+    torch::Tensor depth, alpha;
+    if (extras) {
+        depth = torch::empty({H, W}, float_opts);
+        alpha = torch::empty({H, W}, float_opts);
+    }
+    auto byte_opts = torch::TensorOptions().dtype(torch::kByte).device(dev);
+    BlobAlloc geom{torch::empty({0}, byte_opts), byte_opts}, binning{torch::empty({0}, byte_opts), byte_opts},
+        img{torch::empty({0}, byte_opts), byte_opts};
+
+    das3r_raster_params p;
+    memset(&p, 0, sizeof(p));
+    p.P = P;
+    p.D = degree;
+    p.M = (sh.defined() && sh.numel() > 0) ? (int)sh.size(1) : 0;
+    p.width = W;
+    p.height = H;
+    p.tan_fovx = tan_fovx;
+    p.tan_fovy = tan_fovy;
+    p.scale_modifier = scale_modifier;
+    p.prefiltered = prefiltered;
+    p.debug = debug;
+    p.background = fptr(bg);
+    p.viewmatrix = fptr(view);
+    p.projmatrix = fptr(proj);
+    p.campos = fptr(campos);
+    das3r_raster_inputs in;
+    in.means3D = fptr(means3D);
+    in.shs = fptr(sh);
+    in.colors_precomp = fptr(colors);
+    in.opacities = fptr(opacity);
+    in.scales = fptr(scales);
+    in.rotations = fptr(rotations);
+    in.cov3D_precomp = fptr(cov3D);
+    das3r_raster_outputs out;
+    out.out_color = out_color.data_ptr<float>();
+    out.radii = P > 0 ? radii.data_ptr<int>() : nullptr;
+    out.out_depth = extras ? depth.data_ptr<float>() : nullptr;
+    out.out_alpha = extras ? alpha.data_ptr<float>() : nullptr;
+    das3r_raster_state st;
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    int rendered = das3r_raster_forward(&p, &in, &out, BlobAlloc::fn, &geom, BlobAlloc::fn, &binning, BlobAlloc::fn,
+                                        &img, &st, stream);
+    check(rendered, "rasterize_gaussians");
+    return std::make_tuple(rendered, out_color, radii, geom.t, binning.t, img.t, depth, alpha);
+}
+
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor> RasterizeGaussiansCUDA(
+    const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+    const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+    const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+    const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+    const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+    const bool prefiltered, const bool debug) {
+    auto r = rasterize_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                            viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                            prefiltered, debug, false);
+    return std::make_tuple(std::get<0>(r), std::get<1>(r), std::get<2>(r), std::get<3>(r), std::get<4>(r),
+                           std::get<5>(r));
+}
+
+// Additive surface: same call, also returns depth [H,W] = sum z*alpha*T and alpha [H,W] = 1-final_T.
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansExCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                         const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                         const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                         const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
+                         const float tan_fovy, const int image_height, const int image_width, const torch::Tensor& sh,
+                         const int degree, const torch::Tensor& campos, const bool prefiltered, const bool debug) {
+    return rasterize_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                          viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                          prefiltered, debug, true);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+           torch::Tensor>
+RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D_,
+                               const torch::Tensor& radii_, const torch::Tensor& colors_, const torch::Tensor& scales_,
+                               const torch::Tensor& rotations_, const float scale_modifier,
+                               const torch::Tensor& cov3D_precomp_, const torch::Tensor& viewmatrix_,
+                               const torch::Tensor& projmatrix_, const float tan_fovx, const float tan_fovy,
+                               const torch::Tensor& dL_dout_color_, const torch::Tensor& sh_, const int degree,
+                               const torch::Tensor& campos_, const torch::Tensor& geomBuffer, const int R,
+                               const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug) {
+    TORCH_CHECK(means3D_.is_cuda(), "means3D must be a CUDA tensor: this rasterizer has no CPU path");
+    const auto dev = means3D_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    const int P = means3D_.size(0);
+    const int H = dL_dout_color_.size(1);  // rasterize_points.cu:142-143
+    const int W = dL_dout_color_.size(2);
+
+    auto means3D = prep(means3D_, "means3D", dev);
+    auto colors = prep(colors_, "colors_precomp", dev);
+    auto scales = prep(scales_, "scales", dev);
+    auto rotations = prep(rotations_, "rotations", dev);
+    auto cov3D = prep(cov3D_precomp_, "cov3D_precomp", dev);
+    auto view = prep(viewmatrix_, "viewmatrix", dev);
+    auto proj = prep(projmatrix_, "projmatrix", dev);
+    auto sh = prep(sh_, "shs", dev);
+    auto campos = prep(campos_, "campos", dev);
+    auto bg = prep(background, "bg", dev);
+    auto dL_dout = prep(dL_dout_color_, "dL_dout_color", dev);
+    auto radii = radii_.contiguous();
+    TORCH_CHECK(radii.scalar_type() == torch::kInt32, "radii must be int32");
+
+    int M = 0;
+    if (sh.defined() && sh.numel() > 0) M = sh.size(1);
+
+    auto o = means3D.options();
+    // torch::empty, not zeros: the backward kernels write every element (incl. the zeros of invisible Gaussians).
+    torch::Tensor dL_dmeans3D = torch::empty({P, 3}, o);
+    torch::Tensor dL_dmeans2D = torch::empty({P, 3}, o);
+    torch::Tensor dL_dcolors = torch::empty({P, 3}, o);
+    torch::Tensor dL_dopacity = torch::empty({P, 1}, o);
+    torch::Tensor dL_dcov3D = torch::empty({P, 6}, o);
+    torch::Tensor dL_dsh = torch::empty({P, M, 3}, o);
+    torch::Tensor dL_dscales = torch::empty({P, 3}, o);
+    torch::Tensor dL_drotations = torch::empty({P, 4}, o);
+
+    if (P != 0) {
+        torch::Tensor scratch = torch::empty({(long long)das3r_raster_backward_scratch_bytes(P)},
+                                             torch::TensorOptions().dtype(torch::kByte).device(dev));
+        das3r_raster_params p;
+        memset(&p, 0, sizeof(p));
+        p.P = P;
+        p.D = degree;
+        p.M = M;
+        p.width = W;
+        p.height = H;
+        p.tan_fovx = tan_fovx;
+        p.tan_fovy = tan_fovy;
+        p.scale_modifier = scale_modifier;
+        p.debug = debug;
+        p.background = fptr(bg);
+        p.viewmatrix = fptr(view);
+        p.projmatrix = fptr(proj);
+        p.campos = fptr(campos);
+        das3r_raster_inputs in;
+        memset(&in, 0, sizeof(in));
+        in.means3D = fptr(means3D);
+        in.shs = fptr(sh);
+        in.colors_precomp = fptr(colors);
+        in.scales = fptr(scales);
+        in.rotations = fptr(rotations);
+        in.cov3D_precomp = fptr(cov3D);
+        das3r_raster_state st;
+        st.geom = reinterpret_cast<char*>(geomBuffer.data_ptr());
+        st.geom_bytes = geomBuffer.numel();
+        st.binning = binningBuffer.numel() > 0 ? reinterpret_cast<char*>(binningBuffer.data_ptr()) : nullptr;
+        st.binning_bytes = binningBuffer.numel();
+        st.image = reinterpret_cast<char*>(imageBuffer.data_ptr());
+        st.image_bytes = imageBuffer.numel();
+        st.num_rendered = R;
+        das3r_raster_grads g;
+        g.dL_dmeans2D = dL_dmeans2D.data_ptr<float>();
+        g.dL_dcolors = dL_dcolors.data_ptr<float>();
+        g.dL_dopacity = dL_dopacity.data_ptr<float>();
+        g.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();
+        g.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        g.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
+        g.dL_dscales = dL_dscales.data_ptr<float>();
+        g.dL_drotations = dL_drotations.data_ptr<float>();
+        g.scratch = reinterpret_cast<float*>(scratch.data_ptr());
+        cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(das3r_raster_backward(&p, &in, radii.data_ptr<int>(), &st, dL_dout.data_ptr<float>(), &g, stream),
+              "rasterize_gaussians_backward");
+    }
+    return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+                           dL_drotations);
+}
+
+torch::Tensor markVisible(torch::Tensor& means3D_, torch::Tensor& viewmatrix_, torch::Tensor& projmatrix_) {
+    TORCH_CHECK(means3D_.is_cuda(), "means3D must be a CUDA tensor: this rasterizer has no CPU path");
+    const auto dev = means3D_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    const int P = means3D_.size(0);
+    torch::Tensor present = torch::full({P}, false, means3D_.options().dtype(at::kBool));
+    if (P != 0) {
+        auto means3D = prep(means3D_, "means3D", dev);
+        auto view = prep(viewmatrix_, "viewmatrix", dev);
+        auto proj = prep(projmatrix_, "projmatrix", dev);
+        cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(das3r_mark_visible(P, fptr(means3D), fptr(view), fptr(proj),
+                                 reinterpret_cast<uint8_t*>(present.data_ptr<bool>()), stream),
+              "mark_visible");
+    }
+    return present;
+}
+
+torch::Tensor distCUDA2(const torch::Tensor& points_) {
+    TORCH_CHECK(points_.is_cuda(), "points must be a CUDA tensor: distCUDA2 has no CPU path");
+    const auto dev = points_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    const int P = points_.size(0);
+    auto points = prep(points_, "points", dev);
+    torch::Tensor means = torch::full({P}, 0.0, points_.options().dtype(torch::kFloat32));
+    if (P != 0) {
+        size_t bytes = das3r_knn_scratch_bytes(P);
+        torch::Tensor scratch = torch::empty({(long long)bytes}, torch::TensorOptions().dtype(torch::kByte).device(dev));
+        cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(das3r_knn_dist2(P, fptr(points), means.data_ptr<float>(), scratch.data_ptr(), bytes, stream),
+              "distCUDA2");
+    }
+    return means;
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
+    m.def("rasterize_gaussians_ex", &RasterizeGaussiansExCUDA);
+    m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
+    m.def("mark_visible", &markVisible);
+    m.def("distCUDA2", &distCUDA2);
+    m.def("abi_version", []() { return das3r_abi_version(); });
+}

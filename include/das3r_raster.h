@@ -1,0 +1,170 @@
+/*
+ * das3r_raster.h — C ABI of the B200-native (sm_100a) differentiable Gaussian-splat rasterizer and the 3-NN
+ * initialiser that replace DAS3R's submodules/diff-gaussian-rasterization and submodules/simple-knn.
+ *
+ * Everything here is plain C: POD structs, raw DEVICE pointers, sizes, a CUDA stream passed as void*.
+ * No torch types. The torch extension (das3r_b200/csrc/torch_ext.cpp) and the ctypes tests are the callers.
+ *
+ * Conventions (mirroring the reference library API, submodules/diff-gaussian-rasterization/
+ * cuda_rasterizer/rasterizer.h:20-85):
+ *   - a NULL input pointer means "this optional input is absent" (the reference passes empty tensors whose
+ *     data pointer is null: diff_gaussian_rasterization/__init__.py:197-207 <-> forward.cu:205,241);
+ *   - the caller owns all memory. The three growable state blobs are requested through allocator callbacks
+ *     (rasterizer.h:31-33 uses std::function<char*(size_t)>), and handed back verbatim to the backward;
+ *   - every function returns 0 (or a non-negative count) on success and a negative DAS3R_E* code on failure;
+ *     das3r_last_error() then returns a human-readable message for the calling thread;
+ *   - all work is enqueued on `stream` (cudaStream_t as void*; NULL = legacy default stream).
+ */
+#ifndef DAS3R_RASTER_H_
+#define DAS3R_RASTER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DAS3R_ABI_VERSION 1
+
+#define DAS3R_OK 0
+#define DAS3R_EINVAL (-1)   /* bad argument (shape, null, size) */
+#define DAS3R_ECUDA (-2)    /* a CUDA runtime call or kernel failed */
+#define DAS3R_ENOMEM (-3)   /* an allocator callback returned NULL */
+#define DAS3R_ELIMIT (-4)   /* size beyond a documented limit */
+
+/* Allocator callback: return a DEVICE pointer to at least `bytes` bytes (256-byte aligned), or NULL.
+ * Replaces std::function<char*(size_t)> of rasterizer.h:31-33 / resizeFunctional, rasterize_points.cu:27-33. */
+typedef char* (*das3r_alloc_fn)(size_t bytes, void* ctx);
+
+/* Per-call camera / configuration bundle. Field meaning follows GaussianRasterizationSettings
+ * (diff_gaussian_rasterization/__init__.py:157-169) and the argument list of Rasterizer::forward
+ * (rasterizer_impl.cu:198-221). Matrices are 16 floats in the reference's flat layout (column-major as the
+ * kernels index them: auxiliary.h:58-77). */
+typedef struct das3r_raster_params {
+    int32_t P;              /* number of Gaussians */
+    int32_t D;              /* active SH degree 0..3 */
+    int32_t M;              /* SH coefficients per channel in `shs` rows ((max_degree+1)^2; 0 if shs absent) */
+    int32_t width, height;  /* image size in pixels */
+    float tan_fovx, tan_fovy;
+    float scale_modifier;
+    int32_t prefiltered;    /* nonzero: a culled point is a device-side trap (auxiliary.h:156-160) */
+    int32_t debug;          /* nonzero: synchronise and check after every stage (CHECK_CUDA, auxiliary.h:166-173) */
+    const float* background;  /* device [3] */
+    const float* viewmatrix;  /* device [16] */
+    const float* projmatrix;  /* device [16] */
+    const float* campos;      /* device [3] */
+} das3r_raster_params;
+
+/* Per-Gaussian inputs (device, contiguous fp32). Exactly one of shs / colors_precomp and exactly one of
+ * (scales, rotations) / cov3D_precomp must be non-NULL (the Python surface enforces it). */
+typedef struct das3r_raster_inputs {
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3] or NULL */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL */
+    const float* rotations;      /* [P,4] or NULL (used un-normalised, forward.cu:127) */
+    const float* cov3D_precomp;  /* [P,6] or NULL */
+} das3r_raster_inputs;
+
+/* Forward outputs (device, caller-allocated). out_color and radii need not be pre-zeroed. */
+typedef struct das3r_raster_outputs {
+    float* out_color;   /* [3,H,W] */
+    int32_t* radii;     /* [P] */
+    float* out_depth;   /* [H,W] or NULL: sum_i z_i alpha_i T_i (additive surface) */
+    float* out_alpha;   /* [H,W] or NULL: 1 - final_T */
+} das3r_raster_outputs;
+
+/* The three state blobs produced by the forward and consumed by the backward. Their layout is private to this
+ * library (see das3r_raster_state_layout for the test/debug view). */
+typedef struct das3r_raster_state {
+    char* geom;     size_t geom_bytes;
+    char* binning;  size_t binning_bytes;
+    char* image;    size_t image_bytes;
+    int32_t num_rendered;
+} das3r_raster_state;
+
+/* Gradient outputs (device, caller-allocated, need NOT be pre-zeroed: every element is written).
+ * Shapes follow RasterizeGaussiansBackwardCUDA, rasterize_points.cu:151-159. */
+typedef struct das3r_raster_grads {
+    float* dL_dmeans2D;    /* [P,3] (z is always 0: backward.cu:545-546 never writes it) */
+    float* dL_dcolors;     /* [P,3] */
+    float* dL_dopacity;    /* [P] */
+    float* dL_dmeans3D;    /* [P,3] */
+    float* dL_dcov3D;      /* [P,6] */
+    float* dL_dsh;         /* [P,M,3] or NULL when M == 0 */
+    float* dL_dscales;     /* [P,3] */
+    float* dL_drotations;  /* [P,4] */
+    float* scratch;        /* device scratch, das3r_raster_backward_scratch_bytes(P) bytes; contents undefined */
+} das3r_raster_grads;
+
+/* Library / ABI version (DAS3R_ABI_VERSION). No reference counterpart. */
+int das3r_abi_version(void);
+
+/* Message for the last failure on the calling thread ("" if none). Replaces the std::runtime_error thrown by
+ * CHECK_CUDA (auxiliary.h:166-173) and AT_ERROR (rasterize_points.cu:58). */
+const char* das3r_last_error(void);
+
+/* Forward rasterization. Replaces CudaRasterizer::Rasterizer::forward (rasterizer.h:31-53,
+ * rasterizer_impl.cu:198-336): preprocess -> tile binning -> per-tile depth sort -> tile ranges -> blend.
+ * Returns num_rendered (>= 0) like the reference, or a negative error code. `state` receives the blob pointers
+ * obtained from the allocators. Blocks the host once (4-byte read-back of num_rendered, as rasterizer_impl.cu:281). */
+int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_inputs* in,
+                         const das3r_raster_outputs* out,
+                         das3r_alloc_fn geom_alloc, void* geom_ctx,
+                         das3r_alloc_fn binning_alloc, void* binning_ctx,
+                         das3r_alloc_fn image_alloc, void* image_ctx,
+                         das3r_raster_state* state, void* stream);
+
+/* Backward. Replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:55-84, rasterizer_impl.cu:340-434):
+ * backward blend -> cov2D/projection/SH/cov3D gradients. `radii` is the forward's output. `dL_dpix` is [3,H,W]. */
+int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in,
+                          const int32_t* radii, const das3r_raster_state* state,
+                          const float* dL_dpix, const das3r_raster_grads* grads, void* stream);
+
+/* Bytes of device scratch the backward needs for P Gaussians (screen-space gradient accumulators; they replace
+ * the reference's separate zero-filled dL_dconic/dL_dmean2D/dL_dcolor/dL_dopacity tensors, rasterize_points.cu:151-155). */
+size_t das3r_raster_backward_scratch_bytes(int32_t P);
+
+/* Frustum test. Replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:24-29, rasterizer_impl.cu:141-153,
+ * checkFrustum :54-66) with DAS3R's 0.001 near plane. present: device uint8/bool [P]. */
+int das3r_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present, void* stream);
+
+/* Mean squared distance to the 3 nearest other points. Replaces SimpleKNN::knn (simple-knn/simple_knn.h,
+ * simple_knn.cu:186-222) behind distCUDA2 (spatial.cu:15-25). points: device [P,3]; mean_dist2: device [P].
+ * Scratch comes from the caller (the reference cudaMallocs internally, simple_knn.cu:189-217):
+ * call das3r_knn_scratch_bytes(P) first. Blocks the host once (bounding-box read-back, as simple_knn.cu:197-201). */
+size_t das3r_knn_scratch_bytes(int32_t P);
+int das3r_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes,
+                    void* stream);
+
+/* Test/debug view of the private state layout: byte offsets of the arrays the parity tests compare with the
+ * reference's GeometryState/BinningState/ImageState (rasterizer_impl.cu:155-194). No reference counterpart. */
+typedef struct das3r_raster_state_layout {
+    /* geom blob (P-sized) */
+    size_t g_recA, g_recB, g_recC;   /* float4[P]: {x,y,hx,hy} {conic a,b,c,opacity} {r,g,b,depth} */
+    size_t g_tiles_touched;          /* uint32[P] */
+    size_t g_clamped;                /* uint8[P], bit c = channel c clamped */
+    size_t geom_bytes;
+    /* image blob */
+    size_t i_final_T, i_n_contrib;   /* float[N], uint32[N] */
+    size_t i_ranges;                 /* uint2[T] */
+    size_t i_tile_counts, i_cursors; /* uint32[T] each */
+    size_t i_totals;                 /* uint32[4]: num_rendered, max tile count, 0, 0 */
+    size_t image_bytes;
+    /* binning blob (R-sized) */
+    size_t b_unsorted;               /* uint64[R]: depth_bits<<32 | gaussian index, tile-bucketed */
+    size_t b_point_list;             /* uint32[R] sorted */
+    size_t b_keys_sorted;            /* uint64[R] tile<<32|depth_bits, written only when params.debug != 0 */
+    size_t b_sA, b_sB, b_sC;         /* float4[R] tile-ordered records */
+    size_t binning_bytes;
+} das3r_raster_state_layout;
+int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
+                                    das3r_raster_state_layout* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAS3R_RASTER_H_ */
