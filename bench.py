@@ -1,0 +1,444 @@
+#!/usr/bin/env python
+"""bench.py — the headline benchmark of the rasterizer hot path (BASELINE.json metric:
+"raster fwd+bwd views/s @1M Gaussians 512x288").
+
+    python bench.py --gpus N --steps K --warmup W [--impl ours|reference|oracle-cpu]
+
+For N > 1 the driver launches it under torchrun (one rank per GPU, NCCL); RANK/LOCAL_RANK/WORLD_SIZE come from the env.
+
+A STEP is one pass of the hot path over one batch: every rank rasterizes `--views-per-step` disjoint camera views of
+the (replicated) synthetic scene, forward + backward with a dense dL/d(colour), summing the Gaussian-parameter
+gradients of its views in place into one flat fp32 bucket; for N > 1 the bucket is then summed across ranks with ONE
+NCCL all-reduce per step (double-buffered, overlapping the next step). `value` = views of all ranks / device time, with
+all inputs resident in HBM; `e2e` = the same metric through the public drop-in API (GaussianRasterizer + autograd) with
+the per-view host inputs (camera bundle, dL/d(colour)) copied from pinned memory and the rendered image + loss read
+back inside the timed region.
+
+`--impl reference` times the reference CUDA rasterizer (oracle/_ref, built from /root/reference by
+oracle/build_ref.sh) through its own pybind API in the same step structure (its fresh zero-filled gradients are added
+to the bucket with torch ops, the bucket is all-reduced the same way). `--impl oracle-cpu` times the C port of the
+reference algorithm on the host cores (rank 0 only). Only this file's cpu_baseline / reference legs touch oracle/.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+METRIC = "raster fwd+bwd views/s @1M Gaussians 512x288"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "oracle-cpu"])
+    ap.add_argument("--views-per-step", type=int, default=8)
+    ap.add_argument("--P", type=int, default=1_000_000)
+    ap.add_argument("--V", type=int, default=50)
+    ap.add_argument("--W", type=int, default=512)
+    ap.add_argument("--H", type=int, default=288)
+    ap.add_argument("--sh-degree", type=int, default=3)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-views", type=int, default=4, help="views timed for the CPU baseline sample")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def hbm_peak() -> tuple[float, str]:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def stage_bytes(P, R, N, T, s):
+    """Algorithmic bytes per launch of each stage (SURVEY.md §8d / DESIGN.md §4): compulsory traffic, each array counted
+    once per pass that semantically needs it. s = 12*(D+1)^2 bytes of active SH per Gaussian."""
+    return {
+        "preprocess_fwd": P * (119 + s),
+        "tile_scan": 8 * T,
+        "scatter": 20 * P + 12 * R,
+        "tile_sort": 24 * R,
+        "blend_fwd": 48 * R + 20 * N,
+        "blend_bwd": 40 * R + 20 * N,
+        "preprocess_bwd": P * (199 + 2 * s),
+    }
+
+
+def view_bytes(P, R, N, T, s):
+    return P * (318 + 3 * s) + 124 * R + 40 * N + 8 * T
+
+
+def main():
+    args = parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    vps = args.views_per_step
+
+    from das3r_b200.synth import synth_scene, view_inputs, grad_seed
+    from das3r_b200 import sharding
+
+    if args.impl == "oracle-cpu":
+        if rank != 0:
+            return
+        run_cpu_arm(args)
+        return
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    if args.impl == "ours":
+        from das3r_b200 import load_native
+        C = load_native()
+    else:
+        import oracle
+        if not oracle.reference_available():
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (run oracle/build_ref.sh "
+                                  "where /root/reference exists)"}))
+            return
+        C, _ = oracle.load_reference()
+
+    # ---- the workload: one replicated scene, per-rank view pools ------------------------------------------------
+    sc = synth_scene(P=args.P, V=args.V, W=args.W, H=args.H, seed=args.seed, sh_degree=args.sh_degree)
+    P, W, H, D = args.P, args.W, args.H, args.sh_degree
+    N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    perm = torch.randperm(sc.V, generator=torch.Generator().manual_seed(1234)).tolist()
+    my_views = sharding.shard_views(perm, 0, rank, world, vps)
+    empty = torch.Tensor([])
+    shared = None
+    pool = []
+    for v in my_views:
+        vi = view_inputs(sc, v)
+        if shared is None:
+            shared = dict(shs=vi["shs"].to(dev), opac=vi["opacities"].to(dev), scales=vi["scales"].to(dev),
+                          bg=vi["bg"].to(dev), view=vi["viewmatrix"].to(dev).contiguous(),
+                          proj=vi["projmatrix"].to(dev).contiguous(), campos=vi["campos"].to(dev).contiguous(),
+                          tanx=vi["tanfovx"], tany=vi["tanfovy"])
+        pool.append(dict(means=vi["means3D"].contiguous().to(dev), rots=vi["rotations"].contiguous().to(dev)))
+    dL = grad_seed(sc).to(dev)
+    S = shared
+
+    shapes = sharding.gaussian_grad_shapes(P, 16)
+    buckets = [sharding.GradBucket(shapes, dev) for _ in range(2 if world > 1 else 1)]
+    handles = [None, None]
+    last_R = [0]
+
+    def fwd(pv):
+        return C.rasterize_gaussians(S["bg"], pv["means"], empty, S["opac"], S["scales"], pv["rots"], 1.0, empty,
+                                     S["view"], S["proj"], S["tanx"], S["tany"], H, W, S["shs"], D, S["campos"], False,
+                                     False)
+
+    def step(i):
+        b = i % len(buckets)
+        bk = buckets[b]
+        if handles[b] is not None:
+            handles[b].wait()
+            handles[b] = None
+        bk.zero_()
+        g = bk.views()
+        for pv in pool:
+            R, color, radii, geom, binning, img = fwd(pv)
+            last_R[0] = R
+            bargs = (S["bg"], pv["means"], radii, empty, S["scales"], pv["rots"], 1.0, empty, S["view"], S["proj"],
+                     S["tanx"], S["tany"], dL, S["shs"], D, S["campos"], geom, R, binning, img, False)
+            if args.impl == "ours":
+                outs = [empty, empty, g["opacities"], g["means3D"], empty, g["shs"], g["scales"], g["rotations"]]
+                C.rasterize_gaussians_backward_into(*bargs, outs, True)
+            else:
+                (_m2d, _dc, d_op, d_m3, _dcov, d_sh, d_sc, d_rot) = C.rasterize_gaussians_backward(*bargs)
+                g["opacities"].add_(d_op)
+                g["means3D"].add_(d_m3)
+                g["shs"].add_(d_sh)
+                g["scales"].add_(d_sc)
+                g["rotations"].add_(d_rot)
+        if world > 1:
+            handles[b] = bk.all_reduce(async_op=True)
+
+    def drain():
+        for b in range(len(handles)):
+            if handles[b] is not None:
+                handles[b].wait()
+                handles[b] = None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up, then the timed region -------------------------------------------------------------------------
+    for i in range(args.warmup):
+        step(i)
+    drain()
+    barrier()
+    launches0 = C.launch_count() if args.impl == "ours" else 0
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        step(args.warmup + i)
+    drain()
+    ev1.record()
+    torch.cuda.synchronize()
+    elapsed_ms = ev0.elapsed_time(ev1)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = (C.launch_count() - launches0) if args.impl == "ours" else None
+    elapsed_ms = sharding.all_reduce_max(elapsed_ms, dev)
+    views_total = world * vps * args.steps
+    value = views_total / (elapsed_ms / 1e3)
+    R = int(last_R[0])
+    s_bytes = 12 * (D + 1) ** 2
+
+    out = {
+        "metric": METRIC, "value": round(value, 2), "unit": "views/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(elapsed_ms / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {
+            "workload": f"C2-shaped synthetic scene: {P} Gaussians from {args.V} pointmap views, {W}x{H}, SH degree {D}, "
+                        f"shs+scales/rotations inputs; step = {vps} views/rank (fwd+bwd, dense dL), gradients summed "
+                        f"in place into a {buckets[0].nbytes() // (1 << 20)} MiB fp32 bucket"
+                        + (", one NCCL all-reduce of the bucket per step (overlapped)" if world > 1 else ""),
+            "views_per_step_per_rank": vps, "P": P, "W": W, "H": H, "sh_degree": D, "num_rendered": R,
+            "l2_policy": "inputs larger than L2 (per step each rank streams ~%d MB of distinct inputs; L2 is 126 MB)" %
+                         ((P * (28 * vps + 208)) // 1_000_000),
+            "parallelism": f"views sharded over {world} rank(s), Gaussians replicated",
+        },
+    }
+    if args.impl != "ours":
+        out["impl"] = "reference"
+        out["cpu_baseline"] = {"value": out["value"], "unit": "views/s", "cores": 0, "kind": "reference",
+                               "sample": "reference CUDA rasterizer (oracle/_ref, sm_100 build of the vendored "
+                                         "diff-gaussian-rasterization with DAS3R's 0.001 near plane) on the GPU: the "
+                                         "reference has no CPU implementation of this path; the CPU port is timed by "
+                                         "`--impl oracle-cpu` and in the `ours` line's cpu_baseline"}
+        out["e2e"] = {"value": out["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+        out["clocks"] = clocks
+        if rank == 0:
+            print(json.dumps(out))
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-stage device times (CUDA events on the launching stream), profiled pass right after the timed region ---
+    C.prof_collect(True)
+    C.prof_enable(True)
+    prof_steps = max(2, min(args.steps, 10))
+    for i in range(prof_steps):
+        step(i)
+    drain()
+    torch.cuda.synchronize()
+    stages = {name: (ms / max(calls, 1)) for name, ms, calls in C.prof_collect(True) if calls > 0}
+    C.prof_enable(False)
+    peak, peak_src = hbm_peak()
+    sb = stage_bytes(P, R, N, T, s_bytes)
+    kern = {k: v for k, v in stages.items() if k in sb}
+    dom = max(kern, key=kern.get)
+    achieved = sb[dom] / (kern[dom] * 1e-3) / 1e9
+    vb = view_bytes(P, R, N, T, s_bytes)
+    per_view_ms = elapsed_ms / (vps * args.steps)
+    out["roofline"] = {
+        "bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+        "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": sb[dom], "avg_launch_ms": round(kern[dom], 5),
+        "timing": f"CUDA events around every stage on the launching stream, {prof_steps} steps right after the timed "
+                  "region",
+        "stage_ms": {k: round(v, 5) for k, v in stages.items()},
+        "stage_frac_of_hbm_peak": {k: round(sb[k] / (v * 1e-3) / 1e9 / peak, 4) for k, v in kern.items()},
+        "view": {"algorithmic_bytes": vb, "achieved_gbs": round(vb / (per_view_ms * 1e-3) / 1e9, 1),
+                 "frac": round(vb / (per_view_ms * 1e-3) / 1e9 / peak, 4),
+                 "roofline_views_per_s_per_gpu": round(peak * 1e9 / vb, 1)},
+    }
+    out["gpu_launches"] = int(launches)
+    out["clocks"] = clocks
+
+    # ---- e2e: public API (GaussianRasterizer + autograd), per-view host inputs from pinned memory -------------------
+    if not args.no_e2e:
+        out["e2e"] = run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views)
+    # ---- CPU baseline: the C port of the reference algorithm on the host cores (rank 0, N = 1 only) -----------------
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(args, sc)
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
+    """views/s through the drop-in Python surface. Per view, inside the timed region: H2D (pinned) of the camera bundle
+    (viewmatrix 16 + projmatrix 16 + campos 3 + bg 3 floats) and of dL/d(colour) [3,H,W]; forward; loss; autograd
+    backward (gradients accumulate in the leaves' .grad); D2H of the rendered image and the loss. The Gaussian
+    parameters are the resident model state (like weights). For N > 1 the leaf gradients are all-reduced once per
+    step."""
+    from das3r_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    from das3r_b200 import sharding
+
+    W, H, D, vps = args.W, args.H, args.sh_degree, args.views_per_step
+    cam_host = torch.cat([S["view"].flatten().cpu(), S["proj"].flatten().cpu(), S["campos"].cpu(), S["bg"].cpu()]).pin_memory()
+    dL_host = dL.cpu().pin_memory()
+    cam_dev = torch.empty_like(cam_host, device=dev)
+    dL_dev = torch.empty_like(dL_host, device=dev)
+    img_host = torch.empty(3, H, W).pin_memory()
+    loss_host = torch.empty(1).pin_memory()
+    leaves = dict(shs=S["shs"].clone().requires_grad_(True), opac=S["opac"].clone().requires_grad_(True),
+                  scales=S["scales"].clone().requires_grad_(True))
+    per_view = [dict(means=pv["means"].clone().requires_grad_(True), rots=pv["rots"].clone().requires_grad_(True))
+                for pv in pool]
+    means2D = torch.zeros(args.P, 3, device=dev, requires_grad=True)
+
+    def one_view(pv):
+        cam_dev.copy_(cam_host, non_blocking=True)
+        dL_dev.copy_(dL_host, non_blocking=True)
+        settings = GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=S["tanx"], tanfovy=S["tany"], bg=cam_dev[35:38], scale_modifier=1.0,
+            viewmatrix=cam_dev[0:16].view(4, 4), projmatrix=cam_dev[16:32].view(4, 4), sh_degree=D,
+            campos=cam_dev[32:35], prefiltered=False, debug=False)
+        color, _radii = GaussianRasterizer(settings)(means3D=pv["means"], means2D=means2D, opacities=leaves["opac"],
+                                                     shs=leaves["shs"], scales=leaves["scales"], rotations=pv["rots"])
+        loss = (color * dL_dev).sum()
+        loss.backward()
+        img_host.copy_(color.detach(), non_blocking=True)
+        loss_host.copy_(loss.detach().view(1), non_blocking=True)
+
+    def step():
+        for t in list(leaves.values()) + [means2D] + [x for pv in per_view for x in pv.values()]:
+            if t.grad is not None:
+                t.grad.zero_()
+        for pv in per_view:
+            one_view(pv)
+        if world > 1:
+            for t in (leaves["shs"], leaves["opac"], leaves["scales"], per_view[0]["means"], per_view[0]["rots"]):
+                dist.all_reduce(t.grad)
+        torch.cuda.current_stream().synchronize()  # the step's image and loss are on the host now
+
+    steps = max(3, args.steps // 3)
+    for _ in range(2):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = sharding.all_reduce_max(e0.elapsed_time(e1), dev)
+    if world > 1:
+        dist.barrier()
+    return {"value": round(world * vps * steps / (ms / 1e3), 2), "unit": "views/s",
+            "h2d_bytes_per_step": vps * (38 * 4 + 3 * H * W * 4), "d2h_bytes_per_step": vps * (3 * H * W * 4 + 4),
+            "steps": steps,
+            "what": "GaussianRasterizer.forward + autograd backward per view; per-view H2D (pinned) of camera bundle + "
+                    "dL/dcolour, D2H of rendered image + loss; Gaussian parameters resident (model state)"}
+
+
+def cpu_baseline(args, sc):
+    """C port of the reference algorithm (oracle/raster_oracle.c, OpenMP) on a bounded sample of the same workload."""
+    import oracle
+    from das3r_b200.synth import view_inputs, grad_seed
+
+    oracle.build()
+    dL = grad_seed(sc)
+    n = max(1, args.cpu_views)
+    vi = view_inputs(sc, 0, sh_degree=args.sh_degree)
+    fw = oracle.forward(**vi)  # warm-up (page-in, thread pool)
+    # exclude input construction: time only the oracle calls
+    t = 0.0
+    for v in range(n):
+        vi = view_inputs(sc, v % sc.V, sh_degree=args.sh_degree)
+        a = time.perf_counter()
+        fw = oracle.forward(**vi)
+        oracle.backward(fw, dL, **vi)
+        t += time.perf_counter() - a
+    return {"value": round(n / t, 4), "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{n} views (fwd+bwd) of the same {args.P}-Gaussian {args.W}x{args.H} scene through the C port of "
+                      f"the reference algorithm (oracle/raster_oracle.c, OpenMP on all {os.cpu_count()} host cores)"}
+
+
+def run_cpu_arm(args):
+    from das3r_b200.synth import synth_scene
+
+    sc = synth_scene(P=args.P, V=args.V, W=args.W, H=args.H, seed=args.seed, sh_degree=args.sh_degree)
+    cb = cpu_baseline(args, sc)
+    print(json.dumps({"impl": "oracle-cpu", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 0,
+                      "steps": args.cpu_views, "warmup": 1, "ms_per_step": round(1e3 / cb["value"], 2),
+                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                      "data": "synthetic", "config": {"workload": cb["sample"]}, "cpu_baseline": cb,
+                      "e2e": {"value": cb["value"], "unit": "views/s", "h2d_bytes_per_step": 0,
+                              "d2h_bytes_per_step": 0}}))
+
+
+if __name__ == "__main__":
+    main()

@@ -7,6 +7,8 @@
 #include <stdlib.h>
 #include <string.h>
 #include <string>
+#include <vector>
+#include <atomic>
 
 using namespace das3r;
 
@@ -79,13 +81,68 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
     L->binning_bytes = c.off;
 }
 
+// ---- optional per-stage CUDA-event timing + kernel launch counter (bench.py's roofline leg) ------------------------
+enum Stage {
+    ST_PREPROCESS_FWD = 0, ST_TILE_SCAN, ST_SCATTER, ST_TILE_SORT, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
+    ST_MEMSET, ST_COUNT
+};
+const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "blend_fwd",
+                                           "blend_bwd", "preprocess_bwd", "memset"};
+struct Pending {
+    int stage;
+    cudaEvent_t a, b;
+};
+struct Prof {
+    bool enabled = false;
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> free_events;
+    double ms[ST_COUNT] = {0};
+    long long calls[ST_COUNT] = {0};
+    cudaEvent_t get() {
+        if (!free_events.empty()) {
+            cudaEvent_t e = free_events.back();
+            free_events.pop_back();
+            return e;
+        }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
+};
+Prof g_prof;
+std::atomic<long long> g_launches{0};
+
+struct StageScope {
+    int stage;
+    cudaStream_t stream;
+    cudaEvent_t a = nullptr;
+    StageScope(int st, cudaStream_t s, int kernels) : stage(st), stream(s) {
+        g_launches += kernels;
+        if (g_prof.enabled) {
+            a = g_prof.get();
+            cudaEventRecord(a, stream);
+        }
+    }
+    ~StageScope() {
+        if (a) {
+            cudaEvent_t b = g_prof.get();
+            cudaEventRecord(b, stream);
+            g_prof.pending.push_back({stage, a, b});
+        }
+    }
+};
+
 bool check_params(const das3r_raster_params* p) {
     return p && p->P >= 0 && p->width > 0 && p->height > 0 && p->D >= 0 && p->D <= 3 && p->M >= 0;
 }
 
-#define STAGE(call, name)                                                   \
+#define STAGE(call, name, stage_id, nkernels)                               \
     do {                                                                    \
-        cudaError_t e_ = (call);                                            \
+        cudaError_t e_;                                                     \
+        {                                                                   \
+            StageScope scope_(stage_id, stream, nkernels);                  \
+            e_ = (call);                                                    \
+        }                                                                   \
         if (e_ != cudaSuccess) return fail(DAS3R_ECUDA, name, e_);          \
         if (params->debug) {                                                \
             e_ = cudaStreamSynchronize(stream);                             \
@@ -101,6 +158,40 @@ extern "C" {
 int das3r_abi_version(void) { return DAS3R_ABI_VERSION; }
 
 const char* das3r_last_error(void) { return g_err.c_str(); }
+
+int das3r_prof_enable(int on) {
+    g_prof.enabled = on != 0;
+    return DAS3R_OK;
+}
+
+int das3r_prof_num_stages(void) { return ST_COUNT; }
+
+const char* das3r_prof_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+
+int das3r_prof_collect(double* ms_total, long long* calls, int reset) {
+    for (auto& p : g_prof.pending) {
+        float ms = 0.f;
+        cudaError_t e = cudaEventSynchronize(p.b);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, p.a, p.b);
+        if (e != cudaSuccess) return fail(DAS3R_ECUDA, "prof_collect", e);
+        g_prof.ms[p.stage] += ms;
+        g_prof.calls[p.stage] += 1;
+        g_prof.free_events.push_back(p.a);
+        g_prof.free_events.push_back(p.b);
+    }
+    g_prof.pending.clear();
+    for (int i = 0; i < ST_COUNT; i++) {
+        if (ms_total) ms_total[i] = g_prof.ms[i];
+        if (calls) calls[i] = g_prof.calls[i];
+        if (reset) {
+            g_prof.ms[i] = 0;
+            g_prof.calls[i] = 0;
+        }
+    }
+    return DAS3R_OK;
+}
+
+long long das3r_launch_count(void) { return g_launches.load(); }
 
 int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
                                     das3r_raster_state_layout* out) {
@@ -169,7 +260,7 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     uint32_t* cursors = reinterpret_cast<uint32_t*>(img + L.i_cursors);
     uint32_t* totals = reinterpret_cast<uint32_t*>(img + L.i_totals);
 
-    STAGE(cudaMemsetAsync(tile_counts, 0, (size_t)T * 4, stream), "memset(tile_counts)");
+    STAGE(cudaMemsetAsync(tile_counts, 0, (size_t)T * 4, stream), "memset(tile_counts)", ST_MEMSET, 0);
 
     PreFwdArgs a;
     memset(&a, 0, sizeof(a));
@@ -186,8 +277,8 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     a.radii = out->radii; a.rec = rec; a.tiles_touched = tiles_touched; a.clamped = clamped;
     a.tile_counts = tile_counts;
     static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
-    STAGE(launch_preprocess_fwd(a, stage_sh, stream), "preprocess_fwd");
-    STAGE(launch_tile_scan(tile_counts, T, ranges, cursors, totals, stream), "tile_scan");
+    STAGE(launch_preprocess_fwd(a, stage_sh, stream), "preprocess_fwd", ST_PREPROCESS_FWD, 1);
+    STAGE(launch_tile_scan(tile_counts, T, ranges, cursors, totals, stream), "tile_scan", ST_TILE_SCAN, 1);
 
     // The one host round trip of the forward (the reference has the same one, rasterizer_impl.cu:281).
     uint32_t host_totals[4] = {0, 0, 0, 0};
@@ -212,18 +303,18 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     uint64_t* keys_sorted = params->debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
 
     if (R > 0) {
-        STAGE(launch_scatter(P, gx, gy, rec, out->radii, tiles_touched, cursors, unsorted, stream), "scatter");
+        STAGE(launch_scatter(P, gx, gy, rec, out->radii, tiles_touched, cursors, unsorted, stream), "scatter", ST_SCATTER, 1);
         if (!fallback)
             STAGE(launch_tile_sort(T, max_count, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, stream),
-                  "tile_sort");
+                  "tile_sort", ST_TILE_SORT, 1);
         else
             STAGE(launch_tile_sort_fallback(R, T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted,
                                             bin + X.b_fallback, X.fallback_bytes, stream),
-                  "tile_sort_fallback");
+                  "tile_sort_fallback", ST_TILE_SORT, 3);
     }
     STAGE(launch_blend_fwd(gx, gy, ranges, sorted_rec, W, H, params->background, final_T, n_contrib, out->out_color,
                            out->out_depth, out->out_alpha, stream),
-          "blend_fwd");
+          "blend_fwd", ST_BLEND_FWD, 1);
     return R;
 }
 
@@ -239,8 +330,8 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     if (!check_params(params) || !in || !state || !g) return fail_msg(DAS3R_EINVAL, "backward: null or invalid argument");
     const int P = params->P, W = params->width, H = params->height;
     if (P == 0) return DAS3R_OK;
-    if (!radii || !dL_dpix || !state->geom || !state->image || !g->dL_dmeans2D || !g->dL_dcolors || !g->dL_dopacity ||
-        !g->dL_dmeans3D || !g->dL_dcov3D || !g->dL_dscales || !g->dL_drotations || !g->scratch)
+    if (!radii || !dL_dpix || !state->geom || !state->image || !g->dL_dopacity || !g->dL_dmeans3D || !g->dL_dscales ||
+        !g->dL_drotations || !g->scratch)
         return fail_msg(DAS3R_EINVAL, "backward: null buffer");
     if (in->shs && !g->dL_dsh) return fail_msg(DAS3R_EINVAL, "backward: dL_dsh is null although shs is given");
     const int R = state->num_rendered;
@@ -262,13 +353,13 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     const uint32_t* n_contrib = reinterpret_cast<const uint32_t*>(state->image + L.i_n_contrib);
     const uint2* ranges = reinterpret_cast<const uint2*>(state->image + L.i_ranges);
 
-    STAGE(cudaMemsetAsync(g->scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)");
+    STAGE(cudaMemsetAsync(g->scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)", ST_MEMSET, 0);
     if (R > 0) {
         const uint32_t* point_list = reinterpret_cast<const uint32_t*>(state->binning + L.b_point_list);
         const GaussRec* sorted_rec = reinterpret_cast<const GaussRec*>(state->binning + L.b_sA);
         STAGE(launch_blend_bwd(gx, gy, ranges, point_list, sorted_rec, W, H, params->background, final_T, n_contrib,
                                dL_dpix, g->scratch, stream),
-              "blend_bwd");
+              "blend_bwd", ST_BLEND_BWD, 1);
     }
     PreBwdArgs a;
     memset(&a, 0, sizeof(a));
@@ -284,7 +375,8 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     a.dL_dmeans2D = g->dL_dmeans2D; a.dL_dcolors = g->dL_dcolors; a.dL_dopacity = g->dL_dopacity;
     a.dL_dmeans3D = g->dL_dmeans3D; a.dL_dcov3D = g->dL_dcov3D; a.dL_dsh = in->shs ? g->dL_dsh : nullptr;
     a.dL_dscales = g->dL_dscales; a.dL_drots = g->dL_drotations;
-    STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd");
+    a.accumulate = g->accumulate;
+    STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd", ST_PREPROCESS_BWD, 1);
     return DAS3R_OK;
 }
 
@@ -294,6 +386,7 @@ int das3r_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
     if (P < 0) return fail_msg(DAS3R_EINVAL, "mark_visible: P < 0");
     if (P == 0) return DAS3R_OK;
     if (!means3D || !viewmatrix || !projmatrix || !present) return fail_msg(DAS3R_EINVAL, "mark_visible: null pointer");
+    g_launches += 1;
     cudaError_t e =
         launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, static_cast<cudaStream_t>(stream_v));
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "mark_visible", e);
@@ -309,6 +402,7 @@ int das3r_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scr
     if (P == 0) return DAS3R_OK;
     if (!points || !mean_dist2 || !scratch) return fail_msg(DAS3R_EINVAL, "knn: null pointer");
     if (scratch_bytes < knn_scratch_bytes(P)) return fail_msg(DAS3R_EINVAL, "knn: scratch too small");
+    g_launches += 7;  // init, bbox, morton, (library sort), gather, boxes, search
     cudaError_t e = knn_dist2(P, points, mean_dist2, scratch, scratch_bytes, static_cast<cudaStream_t>(stream_v));
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "knn", e);
     return DAS3R_OK;

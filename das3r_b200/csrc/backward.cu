@@ -307,18 +307,29 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
     float* sh_out = a.dL_dsh ? a.dL_dsh + (size_t)idx * nsh : nullptr;
     const bool sh_aligned = ((a.M & 3) == 0);
 
+    const bool accum = a.accumulate != 0;
+    auto put1 = [accum](float* p, float v) { *p = accum ? *p + v : v; };
+    auto put4 = [accum](float4* p, float4 v) {
+        if (accum) {
+            float4 o = *p;
+            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+        }
+        *p = v;
+    };
     if (!(a.radii[idx] > 0)) {
+        if (accum) return;  // nothing to add
         // invisible: every gradient is zero (the reference relies on torch::zeros for this)
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            a.dL_dmeans2D[3 * idx + k] = 0.f;
-            a.dL_dcolors[3 * idx + k] = 0.f;
+            if (a.dL_dmeans2D) a.dL_dmeans2D[3 * idx + k] = 0.f;
+            if (a.dL_dcolors) a.dL_dcolors[3 * idx + k] = 0.f;
             a.dL_dmeans3D[3 * idx + k] = 0.f;
             a.dL_dscales[3 * idx + k] = 0.f;
         }
         a.dL_dopacity[idx] = 0.f;
+        if (a.dL_dcov3D)
 #pragma unroll
-        for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = 0.f;
+            for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = 0.f;
         reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (sh_out) {
             if (sh_aligned && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
@@ -338,13 +349,17 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
     const float dL_dopac = q1.y;
     const float3 dL_dcol = {q1.z, q1.w, q2.x};
 
-    a.dL_dmeans2D[3 * idx + 0] = dL_dmean2D_x;
-    a.dL_dmeans2D[3 * idx + 1] = dL_dmean2D_y;
-    a.dL_dmeans2D[3 * idx + 2] = 0.f;
-    a.dL_dcolors[3 * idx + 0] = dL_dcol.x;
-    a.dL_dcolors[3 * idx + 1] = dL_dcol.y;
-    a.dL_dcolors[3 * idx + 2] = dL_dcol.z;
-    a.dL_dopacity[idx] = dL_dopac;
+    if (a.dL_dmeans2D) {
+        put1(&a.dL_dmeans2D[3 * idx + 0], dL_dmean2D_x);
+        put1(&a.dL_dmeans2D[3 * idx + 1], dL_dmean2D_y);
+        put1(&a.dL_dmeans2D[3 * idx + 2], 0.f);
+    }
+    if (a.dL_dcolors) {
+        put1(&a.dL_dcolors[3 * idx + 0], dL_dcol.x);
+        put1(&a.dL_dcolors[3 * idx + 1], dL_dcol.y);
+        put1(&a.dL_dcolors[3 * idx + 2], dL_dcol.z);
+    }
+    put1(&a.dL_dopacity[idx], dL_dopac);
 
     const float3 mean = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
     float cov3D[6];
@@ -389,8 +404,9 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
 #pragma unroll
         for (int i = 0; i < 6; i++) dL_dcov[i] = 0;
     }
+    if (a.dL_dcov3D)
 #pragma unroll
-    for (int i = 0; i < 6; i++) a.dL_dcov3D[6 * idx + i] = dL_dcov[i];
+        for (int i = 0; i < 6; i++) put1(&a.dL_dcov3D[6 * idx + i], dL_dcov[i]);
 
     float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
                     (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
@@ -459,17 +475,17 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
                 v.y = (4 * j + 1 < nw) ? o[4 * j + 1] : 0.f;
                 v.z = (4 * j + 2 < nw) ? o[4 * j + 2] : 0.f;
                 v.w = (4 * j + 3 < nw) ? o[4 * j + 3] : 0.f;
-                o4[j] = v;
+                if (!accum || 4 * j < nw) put4(&o4[j], v);
             }
         } else {
 #pragma unroll
             for (int j = 0; j < 48; j++)
-                if (j < nsh) sh_out[j] = (j < nw) ? o[j] : 0.f;
+                if (j < nsh && (!accum || j < nw)) put1(&sh_out[j], (j < nw) ? o[j] : 0.f);
         }
     }
-    a.dL_dmeans3D[3 * idx + 0] = dL_dmean_acc.x;
-    a.dL_dmeans3D[3 * idx + 1] = dL_dmean_acc.y;
-    a.dL_dmeans3D[3 * idx + 2] = dL_dmean_acc.z;
+    put1(&a.dL_dmeans3D[3 * idx + 0], dL_dmean_acc.x);
+    put1(&a.dL_dmeans3D[3 * idx + 1], dL_dmean_acc.y);
+    put1(&a.dL_dmeans3D[3 * idx + 2], dL_dmean_acc.z);
 
     // ---- computeCov3D backward (backward.cu:278-341) ----
     if (a.scales != nullptr) {
@@ -498,9 +514,9 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
         dsc.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
         dsc.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
         dsc.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
-        a.dL_dscales[3 * idx + 0] = dsc.x;
-        a.dL_dscales[3 * idx + 1] = dsc.y;
-        a.dL_dscales[3 * idx + 2] = dsc.z;
+        put1(&a.dL_dscales[3 * idx + 0], dsc.x);
+        put1(&a.dL_dscales[3 * idx + 1], dsc.y);
+        put1(&a.dL_dscales[3 * idx + 2], dsc.z);
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             dL_dMt.m[0][k] *= s.x;
@@ -516,8 +532,8 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
                2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
         dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
                2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
-        reinterpret_cast<float4*>(a.dL_drots)[idx] = dq;
-    } else {
+        put4(&reinterpret_cast<float4*>(a.dL_drots)[idx], dq);
+    } else if (!accum) {
         a.dL_dscales[3 * idx + 0] = 0.f;
         a.dL_dscales[3 * idx + 1] = 0.f;
         a.dL_dscales[3 * idx + 2] = 0.f;

@@ -47,6 +47,7 @@ struct PreBwdArgs {
     const uint8_t* clamped;
     const float* acc;  // [P][ACC_STRIDE]
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drots;
+    int accumulate;  // 1: outputs += gradient, invisible Gaussians untouched; 0: outputs = gradient (zeros if invisible)
 };
 
 // forward.cu

@@ -7,6 +7,7 @@
 #include <c10/cuda/CUDAStream.h>
 #include <tuple>
 #include <string>
+#include <vector>
 #include "../../include/das3r_raster.h"
 
 namespace {
@@ -142,14 +143,15 @@ RasterizeGaussiansExCUDA(const torch::Tensor& background, const torch::Tensor& m
 
 std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
            torch::Tensor>
-RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D_,
+backward_impl(const torch::Tensor& background, const torch::Tensor& means3D_,
                                const torch::Tensor& radii_, const torch::Tensor& colors_, const torch::Tensor& scales_,
                                const torch::Tensor& rotations_, const float scale_modifier,
                                const torch::Tensor& cov3D_precomp_, const torch::Tensor& viewmatrix_,
                                const torch::Tensor& projmatrix_, const float tan_fovx, const float tan_fovy,
                                const torch::Tensor& dL_dout_color_, const torch::Tensor& sh_, const int degree,
                                const torch::Tensor& campos_, const torch::Tensor& geomBuffer, const int R,
-                               const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug) {
+                               const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                               const std::vector<torch::Tensor>* outs, const bool accumulate) {
     TORCH_CHECK(means3D_.is_cuda(), "means3D must be a CUDA tensor: this rasterizer has no CPU path");
     const auto dev = means3D_.device();
     c10::cuda::CUDAGuard guard(dev);
@@ -176,14 +178,30 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
 
     auto o = means3D.options();
     // torch::empty, not zeros: the backward kernels write every element (incl. the zeros of invisible Gaussians).
-    torch::Tensor dL_dmeans3D = torch::empty({P, 3}, o);
-    torch::Tensor dL_dmeans2D = torch::empty({P, 3}, o);
-    torch::Tensor dL_dcolors = torch::empty({P, 3}, o);
-    torch::Tensor dL_dopacity = torch::empty({P, 1}, o);
-    torch::Tensor dL_dcov3D = torch::empty({P, 6}, o);
-    torch::Tensor dL_dsh = torch::empty({P, M, 3}, o);
-    torch::Tensor dL_dscales = torch::empty({P, 3}, o);
-    torch::Tensor dL_drotations = torch::empty({P, 4}, o);
+    torch::Tensor dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations;
+    if (outs) {
+        // caller-provided gradient buffers, same order as the returned tuple
+        TORCH_CHECK(outs->size() == 8, "expected 8 gradient tensors");
+        const int64_t want[8] = {3LL * P, 3LL * P, (int64_t)P, 3LL * P, 6LL * P, 3LL * M * P, 3LL * P, 4LL * P};
+        for (int i = 0; i < 8; i++) {
+            const auto& t = (*outs)[i];
+            if ((i == 0 || i == 1 || i == 4) && (!t.defined() || t.numel() == 0)) continue;  // optional outputs
+            TORCH_CHECK(t.is_cuda() && t.device() == dev && t.scalar_type() == torch::kFloat32 && t.is_contiguous() &&
+                            t.numel() == want[i],
+                        "gradient buffer ", i, " must be a contiguous float32 CUDA tensor of ", want[i], " elements");
+        }
+        dL_dmeans2D = (*outs)[0]; dL_dcolors = (*outs)[1]; dL_dopacity = (*outs)[2]; dL_dmeans3D = (*outs)[3];
+        dL_dcov3D = (*outs)[4]; dL_dsh = (*outs)[5]; dL_dscales = (*outs)[6]; dL_drotations = (*outs)[7];
+    } else {
+        dL_dmeans3D = torch::empty({P, 3}, o);
+        dL_dmeans2D = torch::empty({P, 3}, o);
+        dL_dcolors = torch::empty({P, 3}, o);
+        dL_dopacity = torch::empty({P, 1}, o);
+        dL_dcov3D = torch::empty({P, 6}, o);
+        dL_dsh = torch::empty({P, M, 3}, o);
+        dL_dscales = torch::empty({P, 3}, o);
+        dL_drotations = torch::empty({P, 4}, o);
+    }
 
     if (P != 0) {
         torch::Tensor scratch = torch::empty({(long long)das3r_raster_backward_scratch_bytes(P)},
@@ -220,21 +238,56 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
         st.image_bytes = imageBuffer.numel();
         st.num_rendered = R;
         das3r_raster_grads g;
-        g.dL_dmeans2D = dL_dmeans2D.data_ptr<float>();
-        g.dL_dcolors = dL_dcolors.data_ptr<float>();
+        auto optp = [](torch::Tensor& t) { return t.defined() && t.numel() > 0 ? t.data_ptr<float>() : nullptr; };
+        g.dL_dmeans2D = optp(dL_dmeans2D);
+        g.dL_dcolors = optp(dL_dcolors);
         g.dL_dopacity = dL_dopacity.data_ptr<float>();
         g.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();
-        g.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        g.dL_dcov3D = optp(dL_dcov3D);
         g.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
         g.dL_dscales = dL_dscales.data_ptr<float>();
         g.dL_drotations = dL_drotations.data_ptr<float>();
         g.scratch = reinterpret_cast<float*>(scratch.data_ptr());
+        g.accumulate = accumulate ? 1 : 0;
         cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
         check(das3r_raster_backward(&p, &in, radii.data_ptr<int>(), &st, dL_dout.data_ptr<float>(), &g, stream),
               "rasterize_gaussians_backward");
     }
     return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
                            dL_drotations);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+           torch::Tensor>
+RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D,
+                               const torch::Tensor& radii, const torch::Tensor& colors, const torch::Tensor& scales,
+                               const torch::Tensor& rotations, const float scale_modifier,
+                               const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                               const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                               const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                               const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                               const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug) {
+    return backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                         viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R,
+                         binningBuffer, imageBuffer, debug, nullptr, false);
+}
+
+// Additive: same backward, but the 8 gradients go into caller-provided tensors (order of the returned tuple), either
+// overwritten or accumulated (`accumulate`): sums the views of a step in place, e.g. into one flat all-reduce bucket.
+void RasterizeGaussiansBackwardIntoCUDA(const torch::Tensor& background, const torch::Tensor& means3D,
+                                        const torch::Tensor& radii, const torch::Tensor& colors,
+                                        const torch::Tensor& scales, const torch::Tensor& rotations,
+                                        const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                                        const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
+                                        const float tan_fovx, const float tan_fovy, const torch::Tensor& dL_dout_color,
+                                        const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                                        const torch::Tensor& geomBuffer, const int R,
+                                        const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer,
+                                        const bool debug, const std::vector<torch::Tensor>& outs,
+                                        const bool accumulate) {
+    backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                  projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
+                  imageBuffer, debug, &outs, accumulate);
 }
 
 torch::Tensor markVisible(torch::Tensor& means3D_, torch::Tensor& viewmatrix_, torch::Tensor& projmatrix_) {
@@ -278,6 +331,18 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
     m.def("rasterize_gaussians_ex", &RasterizeGaussiansExCUDA);
     m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
+    m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardIntoCUDA);
+    m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
+    m.def("prof_collect", [](bool reset) {
+        int n = das3r_prof_num_stages();
+        std::vector<double> ms(n);
+        std::vector<long long> calls(n);
+        if (das3r_prof_collect(ms.data(), calls.data(), reset ? 1 : 0) < 0) throw std::runtime_error(das3r_last_error());
+        std::vector<std::tuple<std::string, double, long long>> out;
+        for (int i = 0; i < n; i++) out.emplace_back(das3r_prof_stage_name(i), ms[i], calls[i]);
+        return out;
+    });
+    m.def("launch_count", []() { return das3r_launch_count(); });
     m.def("mark_visible", &markVisible);
     m.def("distCUDA2", &distCUDA2);
     m.def("abi_version", []() { return das3r_abi_version(); });

@@ -88,15 +88,19 @@ typedef struct das3r_raster_state {
 /* Gradient outputs (device, caller-allocated, need NOT be pre-zeroed: every element is written).
  * Shapes follow RasterizeGaussiansBackwardCUDA, rasterize_points.cu:151-159. */
 typedef struct das3r_raster_grads {
-    float* dL_dmeans2D;    /* [P,3] (z is always 0: backward.cu:545-546 never writes it) */
-    float* dL_dcolors;     /* [P,3] */
+    float* dL_dmeans2D;    /* [P,3] (z is always 0: backward.cu:545-546 never writes it); may be NULL = not wanted */
+    float* dL_dcolors;     /* [P,3]; may be NULL = not wanted */
     float* dL_dopacity;    /* [P] */
     float* dL_dmeans3D;    /* [P,3] */
-    float* dL_dcov3D;      /* [P,6] */
+    float* dL_dcov3D;      /* [P,6]; may be NULL = not wanted */
     float* dL_dsh;         /* [P,M,3] or NULL when M == 0 */
     float* dL_dscales;     /* [P,3] */
     float* dL_drotations;  /* [P,4] */
     float* scratch;        /* device scratch, das3r_raster_backward_scratch_bytes(P) bytes; contents undefined */
+    int32_t accumulate;    /* 0: every gradient element is overwritten (reference behaviour: fresh zero-filled
+                              tensors). 1: gradients are ADDED to what the buffers hold and Gaussians that were not
+                              rendered are left untouched - used to sum several views of a step without a second pass
+                              (no reference counterpart; there autograd's AccumulateGrad does it in extra kernels). */
 } das3r_raster_grads;
 
 /* Library / ABI version (DAS3R_ABI_VERSION). No reference counterpart. */
@@ -135,7 +139,8 @@ int das3r_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
 /* Mean squared distance to the 3 nearest other points. Replaces SimpleKNN::knn (simple-knn/simple_knn.h,
  * simple_knn.cu:186-222) behind distCUDA2 (spatial.cu:15-25). points: device [P,3]; mean_dist2: device [P].
  * Scratch comes from the caller (the reference cudaMallocs internally, simple_knn.cu:189-217):
- * call das3r_knn_scratch_bytes(P) first. Blocks the host once (bounding-box read-back, as simple_knn.cu:197-201). */
+ * call das3r_knn_scratch_bytes(P) first. Does not block the host (the reference copies the bounding box back twice,
+ * simple_knn.cu:197-201; here it stays on the device). */
 size_t das3r_knn_scratch_bytes(int32_t P);
 int das3r_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes,
                     void* stream);
@@ -163,6 +168,16 @@ typedef struct das3r_raster_state_layout {
 } das3r_raster_state_layout;
 int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
                                     das3r_raster_state_layout* out);
+
+/* Measurement hooks used by bench.py (no reference counterpart): when enabled, every stage of forward/backward is
+ * bracketed by CUDA events on the launching stream; das3r_prof_collect waits for them and returns, per stage
+ * (das3r_prof_stage_name(i), i < das3r_prof_num_stages()), the summed device time in ms and the number of launches.
+ * das3r_launch_count() is the number of this library's kernels launched by the process so far. Not thread-safe. */
+int das3r_prof_enable(int on);
+int das3r_prof_num_stages(void);
+const char* das3r_prof_stage_name(int i);
+int das3r_prof_collect(double* ms_total, long long* calls, int reset);
+long long das3r_launch_count(void);
 
 #ifdef __cplusplus
 }
