@@ -72,9 +72,9 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
     const size_t n = (size_t)R;
     L->b_unsorted = c.take(n * 8);
     L->b_point_list = c.take(n * 4);
-    L->b_sA = c.take(n * sizeof(GaussRec));
-    L->b_sB = L->b_sA + 16;
-    L->b_sC = L->b_sA + 32;
+    L->b_sA = c.take(n * 16);  // float4[R]  {x, y, h, -tau'}
+    L->b_sB = c.take(n * 32);  // float4[R][2] {conic, opacity} {rgb, gaussian index}
+    L->b_sC = L->b_sB + 16;
     L->b_keys_sorted = with_keys ? c.take(n * 8) : (size_t)0;
     X->fallback_bytes = with_fallback ? tile_sort_fallback_bytes(R, T) : 0;
     X->b_fallback = with_fallback ? c.take(X->fallback_bytes) : 0;
@@ -299,20 +299,21 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     state->binning_bytes = L.binning_bytes;
     uint64_t* unsorted = reinterpret_cast<uint64_t*>(bin + L.b_unsorted);
     uint32_t* point_list = reinterpret_cast<uint32_t*>(bin + L.b_point_list);
-    GaussRec* sorted_rec = reinterpret_cast<GaussRec*>(bin + L.b_sA);
+    float4* sA = reinterpret_cast<float4*>(bin + L.b_sA);
+    float4* sBC = reinterpret_cast<float4*>(bin + L.b_sB);
     uint64_t* keys_sorted = params->debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
 
     if (R > 0) {
         STAGE(launch_scatter(P, gx, gy, rec, out->radii, tiles_touched, cursors, unsorted, stream), "scatter", ST_SCATTER, 1);
         if (!fallback)
-            STAGE(launch_tile_sort(T, max_count, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, stream),
+            STAGE(launch_tile_sort(T, max_count, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, stream),
                   "tile_sort", ST_TILE_SORT, 1);
         else
-            STAGE(launch_tile_sort_fallback(R, T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted,
+            STAGE(launch_tile_sort_fallback(R, T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted,
                                             bin + X.b_fallback, X.fallback_bytes, stream),
                   "tile_sort_fallback", ST_TILE_SORT, 3);
     }
-    STAGE(launch_blend_fwd(gx, gy, ranges, sorted_rec, W, H, params->background, final_T, n_contrib, out->out_color,
+    STAGE(launch_blend_fwd(gx, gy, ranges, sA, sBC, rec, W, H, params->background, final_T, n_contrib, out->out_color,
                            out->out_depth, out->out_alpha, stream),
           "blend_fwd", ST_BLEND_FWD, 1);
     return R;
@@ -355,9 +356,9 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
 
     STAGE(cudaMemsetAsync(g->scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)", ST_MEMSET, 0);
     if (R > 0) {
-        const uint32_t* point_list = reinterpret_cast<const uint32_t*>(state->binning + L.b_point_list);
-        const GaussRec* sorted_rec = reinterpret_cast<const GaussRec*>(state->binning + L.b_sA);
-        STAGE(launch_blend_bwd(gx, gy, ranges, point_list, sorted_rec, W, H, params->background, final_T, n_contrib,
+        const float4* sA = reinterpret_cast<const float4*>(state->binning + L.b_sA);
+        const float4* sBC = reinterpret_cast<const float4*>(state->binning + L.b_sB);
+        STAGE(launch_blend_bwd(gx, gy, ranges, sA, sBC, W, H, params->background, final_T, n_contrib,
                                dL_dpix, g->scratch, stream),
               "blend_bwd", ST_BLEND_BWD, 1);
     }

@@ -1,47 +1,38 @@
 // Backward path of the sm_100a Gaussian-splat rasterizer:
 //   blend_bwd       -> back-to-front replay per 16x16 tile (replaces renderCUDA, reference
-//                      cuda_rasterizer/backward.cu:399-557). Per-Gaussian partials are reduced across the warp with
-//                      shuffles, accumulated per tile batch in shared memory, and flushed with ONE global atomic per
-//                      (tile instance, component) instead of one per (pixel, Gaussian) pair (backward.cu:523-554).
+//                      cuda_rasterizer/backward.cu:399-557); only pairs that really contribute reach the gradient
+//                      math, and their 9 partials leave as two 128-bit + one 32-bit atomics (backward.cu:523-554 uses
+//                      nine scalar ones per pair).
 //   preprocess_bwd  -> computeCov2DCUDA (backward.cu:144-274) + preprocessCUDA (:346-396) + SH backward (:20-139) +
 //                      cov3D backward (:278-341) fused into one pass that also writes the zeros the reference gets from
 //                      nine torch::zeros fills (rasterize_points.cu:151-159).
 #include "common.cuh"
 #include "kernels.cuh"
+#include "blend_common.cuh"
 
 namespace das3r {
 
-constexpr int BLEND_BATCH = 256;
-constexpr int NACC = 9;
-
-struct BlendBwdSmem {
-    GaussRec rec[2][BLEND_BATCH];
-    float acc[NACC][BLEND_BATCH];
-    uint64_t bar[2];
-    uint32_t warp_max[8];
-};
-
-__global__ void __launch_bounds__(256) blend_bwd_kernel(const uint2* __restrict__ ranges,
-                                                        const uint32_t* __restrict__ point_list,
-                                                        const GaussRec* __restrict__ sorted_rec, int W, int H,
-                                                        const float* __restrict__ bg,
-                                                        const float* __restrict__ final_Ts,
-                                                        const uint32_t* __restrict__ n_contrib,
-                                                        const float* __restrict__ dL_dpixels,
-                                                        float* __restrict__ acc_out) {
-    __shared__ __align__(128) BlendBwdSmem sm;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+// Walks the tile list back to front with the same three levels as blend_fwd (warp-rectangle ballot + ring compaction,
+// per-lane power >= -tau' scan into a register queue, lockstep drain), every warp on its own. In the drain every lane
+// holds a DIFFERENT (pixel, Gaussian) pair that really contributes, evaluates backward.cu:490-554 for it and adds the 9
+// partial gradients to the Gaussian's 48-byte accumulator with two 128-bit and one 32-bit no-return atomics
+// (REDG.E.ADD.F32x4) instead of the reference's nine scalar ones.
+__global__ void __launch_bounds__(32 * BLEND_WARPS) blend_bwd_kernel(
+    const uint2* __restrict__ ranges, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
+    unsigned gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
+    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, float* __restrict__ acc_out) {
+    __shared__ __align__(16) RingRec ring_all[BLEND_WARPS][RING];
+    const int lane = threadIdx.x & 31;
+    RingRec* ring = ring_all[threadIdx.x >> 5];
+    const WarpRect wr = warp_rect(W, H, gx);
+    const uint2 range = ranges[wr.tile];
     const int n = (int)(range.y - range.x);
     if (n == 0) return;
-
-    const int wx0 = blockIdx.x * TILE_X + (warp & 1) * 8;
-    const int wy0 = blockIdx.y * TILE_Y + (warp >> 1) * 4;
-    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
-    const bool inside = px < W && py < H;
-    const int pix_id = W * py + px;
-    const float2 pixf = {(float)px, (float)py};
-    const float rx0 = (float)wx0, rx1 = (float)(wx0 + 7), ry0 = (float)wy0, ry1 = (float)(wy0 + 3);
+    const int pix_id = W * wr.py + wr.px;
+    const bool inside = wr.inside;
+    const float2 pixf = {(float)wr.px, (float)wr.py};
+    const float rx0 = (float)wr.wx0, rx1 = (float)(wr.wx0 + 7), ry0 = (float)wr.wy0, ry1 = (float)(wr.wy0 + 3);
+    const unsigned lt_mask = (1u << lane) - 1u;
 
     // backward.cu:431-458
     const float T_final = inside ? final_Ts[pix_id] : 0;
@@ -60,155 +51,123 @@ __global__ void __launch_bounds__(256) blend_bwd_kernel(const uint2* __restrict_
 #pragma unroll
     for (int i = 0; i < 3; i++) bg_dot_dpixel += bg[i] * dL_dpixel[i];
 
-    // Highest list position any pixel of this warp / block still needs.
+    // Highest list position any pixel of this warp still needs: everything behind it is skipped.
     uint32_t wmax = last_contributor;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
-    if (lane == 0) sm.warp_max[warp] = wmax;
-    if (tid == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
-        mbar_fence_init();
-    }
-    for (int i = tid; i < NACC * BLEND_BATCH; i += 256) (&sm.acc[0][0])[i] = 0.f;
-    __syncthreads();
-    uint32_t bmax = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) bmax = max(bmax, sm.warp_max[w]);
-    if (bmax == 0) return;  // nothing contributed anywhere in this tile
-    const int bstart = (int)((bmax - 1) / BLEND_BATCH);
-    const int nsteps = bstart + 1;
+    if (wmax == 0) return;
 
-    auto batch_count = [&](int b) { return min(BLEND_BATCH, n - b * BLEND_BATCH); };
-    if (tid == 0) {
-        for (int i = 0; i < min(nsteps, 2); i++) {
-            int b = bstart - i;
-            uint32_t bytes = (uint32_t)batch_count(b) * (uint32_t)sizeof(GaussRec);
-            mbar_expect_tx(&sm.bar[i], bytes);
-            tma_load_1d(&sm.rec[i][0], sorted_rec + range.x + (size_t)b * BLEND_BATCH, bytes, &sm.bar[i]);
-        }
-    }
+    uint64_t q = 0;
+    int cnt = 0;
+    uint32_t ring_head = 0, ring_free_from = 0;
 
-    for (int i = 0; i < nsteps; i++) {
-        const int b = bstart - i;
-        const int st = i & 1;
-        const int cnt = batch_count(b);
-        mbar_wait(&sm.bar[st], (uint32_t)((i >> 1) & 1));
-        const GaussRec* rec = sm.rec[st];
-        const int base_pos = b * BLEND_BATCH;
-
-        if ((uint32_t)base_pos < wmax) {
-            // chunks of 32 list entries, highest first
-            for (int c0 = ((min(cnt, (int)wmax - base_pos) - 1) / 32) * 32; c0 >= 0; c0 -= 32) {
-                const int g = c0 + lane;
-                bool ov = false;
-                if (g < cnt) {
-                    float4 A = rec[g].A;
-                    ov = (A.z >= 0.f) && (A.x + A.z >= rx0) && (A.x - A.z <= rx1) && (A.y + A.w >= ry0) &&
-                         (A.y - A.w <= ry1);
-                }
-                unsigned m = __ballot_sync(0xffffffffu, ov);
-                while (m) {
-                    const int j = 31 - __clz(m);
-                    m &= ~(1u << j);
-                    const int gi = c0 + j;
-                    const uint32_t pos = (uint32_t)(base_pos + gi);
-                    float gr[NACC];
+    auto drain = [&]() {
+#pragma unroll 1
+        for (int k = 0; k < QCAP; k++) {
+            if (__ballot_sync(0xffffffffu, k < cnt) == 0) break;
+            if (k < cnt) {
+                const RingRec& r = ring[(uint32_t)(q >> (8 * k)) & 0xffu];
+                // backward.cu:490-554
+                const float4 A = r.A;
+                const float4 con_o = r.B;
+                const float2 d = {A.x - pixf.x, A.y - pixf.y};
+                const float power = splat_power(con_o, d);
+                const float G = expf(power);
+                const float alpha = min(0.99f, __fmul_rn(con_o.w, G));
+                if (!(alpha < 1.0f / 255.0f)) {
+                    const float4 col4 = r.C;
+                    const float col[3] = {col4.x, col4.y, col4.z};
+                    T = T / (1.f - alpha);
+                    const float dchannel_dcolor = alpha * T;
+                    float dL_dalpha = 0.0f;
+                    float gcol[3];
 #pragma unroll
-                    for (int k = 0; k < NACC; k++) gr[k] = 0.f;
-                    bool contrib = false;
-                    if (pos < last_contributor) {
-                        // backward.cu:490-554
-                        const float4 A = rec[gi].A;
-                        const float4 con_o = rec[gi].B;
-                        const float2 d = {A.x - pixf.x, A.y - pixf.y};
-                        const float power =
-                            -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-                        if (!(power > 0.0f)) {
-                            const float G = expf(power);
-                            const float alpha = min(0.99f, con_o.w * G);
-                            if (!(alpha < 1.0f / 255.0f)) {
-                                contrib = true;
-                                const float4 col4 = rec[gi].C;
-                                const float col[3] = {col4.x, col4.y, col4.z};
-                                T = T / (1.f - alpha);
-                                const float dchannel_dcolor = alpha * T;
-                                float dL_dalpha = 0.0f;
-#pragma unroll
-                                for (int ch = 0; ch < 3; ch++) {
-                                    const float c = col[ch];
-                                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                                    last_color[ch] = c;
-                                    const float dL_dchannel = dL_dpixel[ch];
-                                    dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
-                                    gr[6 + ch] = dchannel_dcolor * dL_dchannel;
-                                }
-                                dL_dalpha *= T;
-                                last_alpha = alpha;
-                                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-                                const float dL_dG = con_o.w * dL_dalpha;
-                                const float gdx = G * d.x;
-                                const float gdy = G * d.y;
-                                const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-                                const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-                                gr[0] = dL_dG * dG_ddelx * ddelx_dx;
-                                gr[1] = dL_dG * dG_ddely * ddely_dy;
-                                gr[2] = -0.5f * gdx * d.x * dL_dG;
-                                gr[3] = -0.5f * gdx * d.y * dL_dG;
-                                gr[4] = -0.5f * gdy * d.y * dL_dG;
-                                gr[5] = G * dL_dalpha;
-                            }
-                        }
+                    for (int ch = 0; ch < 3; ch++) {
+                        const float c = col[ch];
+                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                        last_color[ch] = c;
+                        const float dL_dchannel = dL_dpixel[ch];
+                        dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
+                        gcol[ch] = dchannel_dcolor * dL_dchannel;
                     }
-                    if (__ballot_sync(0xffffffffu, contrib) != 0) {
-#pragma unroll
-                        for (int k = 0; k < NACC; k++) {
-#pragma unroll
-                            for (int o = 16; o > 0; o >>= 1) gr[k] += __shfl_xor_sync(0xffffffffu, gr[k], o);
-                        }
-                        // lane k adds component k: pick it without dynamic register indexing
-                        float v = gr[0];
-#pragma unroll
-                        for (int k = 1; k < NACC; k++) v = (lane == k) ? gr[k] : v;
-                        if (lane < NACC) atomicAdd(&sm.acc[lane][gi], v);
-                    }
+                    dL_dalpha *= T;
+                    last_alpha = alpha;
+                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                    const float dL_dG = con_o.w * dL_dalpha;
+                    const float gdx = G * d.x;
+                    const float gdy = G * d.y;
+                    const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
+                    const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
+                    float* dst = acc_out + (size_t)__float_as_uint(col4.w) * ACC_STRIDE;
+                    atomicAdd(reinterpret_cast<float4*>(dst),
+                              make_float4(dL_dG * dG_ddelx * ddelx_dx, dL_dG * dG_ddely * ddely_dy,
+                                          -0.5f * gdx * d.x * dL_dG, -0.5f * gdx * d.y * dL_dG));
+                    atomicAdd(reinterpret_cast<float4*>(dst) + 1,
+                              make_float4(-0.5f * gdy * d.y * dL_dG, G * dL_dalpha, gcol[0], gcol[1]));
+                    atomicAdd(dst + 8, gcol[2]);
                 }
             }
         }
-        __syncthreads();
-        // flush this batch's accumulators: one global atomic per (tile instance, component)
-        if (tid < cnt) {
-            float v[NACC];
-            bool any = false;
-#pragma unroll
-            for (int k = 0; k < NACC; k++) {
-                v[k] = sm.acc[k][tid];
-                any = any || (v[k] != 0.f);
-                sm.acc[k][tid] = 0.f;
+        q = 0;
+        cnt = 0;
+    };
+
+    const float4* gA = sA + range.x;
+    const float4* gBC = sBC + 2 * (size_t)range.x;
+    const int nn = min(n, (int)wmax);  // list positions >= wmax are behind every pixel's last contributor
+    int c0 = ((nn - 1) / 32) * 32;
+    float4 a_next = make_float4(0.f, 0.f, -1.f, 0.f);
+    if (c0 + lane < nn) a_next = gA[c0 + lane];
+    for (; c0 >= 0; c0 -= 32) {
+        const float4 a = a_next;
+        const int g = c0 + lane;
+        if (c0 >= 32) a_next = gA[g - 32];
+        const bool ov = (g < nn) && (a.z >= 0.f) && (a.x + a.z >= rx0) && (a.x - a.z <= rx1) && (a.y + a.z >= ry0) &&
+                        (a.y - a.z <= ry1);
+        const unsigned m = __ballot_sync(0xffffffffu, ov);
+        if (m == 0) continue;
+        const int ns = __popc(m);
+        if (ring_head + (uint32_t)ns - ring_free_from > (uint32_t)RING) {
+            drain();
+            ring_free_from = ring_head;
+        }
+        if (ov) {
+            // back to front: the highest list position of the chunk goes first
+            RingRec& r = ring[(ring_head + (uint32_t)(ns - 1 - __popc(m & lt_mask))) % RING];
+            r.A = make_float4(a.x, a.y, __uint_as_float((uint32_t)g), a.w);
+            cp_async_16(&r.B, gBC + 2 * g);
+            cp_async_16(&r.C, gBC + 2 * g + 1);
+        }
+        cp_async_commit();
+        cp_async_wait_all();
+        __syncwarp();
+        for (int s_ = 0; s_ < ns; s_++) {
+            const uint32_t slot = (ring_head + (uint32_t)s_) % RING;
+            const float4 A = ring[slot].A;
+            const float4 con_o = ring[slot].B;
+            const float2 d = {A.x - pixf.x, A.y - pixf.y};
+            const float power = splat_power(con_o, d);
+            if (__float_as_uint(A.z) < last_contributor && !(power > 0.0f) && power >= A.w) {
+                q |= (uint64_t)slot << (8 * cnt);
+                cnt++;
             }
-            if (any) {
-                const uint32_t gid = point_list[range.x + base_pos + tid];
-                float* dst = acc_out + (size_t)gid * ACC_STRIDE;
-#pragma unroll
-                for (int k = 0; k < NACC; k++)
-                    if (v[k] != 0.f) atomicAdd(dst + k, v[k]);
+            if (__ballot_sync(0xffffffffu, cnt == QCAP) != 0) {
+                drain();
+                ring_free_from = ring_head;
             }
         }
-        __syncthreads();
-        if (tid == 0 && i + 2 < nsteps) {
-            int b2 = b - 2;
-            uint32_t bytes = (uint32_t)batch_count(b2) * (uint32_t)sizeof(GaussRec);
-            mbar_expect_tx(&sm.bar[st], bytes);
-            tma_load_1d(&sm.rec[st][0], sorted_rec + range.x + (size_t)b2 * BLEND_BATCH, bytes, &sm.bar[st]);
-        }
+        ring_head += (uint32_t)ns;
+        __syncwarp();
     }
+    drain();
 }
 
-cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* point_list,
-                             const GaussRec* sorted_rec, int W, int H, const float* bg, const float* final_T,
-                             const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t s) {
-    dim3 grid(gx, gy, 1);
-    blend_bwd_kernel<<<grid, 256, 0, s>>>(ranges, point_list, sorted_rec, W, H, bg, final_T, n_contrib, dL_dpix, acc);
+cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC, int W,
+                             int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
+                             const float* dL_dpix, float* acc, cudaStream_t s) {
+    const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
+    blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, 0, s>>>(ranges, sA, sBC, W, H, gx, bg, final_T, n_contrib, dL_dpix,
+                                                         acc);
     return cudaGetLastError();
 }
 

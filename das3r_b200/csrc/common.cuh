@@ -105,9 +105,20 @@ __device__ __forceinline__ void cov3d_from_scale_rot(const float3 scale, float m
     S.m[1][1] = mod * scale.y;
     S.m[2][2] = mod * scale.z;
     float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
-    Mat3 R = mat3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                  2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                  2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    // The products of the rotation matrix are written with explicit rounding/fusion intrinsics: in the reference
+    // source they are plain `a*b +/- c*d` expressions whose FMA contraction is decided by ptxas, and the choice it made
+    // for the reference's preprocessCUDA (sm_100 build, CUDA 12.9: x*z rounded and r*y fused, etc.) is pinned here so
+    // that the tiny off-diagonal covariance entries - and through them conic, radii and tile rectangles - come out
+    // bit-identical no matter how this kernel is scheduled.
+    const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+    const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float xy_m_rz = __fmaf_rn(x, y, -rz), xy_p_rz = __fmaf_rn(x, y, rz);
+    const float xz_p_ry = __fmaf_rn(r, y, xz), xz_m_ry = __fmaf_rn(-r, y, xz);
+    const float yz_m_rx = __fmaf_rn(y, z, -rx), yz_p_rx = __fmaf_rn(y, z, rx);
+    const float yy_zz = __fadd_rn(yy, zz), xx_zz = __fmaf_rn(x, x, zz), xx_yy = __fmaf_rn(x, x, yy);
+    Mat3 R = mat3(__fsub_rn(1.f, __fadd_rn(yy_zz, yy_zz)), __fadd_rn(xy_m_rz, xy_m_rz), __fadd_rn(xz_p_ry, xz_p_ry),
+                  __fadd_rn(xy_p_rz, xy_p_rz), __fsub_rn(1.f, __fadd_rn(xx_zz, xx_zz)), __fadd_rn(yz_m_rx, yz_m_rx),
+                  __fadd_rn(xz_m_ry, xz_m_ry), __fadd_rn(yz_p_rx, yz_p_rx), __fsub_rn(1.f, __fadd_rn(xx_yy, xx_yy)));
     Mat3 M = mul(S, R);
     Mat3 Sigma = mul(transpose(M), M);
     cov3D[0] = Sigma.m[0][0];

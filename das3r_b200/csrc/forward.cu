@@ -14,6 +14,7 @@
 // (tile, depth bits, Gaussian index) and any correct sort on that triple reproduces point_list exactly.
 #include "common.cuh"
 #include "kernels.cuh"
+#include "blend_common.cuh"
 #include <cub/device/device_segmented_radix_sort.cuh>
 #include <stdio.h>
 
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
     float2 point_image = {0.f, 0.f};
     float3 p_orig = {0.f, 0.f, 0.f};
     float3 conic = {0.f, 0.f, 0.f};
-    float depth = 0.f, opacity = 0.f, hx = -1.f, hy = -1.f;
+    float depth = 0.f, opacity = 0.f, hrad = -1.f, negtau = 1.f;
 
     if (idx < a.P) {
         p_orig = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
@@ -145,20 +146,24 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
                     vis = true;
                     depth = p_view.z;
                     opacity = a.opac[idx];
-                    // Conservative half-extent of {alpha >= 1/255}: 0.5*d^T Q d <= tau with tau = ln(255*opacity),
-                    // bounding box of that ellipse = sqrt(2*tau*inv(Q)_xx). Computed in double from the ROUNDED conic
-                    // the blend will use, with a relative and an absolute margin, so a pair skipped by the warp-level
-                    // test is always one the reference would have skipped by `alpha < 1/255` (forward.cu:340).
+                    // A pair can only contribute if alpha = opacity*exp(power) >= 1/255, i.e. power >= -tau with
+                    // tau = ln(255*opacity). tau' = tau*1.0001 + 1e-4 (margin >> expf's error) is stored negated for the
+                    // per-pixel test; h = radius of the bounding box of the ellipse {0.5*d^T Q d <= tau'} (computed in
+                    // double from the ROUNDED conic the blend uses, plus margins) is the warp-level test. A pair skipped
+                    // by either test is always one the reference skips by `alpha < 1/255` (forward.cu:340).
                     float o255 = 255.f * opacity;
                     if (o255 > 1.0f) {
                         double tau = (double)logf(o255) * 1.0001 + 1e-4;
+                        negtau = -(float)(tau * 1.000001);
                         double qa = conic.x, qb = conic.y, qc = conic.z;
                         double qdet = qa * qc - qb * qb;
                         if (qdet > 0.0 && qa > 0.0 && qc > 0.0) {
-                            hx = (float)(sqrt(2.0 * tau * qc / qdet) * 1.0001 + 0.01);
-                            hy = (float)(sqrt(2.0 * tau * qa / qdet) * 1.0001 + 0.01);
+                            double hx = sqrt(2.0 * tau * qc / qdet) * 1.0001 + 0.01;
+                            double hy = sqrt(2.0 * tau * qa / qdet) * 1.0001 + 0.01;
+                            hrad = (float)(fmax(hx, hy) * 1.000001);
                         } else {
-                            hx = hy = 3.0e38f;  // degenerate conic: never cull
+                            hrad = 3.0e38f;  // degenerate conic: never cull at warp level
+                            negtau = -3.0e38f;
                         }
                     }
                 }
@@ -195,7 +200,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
             rgb = {a.colors_precomp[3 * idx], a.colors_precomp[3 * idx + 1], a.colors_precomp[3 * idx + 2]};
         }
         GaussRec r;
-        r.A = make_float4(point_image.x, point_image.y, hx, hy);
+        r.A = make_float4(point_image.x, point_image.y, hrad, negtau);
         r.B = make_float4(conic.x, conic.y, conic.z, opacity);
         r.C = make_float4(rgb.x, rgb.y, rgb.z, depth);
         a.rec[idx] = r;
@@ -310,29 +315,65 @@ cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint3
 // scatter: (Gaussian, tile) pairs into tile buckets. Entry = depth_bits << 32 | gaussian index. The slot order
 // inside a bucket is arbitrary (atomic cursor); the tile sort makes the final order deterministic.
 // ---------------------------------------------------------------------------------------------------------------
+// SMEM: the block first counts its entries per tile in shared memory, reserves one contiguous run per (block, tile)
+// with a single global atomic, then hands out slots with shared-memory atomics. Consecutive Gaussians of a pointmap
+// land in the same few tiles, so this replaces ~R same-address global atomics by a handful per block.
+template <bool SMEM>
 __global__ void __launch_bounds__(256) scatter_kernel(int P, unsigned gx, unsigned gy, const GaussRec* __restrict__ rec,
                                                       const int* __restrict__ radii,
                                                       const uint32_t* __restrict__ tiles_touched,
                                                       uint32_t* __restrict__ cursors,
                                                       uint64_t* __restrict__ unsorted) {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-    if (tiles_touched[idx] == 0) return;
-    float4 A = rec[idx].A;
-    float depth = rec[idx].C.w;
-    uint2 rmin, rmax;
-    tile_rect(make_float2(A.x, A.y), radii[idx], rmin, rmax, gx, gy);
-    uint64_t entry = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
+    extern __shared__ uint32_t s_u32[];
+    const int T = (int)(gx * gy);
+    uint32_t* s_cnt = s_u32;
+    uint32_t* s_base = s_u32 + T;
+    const int tid = threadIdx.x;
+    const int idx = blockIdx.x * blockDim.x + tid;
+    if (SMEM) {
+        for (int i = tid; i < T; i += 256) s_cnt[i] = 0;
+        __syncthreads();
+    }
+    uint2 rmin = {0, 0}, rmax = {0, 0};
+    uint64_t entry = 0;
+    if (idx < P && tiles_touched[idx] != 0) {
+        float4 A = rec[idx].A;
+        float depth = rec[idx].C.w;
+        tile_rect(make_float2(A.x, A.y), radii[idx], rmin, rmax, gx, gy);
+        entry = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
+    }
+    if (!SMEM) {
+        for (unsigned y = rmin.y; y < rmax.y; y++)
+            for (unsigned x = rmin.x; x < rmax.x; x++) {
+                uint32_t slot = atomicAdd(&cursors[y * gx + x], 1u);
+                unsorted[slot] = entry;
+            }
+        return;
+    }
+    for (unsigned y = rmin.y; y < rmax.y; y++)
+        for (unsigned x = rmin.x; x < rmax.x; x++) atomicAdd(&s_cnt[y * gx + x], 1u);
+    __syncthreads();
+    for (int i = tid; i < T; i += 256) {
+        uint32_t c = s_cnt[i];
+        if (c) s_base[i] = atomicAdd(&cursors[i], c);
+        s_cnt[i] = 0;
+    }
+    __syncthreads();
     for (unsigned y = rmin.y; y < rmax.y; y++)
         for (unsigned x = rmin.x; x < rmax.x; x++) {
-            uint32_t slot = atomicAdd(&cursors[y * gx + x], 1u);
+            const unsigned t = y * gx + x;
+            uint32_t slot = s_base[t] + atomicAdd(&s_cnt[t], 1u);
             unsorted[slot] = entry;
         }
 }
 
 cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,
                            const uint32_t* tiles_touched, uint32_t* cursors, uint64_t* unsorted, cudaStream_t s) {
-    scatter_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, rec, radii, tiles_touched, cursors, unsorted);
+    const size_t smem = (size_t)gx * gy * 8;
+    if (smem <= 48 * 1024)
+        scatter_kernel<true><<<(P + 255) / 256, 256, smem, s>>>(P, gx, gy, rec, radii, tiles_touched, cursors, unsorted);
+    else
+        scatter_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, rec, radii, tiles_touched, cursors, unsorted);
     return cudaGetLastError();
 }
 
@@ -421,7 +462,7 @@ template <int MAXE>
 __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
     tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ unsorted,
                      const GaussRec* __restrict__ rec, uint32_t* __restrict__ point_list,
-                     GaussRec* __restrict__ sorted_rec, uint64_t* __restrict__ keys_sorted) {
+                     float4* __restrict__ sA, float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* sm = reinterpret_cast<uint64_t*>(smem_raw);
     const uint32_t tile = blockIdx.x;
@@ -440,7 +481,12 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
         uint64_t key = sm[i];
         uint32_t g = (uint32_t)key;
         point_list[range.x + i] = g;
-        sorted_rec[range.x + i] = rec[g];
+        const GaussRec r = rec[g];
+        // tile-ordered copy, split into the 16-byte stream every warp scans and the 32 bytes only survivors need;
+        // it carries the Gaussian index instead of the depth
+        sA[range.x + i] = r.A;
+        sBC[2 * (size_t)(range.x + i)] = r.B;
+        sBC[2 * (size_t)(range.x + i) + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
         if (keys_sorted) keys_sorted[range.x + i] = ((uint64_t)tile << 32) | (key >> 32);
     }
 }
@@ -449,7 +495,7 @@ int tile_sort_capacity() { return SORT_THREADS * SORT_MAX_E; }
 
 template <int MAXE>
 static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const uint64_t* unsorted, const GaussRec* rec,
-                                            uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted,
+                                            uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                                             cudaStream_t s) {
     const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t);
     if (smem > 48 * 1024) {
@@ -457,27 +503,27 @@ static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const ui
             cudaFuncSetAttribute(tile_sort_kernel<MAXE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
     }
-    tile_sort_kernel<MAXE><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sorted_rec, keys_sorted);
+    tile_sort_kernel<MAXE><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sA, sBC, keys_sorted);
     return cudaGetLastError();
 }
 
 cudaError_t launch_tile_sort(int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
-                             const GaussRec* rec, uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted,
+                             const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                              cudaStream_t s) {
     if (max_count > (uint32_t)tile_sort_capacity()) return cudaErrorInvalidValue;
     if (max_count <= SORT_THREADS * 4)
-        return launch_tile_sort_variant<4>(T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, s);
+        return launch_tile_sort_variant<4>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
     if (max_count <= SORT_THREADS * 8)
-        return launch_tile_sort_variant<8>(T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, s);
-    return launch_tile_sort_variant<32>(T, ranges, unsorted, rec, point_list, sorted_rec, keys_sorted, s);
+        return launch_tile_sort_variant<8>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    return launch_tile_sort_variant<32>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
 }
 
 // Fallback for tiles larger than the in-shared-memory capacity: library segmented radix sort of the
 // (depth|index) entries, segment = tile, then the same gather.
 __global__ void gather_sorted_kernel(int R, int T, const uint2* __restrict__ ranges,
                                      const uint64_t* __restrict__ sorted_entries, const GaussRec* __restrict__ rec,
-                                     uint32_t* __restrict__ point_list, GaussRec* __restrict__ sorted_rec,
-                                     uint64_t* __restrict__ keys_sorted) {
+                                     uint32_t* __restrict__ point_list, float4* __restrict__ sA,
+                                     float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
     // one block per tile so the tile id is known without a search
     const uint32_t tile = blockIdx.x;
     const uint2 range = ranges[tile];
@@ -485,7 +531,10 @@ __global__ void gather_sorted_kernel(int R, int T, const uint2* __restrict__ ran
         uint64_t key = sorted_entries[i];
         uint32_t g = (uint32_t)key;
         point_list[i] = g;
-        sorted_rec[i] = rec[g];
+        const GaussRec r = rec[g];
+        sA[i] = r.A;
+        sBC[2 * (size_t)i] = r.B;
+        sBC[2 * (size_t)i + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
         if (keys_sorted) keys_sorted[i] = ((uint64_t)tile << 32) | (key >> 32);
     }
 }
@@ -509,7 +558,7 @@ size_t tile_sort_fallback_bytes(int R, int T) {
 }
 
 cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
-                                      uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted, void* temp,
+                                      uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted, void* temp,
                                       size_t temp_bytes, cudaStream_t s) {
     char* p = static_cast<char*>(temp);
     uint64_t* sorted_entries = reinterpret_cast<uint64_t*>(p);
@@ -523,144 +572,157 @@ cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_
     cudaError_t e = cub::DeviceSegmentedRadixSort::SortKeys(p, cub_bytes, unsorted, sorted_entries, R, T, beg, end, 0,
                                                             64, s);
     if (e != cudaSuccess) return e;
-    gather_sorted_kernel<<<T, 256, 0, s>>>(R, T, ranges, sorted_entries, rec, point_list, sorted_rec, keys_sorted);
+    gather_sorted_kernel<<<T, 256, 0, s>>>(R, T, ranges, sorted_entries, rec, point_list, sA, sBC, keys_sorted);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// blend_fwd: one block per 16x16 tile, 8 warps, each warp owns an 8x4 pixel rectangle. Batches of 256 tile-ordered
-// records are staged by one TMA bulk copy per batch (double buffered, mbarrier completion). Each warp first tests
-// 32 Gaussians at a time (one per lane) against its rectangle with the conservative extent, then walks only the
-// survivors in list order, so the front-to-back recurrence and `n_contrib` are identical to the reference
-// (forward.cu:306-361) while most (pixel, Gaussian) pairs are never evaluated.
+// blend_fwd. Every warp owns one 8x4 pixel rectangle of one tile (one lane per pixel) and streams through the tile's
+// depth-sorted list on its own - no block-level barrier anywhere, so a warp never waits for a neighbour whose pixels
+// happen to see more Gaussians (depth order correlates with screen position, which made lock-step batches lopsided).
+// The list is walked in three levels so that the expensive part only runs on pairs that contribute:
+//   1. warp level: 32 list entries at a time, one per lane, read with one coalesced 512-byte load of the compact
+//      {x, y, h, -tau'} stream (next chunk prefetched in registers), are tested against the warp's rectangle with the
+//      conservative radius h -> ballot. Survivors' remaining 32 bytes are fetched by their own lanes and the records
+//      are compacted, in list order, into a per-warp shared-memory ring;
+//   2. lane level ("scan"): for each survivor every lane evaluates only the quadratic form `power` (bit-identical
+//      to the reference expression) and keeps the ring slot iff power >= -tau', i.e. iff alpha >= 1/255 is possible
+//      (tau' = ln(255*opacity) with a safety margin): a pair rejected here is one the reference skips at forward.cu:340;
+//   3. lane level ("drain"): kept slots sit in an 8-entry per-lane register queue and are blended, in list order, by
+//      all lanes in lockstep - exp, alpha clamp, transmittance test and colour accumulation exactly as forward.cu:330-361.
+// The front-to-back recurrence per pixel, `n_contrib` (list positions) and the early termination are unchanged.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int BLEND_BATCH = 256;
-
-struct BlendSmem {
-    GaussRec rec[2][BLEND_BATCH];
-    uint64_t bar[2];
-};
-
-__global__ void __launch_bounds__(256) blend_fwd_kernel(const uint2* __restrict__ ranges,
-                                                        const GaussRec* __restrict__ sorted_rec, int W, int H,
-                                                        const float* __restrict__ bg, float* __restrict__ final_T,
-                                                        uint32_t* __restrict__ n_contrib,
-                                                        float* __restrict__ out_color, float* __restrict__ out_depth,
-                                                        float* __restrict__ out_alpha) {
-    __shared__ __align__(128) BlendSmem sm;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+template <bool EXTRAS>
+__global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
+    const uint2* __restrict__ ranges, const float4* __restrict__ sA, const float4* __restrict__ sBC,
+    const GaussRec* __restrict__ rec_by_id, int W, int H, unsigned gx, const float* __restrict__ bg,
+    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+    float* __restrict__ out_depth, float* __restrict__ out_alpha) {
+    __shared__ __align__(16) RingRec ring_all[BLEND_WARPS][RING];
+    const int lane = threadIdx.x & 31;
+    RingRec* ring = ring_all[threadIdx.x >> 5];
+    const WarpRect wr = warp_rect(W, H, gx);
+    const uint2 range = ranges[wr.tile];
     const int n = (int)(range.y - range.x);
-    const int nb = (n + BLEND_BATCH - 1) / BLEND_BATCH;
+    const float2 pixf = {(float)wr.px, (float)wr.py};
+    const float rx0 = (float)wr.wx0, rx1 = (float)(wr.wx0 + 7), ry0 = (float)wr.wy0, ry1 = (float)(wr.wy0 + 3);
+    const unsigned lt_mask = (1u << lane) - 1u;
 
-    const int wx0 = blockIdx.x * TILE_X + (warp & 1) * 8;
-    const int wy0 = blockIdx.y * TILE_Y + (warp >> 1) * 4;
-    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
-    const bool inside = px < W && py < H;
-    const float2 pixf = {(float)px, (float)py};
-    const float rx0 = (float)wx0, rx1 = (float)(wx0 + 7), ry0 = (float)wy0, ry1 = (float)(wy0 + 3);
-
-    if (tid == 0) {
-        mbar_init(&sm.bar[0], 1);
-        mbar_init(&sm.bar[1], 1);
-        mbar_fence_init();
-    }
-    __syncthreads();
-    if (tid == 0) {
-        for (int b = 0; b < min(nb, 2); b++) {
-            uint32_t cnt = (uint32_t)min(BLEND_BATCH, n - b * BLEND_BATCH);
-            mbar_expect_tx(&sm.bar[b], cnt * (uint32_t)sizeof(GaussRec));
-            tma_load_1d(&sm.rec[b][0], sorted_rec + range.x + (size_t)b * BLEND_BATCH, cnt * (uint32_t)sizeof(GaussRec),
-                        &sm.bar[b]);
-        }
-    }
-
-    bool done = !inside;
+    bool done = !wr.inside;
     float T = 1.0f;
     uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     float Dz = 0.f;
+    uint64_t q = 0;  // up to QCAP ring slots, 8 bits each, oldest in the low byte
+    int cnt = 0;
+    uint32_t ring_head = 0, ring_free_from = 0;  // slots [ring_free_from, ring_head) may still be queued
 
-    for (int b = 0; b < nb; b++) {
-        const int st = b & 1;
-        const int cnt = min(BLEND_BATCH, n - b * BLEND_BATCH);
-        mbar_wait(&sm.bar[st], (uint32_t)((b >> 1) & 1));
-        const GaussRec* rec = sm.rec[st];
-        if (__ballot_sync(0xffffffffu, !done) != 0) {
-            for (int c0 = 0; c0 < cnt; c0 += 32) {
-                const int g = c0 + lane;
-                bool ov = false;
-                if (g < cnt) {
-                    float4 A = rec[g].A;
-                    ov = (A.z >= 0.f) && (A.x + A.z >= rx0) && (A.x - A.z <= rx1) && (A.y + A.w >= ry0) &&
-                         (A.y - A.w <= ry1);
-                }
-                unsigned m = __ballot_sync(0xffffffffu, ov);
-                while (m) {
-                    const int j = __ffs(m) - 1;
-                    m &= m - 1;
-                    const int gi = c0 + j;
-                    if (!done) {
-                        // forward.cu:330-361
-                        const float4 A = rec[gi].A;
-                        const float4 con_o = rec[gi].B;
-                        float2 d = {A.x - pixf.x, A.y - pixf.y};
-                        float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-                        if (!(power > 0.0f)) {
-                            float alpha = min(0.99f, con_o.w * expf(power));
-                            if (alpha >= 1.0f / 255.0f) {
-                                float test_T = T * (1 - alpha);
-                                if (test_T < 0.0001f) {
-                                    done = true;
-                                } else {
-                                    const float4 col = rec[gi].C;
-                                    C[0] += col.x * alpha * T;
-                                    C[1] += col.y * alpha * T;
-                                    C[2] += col.z * alpha * T;
-                                    Dz += col.w * alpha * T;
-                                    T = test_T;
-                                    last_contributor = (uint32_t)(b * BLEND_BATCH + gi + 1);
-                                }
-                            }
+    auto drain = [&]() {
+#pragma unroll 1
+        for (int i = 0; i < QCAP; i++) {
+            if (__ballot_sync(0xffffffffu, i < cnt) == 0) break;
+            if (i < cnt && !done) {
+                const RingRec& r = ring[(uint32_t)(q >> (8 * i)) & 0xffu];
+                const float4 A = r.A;
+                const float4 con_o = r.B;
+                const float2 d = {A.x - pixf.x, A.y - pixf.y};
+                const float power = splat_power(con_o, d);
+                // forward.cu:339-361 (power <= 0 is guaranteed by the scan)
+                const float alpha = min(0.99f, __fmul_rn(con_o.w, expf(power)));
+                if (!(alpha < 1.0f / 255.0f)) {
+                    const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+                    if (test_T < 0.0001f) {
+                        done = true;
+                    } else {
+                        const float4 col = r.C;
+                        C[0] = __fmaf_rn(T, __fmul_rn(col.x, alpha), C[0]);
+                        C[1] = __fmaf_rn(T, __fmul_rn(col.y, alpha), C[1]);
+                        C[2] = __fmaf_rn(T, __fmul_rn(col.z, alpha), C[2]);
+                        if (EXTRAS) {
+                            const float z = rec_by_id[__float_as_uint(col.w)].C.w;
+                            Dz = __fmaf_rn(T, __fmul_rn(z, alpha), Dz);
                         }
+                        T = test_T;
+                        last_contributor = __float_as_uint(A.z) + 1u;
                     }
                 }
-                if (__ballot_sync(0xffffffffu, !done) == 0) break;
             }
         }
-        // All threads are finished with this stage; refill it with batch b+2 (or stop if every pixel is done,
-        // forward.cu:309-311).
-        int num_done = __syncthreads_count(done);
-        if (num_done == TILE_PIX) {
-            // a bulk copy for batch b+1 may still be in flight: it must land before this block's shared memory is freed
-            if (b + 1 < nb) mbar_wait(&sm.bar[st ^ 1], (uint32_t)(((b + 1) >> 1) & 1));
-            break;
-        }
-        if (tid == 0 && b + 2 < nb) {
-            uint32_t cnt2 = (uint32_t)min(BLEND_BATCH, n - (b + 2) * BLEND_BATCH);
-            mbar_expect_tx(&sm.bar[st], cnt2 * (uint32_t)sizeof(GaussRec));
-            tma_load_1d(&sm.rec[st][0], sorted_rec + range.x + (size_t)(b + 2) * BLEND_BATCH,
-                        cnt2 * (uint32_t)sizeof(GaussRec), &sm.bar[st]);
-        }
-    }
+        q = 0;
+        cnt = 0;
+    };
 
-    if (inside) {
-        const int pix_id = W * py + px;
+    const float4* gA = sA + range.x;
+    const float4* gBC = sBC + 2 * (size_t)range.x;
+    float4 a_next = make_float4(0.f, 0.f, -1.f, 0.f);
+    if (lane < n) a_next = gA[lane];
+    for (int c0 = 0; c0 < n; c0 += 32) {
+        const float4 a = a_next;
+        const int g = c0 + lane;
+        if (g + 32 < n) a_next = gA[g + 32];
+        const bool ov = (g < n) && (a.z >= 0.f) && (a.x + a.z >= rx0) && (a.x - a.z <= rx1) && (a.y + a.z >= ry0) &&
+                        (a.y - a.z <= ry1);
+        const unsigned m = __ballot_sync(0xffffffffu, ov);
+        if (m == 0) continue;
+        const int ns = __popc(m);
+        if (ring_head + (uint32_t)ns - ring_free_from > (uint32_t)RING) {
+            drain();  // frees every slot written before this chunk
+            ring_free_from = ring_head;
+        }
+        if (ov) {
+            RingRec& r = ring[(ring_head + __popc(m & lt_mask)) % RING];
+            r.A = make_float4(a.x, a.y, __uint_as_float((uint32_t)g), a.w);
+            cp_async_16(&r.B, gBC + 2 * g);  // LDGSTS: global -> ring without a register round trip
+            cp_async_16(&r.C, gBC + 2 * g + 1);
+        }
+        cp_async_commit();
+        cp_async_wait_all();
+        __syncwarp();
+        for (int s = 0; s < ns; s++) {
+            const uint32_t slot = (ring_head + (uint32_t)s) % RING;
+            const float4 A = ring[slot].A;
+            const float4 con_o = ring[slot].B;
+            const float2 d = {A.x - pixf.x, A.y - pixf.y};
+            const float power = splat_power(con_o, d);
+            if (!done && !(power > 0.0f) && power >= A.w) {
+                q |= (uint64_t)slot << (8 * cnt);
+                cnt++;
+            }
+            if (__ballot_sync(0xffffffffu, cnt == QCAP) != 0) {
+                drain();
+                ring_free_from = ring_head;  // this chunk's slots stay live
+            }
+        }
+        ring_head += (uint32_t)ns;
+        if (__ballot_sync(0xffffffffu, !done) == 0) break;  // forward.cu:309-311, per warp
+        __syncwarp();
+    }
+    drain();
+
+    if (wr.inside) {
+        const int pix_id = W * wr.py + wr.px;
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
 #pragma unroll
-        for (int ch = 0; ch < 3; ch++) out_color[ch * H * W + pix_id] = C[ch] + T * bg[ch];
-        if (out_depth) out_depth[pix_id] = Dz;
-        if (out_alpha) out_alpha[pix_id] = 1.0f - T;
+        for (int ch = 0; ch < 3; ch++) out_color[ch * H * W + pix_id] = __fmaf_rn(T, bg[ch], C[ch]);
+        if (EXTRAS) {
+            if (out_depth) out_depth[pix_id] = Dz;
+            if (out_alpha) out_alpha[pix_id] = 1.0f - T;
+        }
     }
 }
 
-cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const GaussRec* sorted_rec, int W, int H,
-                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
-                             float* out_alpha, cudaStream_t s) {
-    dim3 grid(gx, gy, 1);
-    blend_fwd_kernel<<<grid, 256, 0, s>>>(ranges, sorted_rec, W, H, bg, final_T, n_contrib, out_color, out_depth,
-                                          out_alpha);
+cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC,
+                             const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
+                             uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
+                             cudaStream_t s) {
+    const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
+    if (out_depth || out_alpha)
+        blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, 0, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
+                                                                   n_contrib, out_color, out_depth, out_alpha);
+    else
+        blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, 0, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
+                                                                    n_contrib, out_color, out_depth, out_alpha);
     return cudaGetLastError();
 }
 

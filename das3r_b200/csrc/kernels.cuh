@@ -12,9 +12,12 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 
 // Per-Gaussian record, 48 bytes, written by the forward preprocess and gathered (in tile/depth order) by the tile
 // sort so that the blend kernels can stage contiguous batches with one TMA bulk copy.
-//   A = {x, y, hx, hy}      pixel-space mean and a conservative half-extent of the alpha >= 1/255 region
+//   A = {x, y, h, -tau'}    pixel-space mean; h = conservative radius of the region where alpha >= 1/255 is possible
+//                           (< 0: never), tau' = ln(255*opacity) with a margin: a pixel can contribute iff power >= -tau'
 //   B = {conic a, b, c, opacity}   (reference: conic_opacity, forward.cu:253)
 //   C = {r, g, b, depth}
+// The tile-ordered copy is split into two streams: sA[R] = A (the 16 bytes every warp scans) and sBC[R][2] = {B, C'}
+// with C'.w = Gaussian index (as bits) instead of the depth.
 struct __align__(16) GaussRec {
     float4 A, B, C;
 };
@@ -60,22 +63,22 @@ cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec,
 // (the caller then uses the segmented fallback).
 int tile_sort_capacity();
 cudaError_t launch_tile_sort(int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
-                             const GaussRec* rec, uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted,
+                             const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                              cudaStream_t s);
 // Fallback for tiles beyond the shared-memory capacity: library segmented radix sort + gather.
 size_t tile_sort_fallback_bytes(int R, int T);
 cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
-                                      uint32_t* point_list, GaussRec* sorted_rec, uint64_t* keys_sorted, void* temp,
+                                      uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted, void* temp,
                                       size_t temp_bytes, cudaStream_t s);
-cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const GaussRec* sorted_rec, int W, int H,
-                             const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
-                             float* out_alpha, cudaStream_t s);
+cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC,
+                             const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
+                             uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
+                             cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means, const float* view, const float* proj, uint8_t* present,
                                 cudaStream_t s);
 
 // backward.cu
-cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* point_list,
-                             const GaussRec* sorted_rec, int W, int H, const float* bg, const float* final_T,
+cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC, int W, int H, const float* bg, const float* final_T,
                              const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t s);
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
 

@@ -149,7 +149,7 @@ int das3r_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scr
  * reference's GeometryState/BinningState/ImageState (rasterizer_impl.cu:155-194). No reference counterpart. */
 typedef struct das3r_raster_state_layout {
     /* geom blob (P-sized) */
-    size_t g_recA, g_recB, g_recC;   /* float4[P]: {x,y,hx,hy} {conic a,b,c,opacity} {r,g,b,depth} */
+    size_t g_recA, g_recB, g_recC;   /* 48-byte records [P]: {x,y,h,-tau'} {conic a,b,c,opacity} {r,g,b,depth} */
     size_t g_tiles_touched;          /* uint32[P] */
     size_t g_clamped;                /* uint8[P], bit c = channel c clamped */
     size_t geom_bytes;
@@ -163,7 +163,8 @@ typedef struct das3r_raster_state_layout {
     size_t b_unsorted;               /* uint64[R]: depth_bits<<32 | gaussian index, tile-bucketed */
     size_t b_point_list;             /* uint32[R] sorted */
     size_t b_keys_sorted;            /* uint64[R] tile<<32|depth_bits, written only when params.debug != 0 */
-    size_t b_sA, b_sB, b_sC;         /* float4[R] tile-ordered records */
+    size_t b_sA;                     /* float4[R] tile-ordered {x, y, h, -tau'} */
+    size_t b_sB, b_sC;               /* float4[R][2] tile-ordered, interleaved {conic, opacity} {rgb, gaussian index} */
     size_t binning_bytes;
 } das3r_raster_state_layout;
 int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,

@@ -9,13 +9,16 @@
  * Parity pin: the reference ships no tests, golden vectors or fixtures for this path, so this port is
  * pinned against outputs of the reference CUDA code itself (oracle/_ref, built by oracle/build_ref.sh from
  * /root/reference and run on the GPU box; vectors committed under tests/golden/ with tests/golden/make_golden.py).
- * Integer outputs can differ from the CUDA reference on the rare Gaussian that sits within an ulp of a rounding
- * threshold, because gcc's and nvcc's FMA contraction differ; the golden tests state the tolerated count.
+ * Integer outputs could still differ from the CUDA reference on a Gaussian that sits within an ulp of a rounding
+ * threshold if a contraction was missed here; the golden tests state the tolerated count (0 on the committed vectors).
  *
  * Each function cites the reference lines it follows (paths relative to
  * /root/reference/submodules/diff-gaussian-rasterization/ unless noted).
  *
- * Build: gcc -O2 -fopenmp -mfma -ffp-contract=fast -shared -fPIC raster_oracle.c -o _build/liboracle.so -lm
+ * Build: gcc -O2 -fopenmp -mfma -ffp-contract=off -shared -fPIC raster_oracle.c -o _build/liboracle.so -lm
+ * (contraction off: where the reference's sm_100 build fuses a multiply-add on the chain that decides the integer
+ * outputs - transforms, covariance, determinant, radius - the fusion is spelled out with fmaf(); everything else is
+ * evaluated unfused, which stays far inside the float tolerances)
  */
 #include <math.h>
 #include <stdint.h>
@@ -46,7 +49,8 @@ static mat3 mat3_mul(const mat3* A, const mat3* B) {
     mat3 R;
     for (int c = 0; c < 3; c++)
         for (int r = 0; r < 3; r++)
-            R.m[c][r] = A->m[0][r] * B->m[c][0] + A->m[1][r] * B->m[c][1] + A->m[2][r] * B->m[c][2];
+            /* a*b + c*d + e*f as nvcc contracts it: the middle product is rounded, the outer two are fused */
+            R.m[c][r] = fmaf(A->m[2][r], B->m[c][2], fmaf(A->m[0][r], B->m[c][0], A->m[1][r] * B->m[c][1]));
     return R;
 }
 static mat3 mat3_T(const mat3* A) {
@@ -56,17 +60,21 @@ static mat3 mat3_T(const mat3* A) {
     return R;
 }
 /* auxiliary.h:58-66 */
+static float dot3p(float a0, float b0, float a1, float b1, float a2, float b2, float c) {
+    /* a0*b0 + a1*b1 + a2*b2 + c as compiled for the reference: fma(a2,b2, fma(a0,b0, a1*b1)) + c */
+    return fmaf(a2, b2, fmaf(a0, b0, a1 * b1)) + c;
+}
 static f3 xform43(f3 p, const float* m) {
-    f3 t = {m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
-            m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14]};
+    f3 t = {dot3p(m[0], p.x, m[4], p.y, m[8], p.z, m[12]), dot3p(m[1], p.x, m[5], p.y, m[9], p.z, m[13]),
+            dot3p(m[2], p.x, m[6], p.y, m[10], p.z, m[14])};
     return t;
 }
 /* auxiliary.h:68-77 */
 static void xform44(f3 p, const float* m, float o[4]) {
-    o[0] = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
-    o[1] = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
-    o[2] = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
-    o[3] = m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15];
+    o[0] = dot3p(m[0], p.x, m[4], p.y, m[8], p.z, m[12]);
+    o[1] = dot3p(m[1], p.x, m[5], p.y, m[9], p.z, m[13]);
+    o[2] = dot3p(m[2], p.x, m[6], p.y, m[10], p.z, m[14]);
+    o[3] = dot3p(m[3], p.x, m[7], p.y, m[11], p.z, m[15]);
 }
 /* auxiliary.h:89-97 */
 static f3 xformvec43T(f3 p, const float* m) {
@@ -95,9 +103,17 @@ static void computeCov3D(f3 scale, float mod, const float rot[4], float* cov3D) 
     S.m[1][1] = mod * scale.y;
     S.m[2][2] = mod * scale.z;
     float r = rot[0], x = rot[1], y = rot[2], z = rot[3]; /* NOT normalised, forward.cu:127 */
-    mat3 R = mat3_make(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                       2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                       2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    /* forward.cu:134-138. The `a*b +/- c*d` products are spelled with fmaf() the way ptxas contracted them in the
+     * reference's sm_100 build (x*z, r*x, r*z, y*y, z*z rounded; the partner product fused), so the tiny off-diagonal
+     * covariance entries match the CUDA reference bit for bit. */
+    const float xz = x * z, rx = r * x, rz = r * z, yy = y * y, zz = z * z;
+    const float xy_m_rz = fmaf(x, y, -rz), xy_p_rz = fmaf(x, y, rz);
+    const float xz_p_ry = fmaf(r, y, xz), xz_m_ry = fmaf(-r, y, xz);
+    const float yz_m_rx = fmaf(y, z, -rx), yz_p_rx = fmaf(y, z, rx);
+    const float yy_zz = yy + zz, xx_zz = fmaf(x, x, zz), xx_yy = fmaf(x, x, yy);
+    mat3 R = mat3_make(1.f - (yy_zz + yy_zz), xy_m_rz + xy_m_rz, xz_p_ry + xz_p_ry,
+                       xy_p_rz + xy_p_rz, 1.f - (xx_zz + xx_zz), yz_m_rx + yz_m_rx,
+                       xz_m_ry + xz_m_ry, yz_p_rx + yz_p_rx, 1.f - (xx_yy + xx_yy));
     mat3 M = mat3_mul(&S, &R);
     mat3 Mt = mat3_T(&M);
     mat3 Sigma = mat3_mul(&Mt, &M);
@@ -203,13 +219,13 @@ void oracle_preprocess(int P, int D, int M, const float* means, const float* sca
         }
         ewa_t e = ewa(p_orig, focal_x, focal_y, tan_fovx, tan_fovy, cov3D, view);
         float cx = e.a, cy = e.b, cz = e.c;
-        float det = (cx * cz - cy * cy);
+        float det = fmaf(cx, cz, -(cy * cy)); /* FFMA(cov.x, cov.z, -(cov.y*cov.y)) in the reference build */
         if (det == 0.0f) continue;
         float det_inv = 1.f / det;
         float conic[3] = {cz * det_inv, -cy * det_inv, cx * det_inv};
         float mid = 0.5f * (cx + cz);
-        float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
-        float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
+        float lambda1 = mid + sqrtf(fmaxf(0.1f, fmaf(mid, mid, -det)));
+        float lambda2 = mid - sqrtf(fmaxf(0.1f, fmaf(mid, mid, -det)));
         float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
         float pix = ndc2Pix(p_proj.x, W), piy = ndc2Pix(p_proj.y, H);
         int rmin[2], rmax[2];
