@@ -9,6 +9,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "blend_common.cuh"
+#include <stdlib.h>
 
 namespace das3r {
 
@@ -166,8 +167,10 @@ cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, cons
                              int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
                              const float* dL_dpix, float* acc, cudaStream_t s) {
     const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, 0, s>>>(ranges, sA, sBC, W, H, gx, bg, final_T, n_contrib, dL_dpix,
-                                                         acc);
+    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)blocks, 32 * BLEND_WARPS,
+                                       sizeof(RingRec) * BLEND_WARPS * RING);
+    blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, sA, sBC, W, H, gx, bg, final_T, n_contrib, dL_dpix,
+                                                           acc);
     return cudaGetLastError();
 }
 
@@ -184,89 +187,76 @@ __device__ __forceinline__ float3 dnormvdv3(float3 v, float3 dv) {  // auxiliary
     return r;
 }
 
-struct V3 {
-    float x, y, z;
-};
-__device__ __forceinline__ V3 operator*(float s, V3 v) { return {s * v.x, s * v.y, s * v.z}; }
-__device__ __forceinline__ V3 operator*(V3 v, float s) { return {v.x * s, v.y * s, v.z * s}; }
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
-__device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
-__device__ __forceinline__ V3& operator+=(V3& a, V3 b) {
-    a.x += b.x; a.y += b.y; a.z += b.z;
-    return a;
-}
-__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-
-// SH backward (backward.cu:20-139). sh[k] / out[k] are rows of 3 floats. Writes the first (deg+1)^2 rows of `out`
-// (the caller zero-fills the rest) and returns the view-direction part of dL_dmean.
-__device__ __forceinline__ float3 sh_backward(int deg, const float* f, float3 pos, float3 campos, uint8_t clamped,
-                                              float3 dL_dcolor, float* out) {
+// SH backward (backward.cu:20-139), restated per coefficient so that nothing but three running sums has to stay live:
+//   dL_dsh[k] = B_k(dir) * dL_dRGB            (B_k = the k-th real SH basis function, as in the forward)
+//   dL_ddir   = sum_k grad(B_k)(dir) * (sh[k] . dL_dRGB)
+// which is the reference's dRGBdx/dRGBdy/dRGBdz contraction with the sums over channels and coefficients swapped.
+// `get(k)` returns sh[k] as float3, `put(k, v)` stores dL_dsh[k]. Returns the view-direction part of dL_dmean.
+template <typename Get, typename Put>
+__device__ __forceinline__ float3 sh_backward(int deg, float3 pos, float3 campos, uint8_t clamped, float3 dL_dcolor,
+                                              Get get, Put put) {
     float3 dir_orig = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
     float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
-    float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
-    V3 dL_dRGB = {dL_dcolor.x, dL_dcolor.y, dL_dcolor.z};
-    dL_dRGB.x *= (clamped & 1) ? 0 : 1;
-    dL_dRGB.y *= (clamped & 2) ? 0 : 1;
-    dL_dRGB.z *= (clamped & 4) ? 0 : 1;
-    auto sh = [&](int k) -> V3 { return {f[3 * k], f[3 * k + 1], f[3 * k + 2]}; };
-    auto put = [&](int k, float w) {
-        out[3 * k] = w * dL_dRGB.x;
-        out[3 * k + 1] = w * dL_dRGB.y;
-        out[3 * k + 2] = w * dL_dRGB.z;
+    const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+    // PyTorch clamping rule: a clamped channel passes no gradient (backward.cu:31-34)
+    const float3 g = {(clamped & 1) ? 0.f : dL_dcolor.x, (clamped & 2) ? 0.f : dL_dcolor.y,
+                      (clamped & 4) ? 0.f : dL_dcolor.z};
+    float3 dd = {0.f, 0.f, 0.f};
+    auto term = [&](int k, float B, float bx, float by, float bz) {
+        const float3 c = get(k);
+        const float sdot = c.x * g.x + c.y * g.y + c.z * g.z;
+        dd.x += bx * sdot;
+        dd.y += by * sdot;
+        dd.z += bz * sdot;
+        put(k, make_float3(B * g.x, B * g.y, B * g.z));
     };
-    V3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
-    put(0, kSH0);
+    put(0, make_float3(kSH0 * g.x, kSH0 * g.y, kSH0 * g.z));
     if (deg > 0) {
-        put(1, -kSH1 * y);
-        put(2, kSH1 * z);
-        put(3, -kSH1 * x);
-        dRGBdx = -kSH1 * sh(3);
-        dRGBdy = -kSH1 * sh(1);
-        dRGBdz = kSH1 * sh(2);
+        term(1, -kSH1 * y, 0.f, -kSH1, 0.f);
+        term(2, kSH1 * z, 0.f, 0.f, kSH1);
+        term(3, -kSH1 * x, -kSH1, 0.f, 0.f);
         if (deg > 1) {
-            float xx = x * x, yy = y * y, zz = z * z;
-            float xy = x * y, yz = y * z, xz = x * z;
-            put(4, kSH2[0] * xy);
-            put(5, kSH2[1] * yz);
-            put(6, kSH2[2] * (2.f * zz - xx - yy));
-            put(7, kSH2[3] * xz);
-            put(8, kSH2[4] * (xx - yy));
-            dRGBdx += kSH2[0] * y * sh(4) + kSH2[2] * 2.f * -x * sh(6) + kSH2[3] * z * sh(7) + kSH2[4] * 2.f * x * sh(8);
-            dRGBdy += kSH2[0] * x * sh(4) + kSH2[1] * z * sh(5) + kSH2[2] * 2.f * -y * sh(6) + kSH2[4] * 2.f * -y * sh(8);
-            dRGBdz += kSH2[1] * y * sh(5) + kSH2[2] * 2.f * 2.f * z * sh(6) + kSH2[3] * x * sh(7);
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            term(4, kSH2[0] * xy, kSH2[0] * y, kSH2[0] * x, 0.f);
+            term(5, kSH2[1] * yz, 0.f, kSH2[1] * z, kSH2[1] * y);
+            term(6, kSH2[2] * (2.f * zz - xx - yy), kSH2[2] * -2.f * x, kSH2[2] * -2.f * y, kSH2[2] * 4.f * z);
+            term(7, kSH2[3] * xz, kSH2[3] * z, 0.f, kSH2[3] * x);
+            term(8, kSH2[4] * (xx - yy), kSH2[4] * 2.f * x, kSH2[4] * -2.f * y, 0.f);
             if (deg > 2) {
-                put(9, kSH3[0] * y * (3.f * xx - yy));
-                put(10, kSH3[1] * xy * z);
-                put(11, kSH3[2] * y * (4.f * zz - xx - yy));
-                put(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-                put(13, kSH3[4] * x * (4.f * zz - xx - yy));
-                put(14, kSH3[5] * z * (xx - yy));
-                put(15, kSH3[6] * x * (xx - 3.f * yy));
-                dRGBdx += (kSH3[0] * sh(9) * 3.f * 2.f * xy + kSH3[1] * sh(10) * yz + kSH3[2] * sh(11) * -2.f * xy +
-                           kSH3[3] * sh(12) * -3.f * 2.f * xz + kSH3[4] * sh(13) * (-3.f * xx + 4.f * zz - yy) +
-                           kSH3[5] * sh(14) * 2.f * xz + kSH3[6] * sh(15) * 3.f * (xx - yy));
-                dRGBdy += (kSH3[0] * sh(9) * 3.f * (xx - yy) + kSH3[1] * sh(10) * xz +
-                           kSH3[2] * sh(11) * (-3.f * yy + 4.f * zz - xx) + kSH3[3] * sh(12) * -3.f * 2.f * yz +
-                           kSH3[4] * sh(13) * -2.f * xy + kSH3[5] * sh(14) * -2.f * yz +
-                           kSH3[6] * sh(15) * -3.f * 2.f * xy);
-                dRGBdz += (kSH3[1] * sh(10) * xy + kSH3[2] * sh(11) * 4.f * 2.f * yz +
-                           kSH3[3] * sh(12) * 3.f * (2.f * zz - xx - yy) + kSH3[4] * sh(13) * 4.f * 2.f * xz +
-                           kSH3[5] * sh(14) * (xx - yy));
+                term(9, kSH3[0] * y * (3.f * xx - yy), kSH3[0] * 6.f * xy, kSH3[0] * 3.f * (xx - yy), 0.f);
+                term(10, kSH3[1] * xy * z, kSH3[1] * yz, kSH3[1] * xz, kSH3[1] * xy);
+                term(11, kSH3[2] * y * (4.f * zz - xx - yy), kSH3[2] * -2.f * xy,
+                     kSH3[2] * (4.f * zz - xx - 3.f * yy), kSH3[2] * 8.f * yz);
+                term(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy), kSH3[3] * -6.f * xz, kSH3[3] * -6.f * yz,
+                     kSH3[3] * 3.f * (2.f * zz - xx - yy));
+                term(13, kSH3[4] * x * (4.f * zz - xx - yy), kSH3[4] * (4.f * zz - 3.f * xx - yy),
+                     kSH3[4] * -2.f * xy, kSH3[4] * 8.f * xz);
+                term(14, kSH3[5] * z * (xx - yy), kSH3[5] * 2.f * xz, kSH3[5] * -2.f * yz, kSH3[5] * (xx - yy));
+                term(15, kSH3[6] * x * (xx - 3.f * yy), kSH3[6] * 3.f * (xx - yy), kSH3[6] * -6.f * xy, 0.f);
             }
         }
     }
-    float3 dL_ddir = {dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB)};
-    return dnormvdv3(dir_orig, dL_ddir);
+    return dnormvdv3(dir_orig, dd);
 }
 
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
-    const int nsh = 3 * a.M;  // floats per dL_dsh row
-    float* sh_out = a.dL_dsh ? a.dL_dsh + (size_t)idx * nsh : nullptr;
-    const bool sh_aligned = ((a.M & 3) == 0);
+constexpr int PB_THREADS = 256;
+constexpr int PB_ROW_F4 = 12;      // a degree-3 SH row: 48 floats
+constexpr int PB_ROW_PAD_F4 = 13;  // padded pitch in shared memory (odd number of float4: conflict-free LDS/STS.128)
 
+// STAGE (degree 3, M == 16): the block's 256 SH rows are brought into shared memory with coalesced 16-byte cp.async
+// while the covariance / projection gradients are computed; each thread then turns ITS row into the dL_dsh row in
+// registers, puts it back, and the block writes (or, in accumulate mode, adds) the 48 KB with coalesced 128-bit accesses.
+template <bool STAGE>
+__global__ void __launch_bounds__(PB_THREADS, 3) preprocess_bwd_kernel(const PreBwdArgs a) {
+    extern __shared__ __align__(16) unsigned char pb_smem[];
+    float4* stage = reinterpret_cast<float4*>(pb_smem);
+    const int tid = threadIdx.x;
+    const int base = blockIdx.x * PB_THREADS;
+    const int idx = base + tid;
+    const int nsh = 3 * a.M;  // floats per dL_dsh row
     const bool accum = a.accumulate != 0;
+    const bool in_range = idx < a.P;
+    const bool visible = in_range && (a.radii[idx] > 0);
     auto put1 = [accum](float* p, float v) { *p = accum ? *p + v : v; };
     auto put4 = [accum](float4* p, float4 v) {
         if (accum) {
@@ -275,9 +265,26 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
         }
         *p = v;
     };
-    if (!(a.radii[idx] > 0)) {
-        if (accum) return;  // nothing to add
-        // invisible: every gradient is zero (the reference relies on torch::zeros for this)
+
+    if (STAGE) {
+        const int nvalid = min(PB_THREADS, a.P - base);
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)base * PB_ROW_F4;
+        const int total = nvalid * PB_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < PB_ROW_F4; k++) {
+            int e = tid + k * PB_THREADS;
+            if (e < total) {
+                int g = e / PB_ROW_F4, j = e - g * PB_ROW_F4;
+                cp_async_16(&stage[g * PB_ROW_PAD_F4 + j], src + e);
+            }
+        }
+        cp_async_commit();
+    }
+
+    float3 mean = {0.f, 0.f, 0.f}, dL_dcol = {0.f, 0.f, 0.f}, dL_dmean_acc = {0.f, 0.f, 0.f};
+
+    if (in_range && !visible && !accum) {
+        // not rendered: every gradient is zero (the reference relies on torch::zeros for this, rasterize_points.cu:151-159)
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             if (a.dL_dmeans2D) a.dL_dmeans2D[3 * idx + k] = 0.f;
@@ -290,218 +297,278 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
 #pragma unroll
             for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * idx + k] = 0.f;
         reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (sh_out) {
-            if (sh_aligned && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
+        if (a.dL_dsh && !STAGE) {
+            float* sh_out = a.dL_dsh + (size_t)idx * nsh;
+            if (((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
                 float4* o4 = reinterpret_cast<float4*>(sh_out);
                 for (int j = 0; j < nsh / 4; j++) o4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             } else {
                 for (int j = 0; j < nsh; j++) sh_out[j] = 0.f;
             }
         }
-        return;
     }
 
-    const float4* acc4 = reinterpret_cast<const float4*>(a.acc + (size_t)idx * ACC_STRIDE);
-    const float4 q0 = acc4[0], q1 = acc4[1], q2 = acc4[2];
-    const float dL_dmean2D_x = q0.x, dL_dmean2D_y = q0.y;
-    const float3 dL_dconic = {q0.z, q0.w, q1.x};  // (x, y, w) of the reference's float4
-    const float dL_dopac = q1.y;
-    const float3 dL_dcol = {q1.z, q1.w, q2.x};
+    if (visible) {
+        const float4* acc4 = reinterpret_cast<const float4*>(a.acc + (size_t)idx * ACC_STRIDE);
+        const float4 q0 = acc4[0], q1 = acc4[1], q2 = acc4[2];
+        const float dL_dmean2D_x = q0.x, dL_dmean2D_y = q0.y;
+        const float3 dL_dconic = {q0.z, q0.w, q1.x};  // (x, y, w) of the reference's float4
+        const float dL_dopac = q1.y;
+        dL_dcol = {q1.z, q1.w, q2.x};
 
-    if (a.dL_dmeans2D) {
-        put1(&a.dL_dmeans2D[3 * idx + 0], dL_dmean2D_x);
-        put1(&a.dL_dmeans2D[3 * idx + 1], dL_dmean2D_y);
-        put1(&a.dL_dmeans2D[3 * idx + 2], 0.f);
-    }
-    if (a.dL_dcolors) {
-        put1(&a.dL_dcolors[3 * idx + 0], dL_dcol.x);
-        put1(&a.dL_dcolors[3 * idx + 1], dL_dcol.y);
-        put1(&a.dL_dcolors[3 * idx + 2], dL_dcol.z);
-    }
-    put1(&a.dL_dopacity[idx], dL_dopac);
+        if (a.dL_dmeans2D) {
+            put1(&a.dL_dmeans2D[3 * idx + 0], dL_dmean2D_x);
+            put1(&a.dL_dmeans2D[3 * idx + 1], dL_dmean2D_y);
+            put1(&a.dL_dmeans2D[3 * idx + 2], 0.f);
+        }
+        if (a.dL_dcolors) {
+            put1(&a.dL_dcolors[3 * idx + 0], dL_dcol.x);
+            put1(&a.dL_dcolors[3 * idx + 1], dL_dcol.y);
+            put1(&a.dL_dcolors[3 * idx + 2], dL_dcol.z);
+        }
+        put1(&a.dL_dopacity[idx], dL_dopac);
 
-    const float3 mean = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
-    float cov3D[6];
-    float3 sc = {0.f, 0.f, 0.f};
-    float4 rq = {0.f, 0.f, 0.f, 0.f};
-    if (a.cov3D_precomp != nullptr) {
+        mean = {a.means[3 * idx], a.means[3 * idx + 1], a.means[3 * idx + 2]};
+        float cov3D[6];
+        float3 sc = {0.f, 0.f, 0.f};
+        float4 rq = {0.f, 0.f, 0.f, 0.f};
+        if (a.cov3D_precomp != nullptr) {
 #pragma unroll
-        for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D_precomp[6 * idx + k];
-    } else {
-        sc = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
-        rq = __ldg(reinterpret_cast<const float4*>(a.rots) + idx);
-        cov3d_from_scale_rot(sc, a.scale_mod, rq, cov3D);  // recomputed instead of stored (same code as forward)
+            for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D_precomp[6 * idx + k];
+        } else {
+            sc = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
+            rq = __ldg(reinterpret_cast<const float4*>(a.rots) + idx);
+            cov3d_from_scale_rot(sc, a.scale_mod, rq, cov3D);  // recomputed instead of stored (same code as forward)
+        }
+
+        // ---- computeCov2DCUDA, backward.cu:162-273 ----
+        const float h_x = a.focal_x, h_y = a.focal_y;
+        Ewa e = ewa_project(mean, h_x, h_y, a.tan_fovx, a.tan_fovy, cov3D, a.view);
+        const float3 t = e.t;
+        const float x_grad_mul = e.txtz < -e.limx || e.txtz > e.limx ? 0 : 1;
+        const float y_grad_mul = e.tytz < -e.limy || e.tytz > e.limy ? 0 : 1;
+        const Mat3& T = e.T;
+        const Mat3& Vrk = e.Vrk;
+        const float ca = e.a, cb = e.b, cc = e.c;
+        float denom = ca * cc - cb * cb;
+        float dL_da = 0, dL_db = 0, dL_dc = 0;
+        float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        float dL_dcov[6];
+        if (denom2inv != 0) {
+            dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
+            dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
+            dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
+            dL_dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+            dL_dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+            dL_dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+            dL_dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+                         2 * T.m[1][0] * T.m[1][1] * dL_dc;
+            dL_dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+                         2 * T.m[1][0] * T.m[1][2] * dL_dc;
+            dL_dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+                         2 * T.m[1][1] * T.m[1][2] * dL_dc;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 6; i++) dL_dcov[i] = 0;
+        }
+        if (a.dL_dcov3D)
+#pragma unroll
+            for (int i = 0; i < 6; i++) put1(&a.dL_dcov3D[6 * idx + i], dL_dcov[i]);
+
+        float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
+                        (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
+        float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
+                        (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
+        float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
+                        (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
+        float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
+                        (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
+        float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
+                        (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
+        float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
+                        (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
+
+        // W as built in ewa_project: W.m[c][r] = view[4*r + c]  (glm::mat3(view[0], view[4], view[8], ...))
+        const float* vm = a.view;
+        const float W00 = vm[0], W01 = vm[4], W02 = vm[8];
+        const float W10 = vm[1], W11 = vm[5], W12 = vm[9];
+        const float W20 = vm[2], W21 = vm[6], W22 = vm[10];
+        float dL_dJ00 = W00 * dL_dT00 + W01 * dL_dT01 + W02 * dL_dT02;
+        float dL_dJ02 = W20 * dL_dT00 + W21 * dL_dT01 + W22 * dL_dT02;
+        float dL_dJ11 = W10 * dL_dT10 + W11 * dL_dT11 + W12 * dL_dT12;
+        float dL_dJ12 = W20 * dL_dT10 + W21 * dL_dT11 + W22 * dL_dT12;
+
+        float tz = 1.f / t.z;
+        float tz2 = tz * tz;
+        float tz3 = tz2 * tz;
+        float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+        float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+        float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                       (2 * h_y * t.y) * tz3 * dL_dJ12;
+        dL_dmean_acc = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, a.view);
+
+        // ---- preprocessCUDA (backward.cu:366-395) ----
+        const float* proj = a.proj;
+        float4 m_hom = xform_point_4x4(mean, proj);
+        float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+        float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+        float3 dL_dmean;
+        dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D_y;
+        dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D_y;
+        dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D_y;
+        dL_dmean_acc.x += dL_dmean.x;
+        dL_dmean_acc.y += dL_dmean.y;
+        dL_dmean_acc.z += dL_dmean.z;
+
+        // ---- computeCov3D backward (backward.cu:278-341) ----
+        if (a.scales != nullptr) {
+            float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
+            Mat3 R = mat3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                          2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                          2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+            Mat3 S = mat3(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+            float3 s = {a.scale_mod * sc.x, a.scale_mod * sc.y, a.scale_mod * sc.z};
+            S.m[0][0] = s.x;
+            S.m[1][1] = s.y;
+            S.m[2][2] = s.z;
+            Mat3 M = mul(S, R);
+            Mat3 dL_dSigma = mat3(dL_dcov[0], 0.5f * dL_dcov[1], 0.5f * dL_dcov[2], 0.5f * dL_dcov[1], dL_dcov[3],
+                                  0.5f * dL_dcov[4], 0.5f * dL_dcov[2], 0.5f * dL_dcov[4], dL_dcov[5]);
+            // dL_dM = 2.0f * M * dL_dSigma  (glm: scalar*mat first, then the product)
+            Mat3 M2;
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+#pragma unroll
+                for (int rr = 0; rr < 3; rr++) M2.m[c][rr] = 2.0f * M.m[c][rr];
+            Mat3 dL_dM = mul(M2, dL_dSigma);
+            Mat3 Rt = transpose(R);
+            Mat3 dL_dMt = transpose(dL_dM);
+            float3 dsc;
+            dsc.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+            dsc.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+            dsc.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+            put1(&a.dL_dscales[3 * idx + 0], dsc.x);
+            put1(&a.dL_dscales[3 * idx + 1], dsc.y);
+            put1(&a.dL_dscales[3 * idx + 2], dsc.z);
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                dL_dMt.m[0][k] *= s.x;
+                dL_dMt.m[1][k] *= s.y;
+                dL_dMt.m[2][k] *= s.z;
+            }
+            float4 dq;
+            dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+                   2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
+            dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+                   2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
+            dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+                   2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
+            dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+                   2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
+            put4(&reinterpret_cast<float4*>(a.dL_drots)[idx], dq);
+        } else if (!accum) {
+            a.dL_dscales[3 * idx + 0] = 0.f;
+            a.dL_dscales[3 * idx + 1] = 0.f;
+            a.dL_dscales[3 * idx + 2] = 0.f;
+            reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     }
 
-    // ---- computeCov2DCUDA, backward.cu:162-273 ----
-    const float h_x = a.focal_x, h_y = a.focal_y;
-    Ewa e = ewa_project(mean, h_x, h_y, a.tan_fovx, a.tan_fovy, cov3D, a.view);
-    const float3 t = e.t;
-    const float x_grad_mul = e.txtz < -e.limx || e.txtz > e.limx ? 0 : 1;
-    const float y_grad_mul = e.tytz < -e.limy || e.tytz > e.limy ? 0 : 1;
-    const Mat3& T = e.T;
-    const Mat3& Vrk = e.Vrk;
-    const float ca = e.a, cb = e.b, cc = e.c;
-    float denom = ca * cc - cb * cb;
-    float dL_da = 0, dL_db = 0, dL_dc = 0;
-    float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-    float dL_dcov[6];
-    if (denom2inv != 0) {
-        dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
-        dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
-        dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
-        dL_dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
-        dL_dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
-        dL_dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
-        dL_dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
-                     2 * T.m[1][0] * T.m[1][1] * dL_dc;
-        dL_dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
-                     2 * T.m[1][0] * T.m[1][2] * dL_dc;
-        dL_dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
-                     2 * T.m[1][1] * T.m[1][2] * dL_dc;
-    } else {
-#pragma unroll
-        for (int i = 0; i < 6; i++) dL_dcov[i] = 0;
-    }
-    if (a.dL_dcov3D)
-#pragma unroll
-        for (int i = 0; i < 6; i++) put1(&a.dL_dcov3D[6 * idx + i], dL_dcov[i]);
-
-    float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
-                    (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
-    float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
-                    (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
-    float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
-                    (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
-    float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
-                    (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
-    float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
-                    (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
-    float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
-                    (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
-
-    // W as built in ewa_project: W.m[c][r] = view[4*r + c]  (glm::mat3(view[0], view[4], view[8], ...))
-    const float* vm = a.view;
-    const float W00 = vm[0], W01 = vm[4], W02 = vm[8];
-    const float W10 = vm[1], W11 = vm[5], W12 = vm[9];
-    const float W20 = vm[2], W21 = vm[6], W22 = vm[10];
-    float dL_dJ00 = W00 * dL_dT00 + W01 * dL_dT01 + W02 * dL_dT02;
-    float dL_dJ02 = W20 * dL_dT00 + W21 * dL_dT01 + W22 * dL_dT02;
-    float dL_dJ11 = W10 * dL_dT10 + W11 * dL_dT11 + W12 * dL_dT12;
-    float dL_dJ12 = W20 * dL_dT10 + W21 * dL_dT11 + W22 * dL_dT12;
-
-    float tz = 1.f / t.z;
-    float tz2 = tz * tz;
-    float tz3 = tz2 * tz;
-    float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
-    float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-    float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
-                   (2 * h_y * t.y) * tz3 * dL_dJ12;
-    float3 dL_dmean_acc = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, a.view);
-
-    // ---- preprocessCUDA (backward.cu:366-395) ----
-    const float* proj = a.proj;
-    float4 m_hom = xform_point_4x4(mean, proj);
-    float m_w = 1.0f / (m_hom.w + 0.0000001f);
-    float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
-    float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
-    float3 dL_dmean;
-    dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D_y;
-    dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D_y;
-    dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D_y;
-    dL_dmean_acc.x += dL_dmean.x;
-    dL_dmean_acc.y += dL_dmean.y;
-    dL_dmean_acc.z += dL_dmean.z;
-
-    if (a.shs != nullptr && sh_out != nullptr) {
+    // ---- SH backward (backward.cu:20-139) ----
+    if (STAGE) {
+        cp_async_wait_all();
+        __syncthreads();  // every thread's copies have landed: the rows are complete
         float f[48];
-        float o[48];
-        const float* row = a.shs + (size_t)idx * nsh;
-        const bool al = sh_aligned && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
-        load_sh_row(row, a.D, al, f);
-        float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
-        float3 dm = sh_backward(a.D, f, mean, cam, a.clamped[idx], dL_dcol, o);
+        float4* myrow = &stage[tid * PB_ROW_PAD_F4];
+        if (visible) {
+#pragma unroll
+            for (int j = 0; j < PB_ROW_F4; j++) {
+                float4 v = myrow[j];
+                f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
+            }
+            const float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
+            const float3 dm = sh_backward(
+                3, mean, cam, a.clamped[idx], dL_dcol,
+                [&](int k) { return make_float3(f[3 * k], f[3 * k + 1], f[3 * k + 2]); },
+                [&](int k, float3 v) { f[3 * k] = v.x; f[3 * k + 1] = v.y; f[3 * k + 2] = v.z; });
+            dL_dmean_acc.x += dm.x;
+            dL_dmean_acc.y += dm.y;
+            dL_dmean_acc.z += dm.z;
+#pragma unroll
+            for (int j = 0; j < PB_ROW_F4; j++)
+                myrow[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < PB_ROW_F4; j++) myrow[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+        const int nvalid = min(PB_THREADS, a.P - base);
+        const int total = nvalid * PB_ROW_F4;
+        float4* dst = reinterpret_cast<float4*>(a.dL_dsh) + (size_t)base * PB_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < PB_ROW_F4; k++) {
+            int e = tid + k * PB_THREADS;
+            if (e < total) {
+                int g = e / PB_ROW_F4, j = e - g * PB_ROW_F4;
+                put4(&dst[e], stage[g * PB_ROW_PAD_F4 + j]);
+            }
+        }
+    } else if (visible && a.shs != nullptr && a.dL_dsh != nullptr) {
+        float* sh_out = a.dL_dsh + (size_t)idx * nsh;
+        float f[48];
+        const float* rowp = a.shs + (size_t)idx * nsh;
+        const bool al = ((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+        load_sh_row(rowp, a.D, al, f);
+        const int nw = 3 * (a.D + 1) * (a.D + 1);
+        const float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
+        const float3 dm = sh_backward(
+            a.D, mean, cam, a.clamped[idx], dL_dcol,
+            [&](int k) { return make_float3(f[3 * k], f[3 * k + 1], f[3 * k + 2]); },
+            [&](int k, float3 v) { f[3 * k] = v.x; f[3 * k + 1] = v.y; f[3 * k + 2] = v.z; });
         dL_dmean_acc.x += dm.x;
         dL_dmean_acc.y += dm.y;
         dL_dmean_acc.z += dm.z;
-        const int nw = 3 * (a.D + 1) * (a.D + 1);
-        if (a.M == 16 && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
+        if ((a.M == 16) && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0)) {
             float4* o4 = reinterpret_cast<float4*>(sh_out);
 #pragma unroll
             for (int j = 0; j < 12; j++) {
                 float4 v;
-                v.x = (4 * j + 0 < nw) ? o[4 * j + 0] : 0.f;
-                v.y = (4 * j + 1 < nw) ? o[4 * j + 1] : 0.f;
-                v.z = (4 * j + 2 < nw) ? o[4 * j + 2] : 0.f;
-                v.w = (4 * j + 3 < nw) ? o[4 * j + 3] : 0.f;
+                v.x = (4 * j + 0 < nw) ? f[4 * j + 0] : 0.f;
+                v.y = (4 * j + 1 < nw) ? f[4 * j + 1] : 0.f;
+                v.z = (4 * j + 2 < nw) ? f[4 * j + 2] : 0.f;
+                v.w = (4 * j + 3 < nw) ? f[4 * j + 3] : 0.f;
                 if (!accum || 4 * j < nw) put4(&o4[j], v);
             }
         } else {
 #pragma unroll
             for (int j = 0; j < 48; j++)
-                if (j < nsh && (!accum || j < nw)) put1(&sh_out[j], (j < nw) ? o[j] : 0.f);
+                if (j < nsh && (!accum || j < nw)) put1(&sh_out[j], (j < nw) ? f[j] : 0.f);
         }
     }
-    put1(&a.dL_dmeans3D[3 * idx + 0], dL_dmean_acc.x);
-    put1(&a.dL_dmeans3D[3 * idx + 1], dL_dmean_acc.y);
-    put1(&a.dL_dmeans3D[3 * idx + 2], dL_dmean_acc.z);
 
-    // ---- computeCov3D backward (backward.cu:278-341) ----
-    if (a.scales != nullptr) {
-        float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
-        Mat3 R = mat3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                      2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                      2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-        Mat3 S = mat3(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
-        float3 s = {a.scale_mod * sc.x, a.scale_mod * sc.y, a.scale_mod * sc.z};
-        S.m[0][0] = s.x;
-        S.m[1][1] = s.y;
-        S.m[2][2] = s.z;
-        Mat3 M = mul(S, R);
-        Mat3 dL_dSigma = mat3(dL_dcov[0], 0.5f * dL_dcov[1], 0.5f * dL_dcov[2], 0.5f * dL_dcov[1], dL_dcov[3],
-                              0.5f * dL_dcov[4], 0.5f * dL_dcov[2], 0.5f * dL_dcov[4], dL_dcov[5]);
-        // dL_dM = 2.0f * M * dL_dSigma  (glm: scalar*mat first, then the product)
-        Mat3 M2;
-#pragma unroll
-        for (int c = 0; c < 3; c++)
-#pragma unroll
-            for (int rr = 0; rr < 3; rr++) M2.m[c][rr] = 2.0f * M.m[c][rr];
-        Mat3 dL_dM = mul(M2, dL_dSigma);
-        Mat3 Rt = transpose(R);
-        Mat3 dL_dMt = transpose(dL_dM);
-        float3 dsc;
-        dsc.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
-        dsc.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
-        dsc.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
-        put1(&a.dL_dscales[3 * idx + 0], dsc.x);
-        put1(&a.dL_dscales[3 * idx + 1], dsc.y);
-        put1(&a.dL_dscales[3 * idx + 2], dsc.z);
-#pragma unroll
-        for (int k = 0; k < 3; k++) {
-            dL_dMt.m[0][k] *= s.x;
-            dL_dMt.m[1][k] *= s.y;
-            dL_dMt.m[2][k] *= s.z;
-        }
-        float4 dq;
-        dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
-               2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
-        dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
-               2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
-        dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
-               2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
-        dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
-               2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
-        put4(&reinterpret_cast<float4*>(a.dL_drots)[idx], dq);
-    } else if (!accum) {
-        a.dL_dscales[3 * idx + 0] = 0.f;
-        a.dL_dscales[3 * idx + 1] = 0.f;
-        a.dL_dscales[3 * idx + 2] = 0.f;
-        reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (visible) {
+        put1(&a.dL_dmeans3D[3 * idx + 0], dL_dmean_acc.x);
+        put1(&a.dL_dmeans3D[3 * idx + 1], dL_dmean_acc.y);
+        put1(&a.dL_dmeans3D[3 * idx + 2], dL_dmean_acc.z);
     }
 }
 
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s) {
-    preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(a);
+    const int blocks = (a.P + PB_THREADS - 1) / PB_THREADS;
+    static const bool allow_stage = getenv("DAS3R_NO_SH_STAGE") == nullptr;
+    const bool stage = allow_stage && a.shs != nullptr && a.dL_dsh != nullptr && a.D == 3 && a.M == 16 &&
+                       ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0);
+    if (stage) {
+        const size_t smem = (size_t)PB_THREADS * PB_ROW_PAD_F4 * 16;
+        cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem);
+        if (e != cudaSuccess) return e;
+        preprocess_bwd_kernel<true><<<blocks, PB_THREADS, smem, s>>>(a);
+    } else {
+        preprocess_bwd_kernel<false><<<blocks, PB_THREADS, 0, s>>>(a);
+    }
     return cudaGetLastError();
 }
 

@@ -17,6 +17,8 @@
 #include "blend_common.cuh"
 #include <cub/device/device_segmented_radix_sort.cuh>
 #include <stdio.h>
+#include <map>
+#include <mutex>
 
 namespace das3r {
 
@@ -456,66 +458,227 @@ __device__ __forceinline__ void bitonic_sort_tile(uint64_t* sm, const uint64_t* 
     __syncthreads();
 }
 
-// MAXE bounds the per-thread key count the instantiation supports, so the common small-tile variants keep a low
-// register count (2 blocks/SM) and only the rare huge-tile variant pays for 32 keys per thread.
-template <int MAXE>
+// Per-tile sort, one block of 512 threads per tile. The keys of a tile are (depth bits << 32 | Gaussian index), all
+// distinct, and the required order is plain ascending - which is exactly the order of the reference's stable LSD radix
+// sort on tile|depth keys (ties in depth keep emission = index order). The common path is a most-significant-digit
+// bucket sort entirely in shared memory:
+//   1. every thread keeps its (striped, coalesced) keys in registers; a block-wide AND/OR finds the depth bits that
+//      actually vary inside the tile, and the top LOG_NB of them become the digit (monotone in depth);
+//   2. histogram, exclusive scan and scatter into 2^LOG_NB buckets with shared-memory atomics (order inside a bucket
+//      is arbitrary at this point);
+//   3. each bucket (a handful of keys) is put in order by one thread with an insertion sort on the FULL 64-bit key,
+//      so equal depths come out in index order without any extra pass.
+// If the depth distribution is so skewed that some bucket holds more than LEAF_MAX keys (e.g. thousands of Gaussians
+// at exactly the same depth), the block falls back to the bitonic network over the whole tile.
+// MAXE bounds the per-thread key count of the instantiation (registers / shared memory); MIN_N..512*MAXE is the size
+// class this launch handles, blocks of other classes exit at once.
+constexpr int LOG_NB = 10;
+constexpr int NB = 1 << LOG_NB;
+constexpr int LEAF_MAX = 128;
+
+template <int MAXE, int MIN_N>
 __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
     tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ unsorted,
-                     const GaussRec* __restrict__ rec, uint32_t* __restrict__ point_list,
-                     float4* __restrict__ sA, float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
+                     const GaussRec* __restrict__ rec, uint32_t* __restrict__ point_list, float4* __restrict__ sA,
+                     float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* sm = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* sm = reinterpret_cast<uint64_t*>(smem_raw);                                   // [512*MAXE] keys
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw + (size_t)SORT_THREADS * MAXE * 8);  // [NB] bucket sizes
+    uint32_t* s_off = s_cnt + NB;                                                           // [NB] bucket starts
+    uint32_t* s_cur = s_off + NB;                                                           // [NB] scatter cursors
+    __shared__ uint32_t s_red[2][SORT_THREADS / 32];
+    __shared__ uint32_t s_warp_tot[SORT_THREADS / 32];
+    __shared__ uint32_t s_flags[2];
     const uint32_t tile = blockIdx.x;
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
-    if (n == 0) return;
+    if (n <= MIN_N || n > SORT_THREADS * MAXE) return;  // empty, or another launch's size class
     const uint64_t* in = unsorted + range.x;
-    if (n <= SORT_THREADS * 1) bitonic_sort_tile<1>(sm, in, n);
-    else if (MAXE >= 2 && n <= SORT_THREADS * 2) bitonic_sort_tile<(MAXE >= 2 ? 2 : 1)>(sm, in, n);
-    else if (MAXE >= 4 && n <= SORT_THREADS * 4) bitonic_sort_tile<(MAXE >= 4 ? 4 : 1)>(sm, in, n);
-    else if (MAXE >= 8 && n <= SORT_THREADS * 8) bitonic_sort_tile<(MAXE >= 8 ? 8 : 1)>(sm, in, n);
-    else if (MAXE >= 16 && n <= SORT_THREADS * 16) bitonic_sort_tile<(MAXE >= 16 ? 16 : 1)>(sm, in, n);
-    else if (MAXE >= 32 && n <= SORT_THREADS * 32) bitonic_sort_tile<(MAXE >= 32 ? 32 : 1)>(sm, in, n);
-    else return;  // host never launches this variant when a tile exceeds its capacity
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+
+    // ---- 1. keys into registers, varying depth bits ----
+    uint64_t k[MAXE];
+    uint32_t v_and = 0xffffffffu, v_or = 0u;
+#pragma unroll
+    for (int e = 0; e < MAXE; e++) {
+        const int i = t + e * SORT_THREADS;
+        if (i < n) {
+            k[e] = in[i];
+            const uint32_t d = (uint32_t)(k[e] >> 32);
+            v_and &= d;
+            v_or |= d;
+        }
+    }
+    for (int i = t; i < NB; i += SORT_THREADS) s_cnt[i] = 0;
+    v_and = __reduce_and_sync(0xffffffffu, v_and);
+    v_or = __reduce_or_sync(0xffffffffu, v_or);
+    if (lane == 0) {
+        s_red[0][warp] = v_and;
+        s_red[1][warp] = v_or;
+    }
+    if (t == 0) s_flags[0] = 0;
+    __syncthreads();
+    v_and = 0xffffffffu;
+    v_or = 0u;
+#pragma unroll
+    for (int w = 0; w < SORT_THREADS / 32; w++) {
+        v_and &= s_red[0][w];
+        v_or |= s_red[1][w];
+    }
+    const uint32_t diff = v_and ^ v_or;
+    const int top = diff ? (31 - __clz(diff)) : 0;
+    const int shift = max(0, top - (LOG_NB - 1));
+
+    // ---- 2. histogram ----
+#pragma unroll
+    for (int e = 0; e < MAXE; e++) {
+        const int i = t + e * SORT_THREADS;
+        if (i < n) atomicAdd(&s_cnt[((uint32_t)(k[e] >> 32) >> shift) & (NB - 1)], 1u);
+    }
+    __syncthreads();
+    // exclusive scan of the NB counts (2 per thread) + largest bucket
+    {
+        const uint32_t c0 = s_cnt[2 * t], c1 = s_cnt[2 * t + 1];
+        if (max(c0, c1) > (uint32_t)LEAF_MAX) atomicOr(&s_flags[0], 1u);
+        uint32_t incl = c0 + c1;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_warp_tot[warp] = incl;
+        __syncthreads();
+        uint32_t wbase = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_THREADS / 32; w++) wbase += (w < warp) ? s_warp_tot[w] : 0u;
+        const uint32_t ex = wbase + incl - (c0 + c1);
+        s_off[2 * t] = ex;
+        s_off[2 * t + 1] = ex + c0;
+        s_cur[2 * t] = ex;
+        s_cur[2 * t + 1] = ex + c0;
+    }
+    __syncthreads();
+
+    if (s_flags[0] != 0) {
+        // skewed depths: bitonic network over the whole tile (reads the keys again from global memory)
+        if (n <= SORT_THREADS * 1) bitonic_sort_tile<1>(sm, in, n);
+        else if (MAXE >= 2 && n <= SORT_THREADS * 2) bitonic_sort_tile<(MAXE >= 2 ? 2 : 1)>(sm, in, n);
+        else if (MAXE >= 4 && n <= SORT_THREADS * 4) bitonic_sort_tile<(MAXE >= 4 ? 4 : 1)>(sm, in, n);
+        else if (MAXE >= 8 && n <= SORT_THREADS * 8) bitonic_sort_tile<(MAXE >= 8 ? 8 : 1)>(sm, in, n);
+        else if (MAXE >= 16 && n <= SORT_THREADS * 16) bitonic_sort_tile<(MAXE >= 16 ? 16 : 1)>(sm, in, n);
+        else bitonic_sort_tile<(MAXE >= 32 ? 32 : 1)>(sm, in, n);
+    } else {
+        // ---- scatter into buckets ----
+#pragma unroll
+        for (int e = 0; e < MAXE; e++) {
+            const int i = t + e * SORT_THREADS;
+            if (i < n) {
+                const uint32_t pos = atomicAdd(&s_cur[((uint32_t)(k[e] >> 32) >> shift) & (NB - 1)], 1u);
+                sm[pos] = k[e];
+            }
+        }
+        __syncthreads();
+        // ---- 3. leaf: every bucket is put in order on the FULL key ----
+        // (a) small buckets (<= 8 keys): one thread each, keys in registers, fixed odd-even transposition network
+        for (int b = t; b < NB; b += SORT_THREADS) {
+            const uint32_t s0 = s_off[b], m = s_cnt[b];
+            if (m > 1 && m <= 8) {
+                uint64_t v[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = (j < (int)m) ? sm[s0 + j] : ~0ull;
+#pragma unroll
+                for (int round = 0; round < 8; round++) {
+#pragma unroll
+                    for (int j = (round & 1); j + 1 < 8; j += 2) {
+                        const uint64_t lo = min(v[j], v[j + 1]), hi = max(v[j], v[j + 1]);
+                        v[j] = lo;
+                        v[j + 1] = hi;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (j < (int)m) sm[s0 + j] = v[j];
+            }
+        }
+        // (b) medium buckets (9..128 keys): one warp each, rank sort (a key's final slot = number of smaller keys)
+        for (int b = warp; b < NB; b += SORT_THREADS / 32) {
+            const uint32_t s0 = s_off[b], m = s_cnt[b];
+            if (m > 8) {  // m <= LEAF_MAX is guaranteed by the flag test above
+                uint64_t mine[LEAF_MAX / 32];
+                uint32_t rank[LEAF_MAX / 32];
+#pragma unroll
+                for (int r = 0; r < LEAF_MAX / 32; r++) {
+                    const uint32_t j = (uint32_t)lane + 32u * r;
+                    mine[r] = (j < m) ? sm[s0 + j] : ~0ull;
+                    rank[r] = 0;
+                }
+                for (uint32_t j = 0; j < m; j++) {
+                    const uint64_t o = sm[s0 + j];  // broadcast read
+#pragma unroll
+                    for (int r = 0; r < LEAF_MAX / 32; r++) rank[r] += (o < mine[r]) ? 1u : 0u;
+                }
+                __syncwarp();
+#pragma unroll
+                for (int r = 0; r < LEAF_MAX / 32; r++)
+                    if ((uint32_t)lane + 32u * r < m) sm[s0 + rank[r]] = mine[r];
+            }
+        }
+        __syncthreads();
+    }
+
+    // The sorted keys leave as point_list (+ the debug key array); the tile-ordered record streams are produced by a
+    // separate, fully parallel gather kernel so that no tile serialises long-latency gathers behind its sort.
     for (int i = threadIdx.x; i < n; i += SORT_THREADS) {
-        uint64_t key = sm[i];
-        uint32_t g = (uint32_t)key;
-        point_list[range.x + i] = g;
-        const GaussRec r = rec[g];
-        // tile-ordered copy, split into the 16-byte stream every warp scans and the 32 bytes only survivors need;
-        // it carries the Gaussian index instead of the depth
-        sA[range.x + i] = r.A;
-        sBC[2 * (size_t)(range.x + i)] = r.B;
-        sBC[2 * (size_t)(range.x + i) + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
+        const uint64_t key = sm[i];
+        point_list[range.x + i] = (uint32_t)key;
         if (keys_sorted) keys_sorted[range.x + i] = ((uint64_t)tile << 32) | (key >> 32);
     }
 }
 
+// gather_records: entry i of the sorted list -> sA[i] = {x, y, h, -tau'}, sBC[i] = {conic, opacity}, {rgb, index}.
+__global__ void __launch_bounds__(256) gather_records_kernel(int R, const uint32_t* __restrict__ point_list,
+                                                             const GaussRec* __restrict__ rec, float4* __restrict__ sA,
+                                                             float4* __restrict__ sBC) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    const uint32_t g = point_list[i];
+    const GaussRec r = rec[g];
+    sA[i] = r.A;
+    sBC[2 * (size_t)i] = r.B;
+    sBC[2 * (size_t)i + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
+}
+
 int tile_sort_capacity() { return SORT_THREADS * SORT_MAX_E; }
 
-template <int MAXE>
+template <int MAXE, int MIN_N>
 static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const uint64_t* unsorted, const GaussRec* rec,
                                             uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                                             cudaStream_t s) {
-    const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t);
+    const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t) + 3 * NB * sizeof(uint32_t);
     if (smem > 48 * 1024) {
         cudaError_t err =
-            cudaFuncSetAttribute(tile_sort_kernel<MAXE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaFuncSetAttribute(tile_sort_kernel<MAXE, MIN_N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
     }
-    tile_sort_kernel<MAXE><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sA, sBC, keys_sorted);
+    tile_sort_kernel<MAXE, MIN_N><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sA, sBC, keys_sorted);
     return cudaGetLastError();
 }
 
-cudaError_t launch_tile_sort(int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
+cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
                              const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                              cudaStream_t s) {
     if (max_count > (uint32_t)tile_sort_capacity()) return cudaErrorInvalidValue;
-    if (max_count <= SORT_THREADS * 4)
-        return launch_tile_sort_variant<4>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
-    if (max_count <= SORT_THREADS * 8)
-        return launch_tile_sort_variant<8>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
-    return launch_tile_sort_variant<32>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    // Tiles are sorted by the cheapest variant that fits them: every launch covers all tiles, and a block whose tile
+    // belongs to another size class exits at once, so a few crowded tiles do not drag the whole grid to the
+    // 128-register variant.
+    cudaError_t e = cudaSuccess;
+    if (max_count > SORT_THREADS * 8)  // the few crowded tiles first: they are the long pole
+        e = launch_tile_sort_variant<32, SORT_THREADS * 8>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    if (e != cudaSuccess) return e;
+    e = launch_tile_sort_variant<8, 0>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    if (e != cudaSuccess) return e;
+    gather_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, point_list, rec, sA, sBC);
+    return cudaGetLastError();
 }
 
 // Fallback for tiles larger than the in-shared-memory capacity: library segmented radix sort of the
@@ -549,6 +712,55 @@ __global__ void ranges_to_offsets_kernel(int T, const uint2* __restrict__ ranges
 }
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static size_t spread_pad_smem_uncached(const void* kernel, int grid, int block_threads, size_t static_smem);
+
+size_t spread_pad_smem(const void* kernel, int grid, int block_threads, size_t static_smem) {
+    // the answer only depends on (device, kernel, grid): memoise it, the queries cost several microseconds per launch
+    struct Key {
+        int dev;
+        const void* k;
+        int grid;
+        bool operator<(const Key& o) const {
+            return dev != o.dev ? dev < o.dev : (k != o.k ? k < o.k : grid < o.grid);
+        }
+    };
+    static std::mutex mu;
+    static std::map<Key, size_t> cache;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    std::lock_guard<std::mutex> lock(mu);
+    Key key{dev, kernel, grid};
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    size_t v = spread_pad_smem_uncached(kernel, grid, block_threads, static_smem);
+    cache[key] = v;
+    return v;
+}
+
+static size_t spread_pad_smem_uncached(const void* kernel, int grid, int block_threads, size_t static_smem) {
+    int dev = 0, sms = 0, smem_sm = 0, smem_optin = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (sms <= 0 || smem_sm <= 0) return 0;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, block_threads, 0) != cudaSuccess || occ <= 0)
+        return 0;
+    const int want = (grid + sms - 1) / sms;  // blocks per SM of an even spread
+    if (want >= occ) return 0;                // more than one wave, or already exactly full
+    // each block also pays 1 KB of driver-reserved shared memory
+    size_t per_block = (size_t)smem_sm / (size_t)want;
+    if (per_block <= static_smem + 1024) return 0;
+    size_t dyn = per_block - static_smem - 1024;
+    dyn = dyn / 256 * 256;
+    if (dyn + static_smem > (size_t)smem_optin) dyn = (size_t)smem_optin - static_smem;
+    if (dyn > 48 * 1024 - static_smem)
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn) != cudaSuccess)
+            return 0;
+    return dyn;
+}
 
 size_t tile_sort_fallback_bytes(int R, int T) {
     size_t cub_bytes = 0;
@@ -717,12 +929,16 @@ cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, cons
                              uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
                              cudaStream_t s) {
     const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    if (out_depth || out_alpha)
-        blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, 0, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
-                                                                   n_contrib, out_color, out_depth, out_alpha);
-    else
-        blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, 0, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
-                                                                    n_contrib, out_color, out_depth, out_alpha);
+    const size_t ring_bytes = sizeof(RingRec) * BLEND_WARPS * RING;
+    if (out_depth || out_alpha) {
+        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<true>, (int)blocks, 32 * BLEND_WARPS, ring_bytes);
+        blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
+                                                                     n_contrib, out_color, out_depth, out_alpha);
+    } else {
+        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS, ring_bytes);
+        blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
+                                                                      n_contrib, out_color, out_depth, out_alpha);
+    }
     return cudaGetLastError();
 }
 

@@ -62,7 +62,7 @@ cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec,
 // Sorts every tile whose entry count is <= tile_sort_capacity(); returns cudaErrorInvalidValue if max_count is larger
 // (the caller then uses the segmented fallback).
 int tile_sort_capacity();
-cudaError_t launch_tile_sort(int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
+cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
                              const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                              cudaStream_t s);
 // Fallback for tiles beyond the shared-memory capacity: library segmented radix sort + gather.
@@ -81,6 +81,12 @@ cudaError_t launch_mark_visible(int P, const float* means, const float* view, co
 cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC, int W, int H, const float* bg, const float* final_T,
                              const uint32_t* n_contrib, const float* dL_dpix, float* acc, cudaStream_t s);
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
+
+// One-wave launches must be spread evenly: the hardware block scheduler fills an SM up to its occupancy limit before
+// moving on, so a grid smaller than one full wave leaves some SMs empty while others run at the limit (measured on
+// blend_fwd: sm__cycles_active min 199k / max 717k). Returns the number of bytes of (unused) dynamic shared memory to
+// request so that at most ceil(grid / #SMs) blocks fit on an SM; 0 when the grid spans several waves anyway.
+size_t spread_pad_smem(const void* kernel, int grid, int block_threads, size_t static_smem);
 
 // knn.cu
 size_t knn_scratch_bytes(int P);
