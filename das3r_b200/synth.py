@@ -118,10 +118,7 @@ def knn_dist2_cpu(xyz: torch.Tensor) -> torch.Tensor:
     idx = idx.reshape(n, k)
     # drop self (first column is normally self; with exact duplicates any of the zero-distance hits may be self)
     rows = np.arange(n)
-    nb = np.empty((n, 3), dtype=np.int64)
     d2 = np.full((n, 3), np.finfo(np.float32).max, dtype=np.float32)
-    for r in range(n) if n < 4 else ():
-        pass
     if k == 4:
         self_pos = np.argmax(idx == rows[:, None], axis=1)
         has_self = (idx == rows[:, None]).any(axis=1)

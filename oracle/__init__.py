@@ -79,8 +79,18 @@ def forward(*, means3D, opacities, viewmatrix, projmatrix, campos, bg, tanfovx, 
     Returns every output and intermediate the parity tests compare."""
     L = lib()
     means = _np(means3D)
-    P = means.shape[0]
     W, H = int(image_width), int(image_height)
+    if means is None:  # P == 0: all-zero image, no background (rasterize_points.cu:68,:81)
+        gx, gy = (W + 15) // 16, (H + 15) // 16
+        return dict(color=np.zeros((3, H, W), np.float32), radii=np.zeros(0, np.int32),
+                    depth=np.zeros((H, W), np.float32), alpha=np.zeros((H, W), np.float32), num_rendered=0,
+                    xy=np.zeros((0, 2), np.float32), depths=np.zeros(0, np.float32), cov3D=np.zeros((0, 6), np.float32),
+                    rgb=np.zeros((0, 3), np.float32), conic_opacity=np.zeros((0, 4), np.float32),
+                    tiles_touched=np.zeros(0, np.uint32), clamped=np.zeros((0, 3), np.uint8),
+                    point_offsets=np.zeros(0, np.uint32), keys_sorted=np.zeros(0, np.uint64),
+                    point_list=np.zeros(0, np.uint32), ranges=np.zeros((gx * gy, 2), np.uint32),
+                    final_T=np.ones(W * H, np.float32), n_contrib=np.zeros(W * H, np.uint32), W=W, H=H, M=0)
+    P = means.shape[0]
     shs_ = _np(shs)
     M = shs_.shape[1] if shs_ is not None else 0
     colors_ = _np(colors_precomp)

@@ -1,0 +1,72 @@
+"""The C-ABI library loads without a GPU and exports every symbol include/das3r_raster.h declares; the pure-host entry
+points behave (no compute calls here)."""
+import ctypes
+import os
+import re
+
+import _harness as Hn
+
+ROOT = Hn.ROOT
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "das3r_raster.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(das3r_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported():
+    lib = Hn.cabi()
+    names = declared_symbols()
+    assert "das3r_raster_forward" in names and "das3r_raster_backward" in names and "das3r_knn_dist2" in names
+    assert "das3r_mark_visible" in names
+    for n in names:
+        assert hasattr(lib, n), f"{n} is declared in include/das3r_raster.h but not exported by libdas3r_raster.so"
+
+
+def test_every_entry_point_cites_the_reference():
+    text = open(os.path.join(ROOT, "include", "das3r_raster.h")).read()
+    for n in ("das3r_raster_forward", "das3r_raster_backward", "das3r_mark_visible", "das3r_knn_dist2"):
+        i = text.index(f"int {n}(")
+        comment = text[text.rfind("/*", 0, i):i]
+        assert re.search(r"\.(cu|h|py):\d+", comment), f"{n} lacks a reference file:line citation"
+
+
+def test_version_and_error_string():
+    lib = Hn.cabi()
+    assert lib.das3r_abi_version() == 1
+    assert lib.das3r_last_error() in (b"",) or isinstance(lib.das3r_last_error(), bytes)
+
+
+def test_layout_query_is_consistent():
+    P, W, H, R = 1000, 70, 50, 4321
+    L = Hn.layout(P, W, H, R)
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    assert L.g_recB == L.g_recA + 16 and L.g_recC == L.g_recA + 32
+    assert L.g_tiles_touched >= L.g_recA + 48 * P
+    assert L.g_clamped >= L.g_tiles_touched + 4 * P
+    assert L.geom_bytes >= L.g_clamped + P
+    assert L.i_n_contrib >= L.i_final_T + 4 * W * H
+    assert L.i_ranges >= L.i_n_contrib + 4 * W * H
+    assert L.i_tile_counts >= L.i_ranges + 8 * T
+    assert L.b_point_list >= L.b_unsorted + 8 * R
+    assert L.b_sA >= L.b_point_list + 4 * R
+    assert L.b_sB >= L.b_sA + 16 * R
+    assert L.binning_bytes >= L.b_keys_sorted + 8 * R
+    for f, _ in L._fields_:
+        assert getattr(L, f) % 16 == 0, f
+
+
+def test_bad_arguments_are_rejected_without_touching_the_gpu():
+    lib = Hn.cabi()
+    rc = lib.das3r_raster_forward(None, None, None, None, None, None, None, None, None, None, None)
+    assert rc == -1
+    assert b"forward" in lib.das3r_last_error()
+    rc = lib.das3r_raster_backward(None, None, None, None, None, None, None)
+    assert rc == -1
+    assert lib.das3r_mark_visible(ctypes.c_int32(-1), None, None, None, None, None) == -1
+    assert lib.das3r_knn_dist2(ctypes.c_int32(-5), None, None, None, ctypes.c_size_t(0), None) == -1
+    # zero-sized problems are no-ops
+    assert lib.das3r_mark_visible(ctypes.c_int32(0), None, None, None, None, None) == 0
+    assert lib.das3r_knn_dist2(ctypes.c_int32(0), None, None, None, ctypes.c_size_t(0), None) == 0
+    assert lib.das3r_raster_backward_scratch_bytes(ctypes.c_int32(1000)) >= 48 * 1000

@@ -1,0 +1,86 @@
+"""View/frame sharding and the one-collective gradient exchange, on CPU with gloo (world_size 2)."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from das3r_b200 import sharding
+
+
+def test_shard_views_disjoint_and_complete():
+    perm = list(range(10))
+    world, vps = 4, 2
+    seen = []
+    for step in range(3):
+        per_step = []
+        for r in range(world):
+            v = sharding.shard_views(perm, step, r, world, vps)
+            assert len(v) == vps
+            per_step += v
+        assert len(set(per_step)) == min(len(per_step), len(perm)) or len(per_step) > len(perm)
+        seen += per_step
+    # consecutive entries of the permutation are consumed in order, wrapping around
+    assert seen[:10] == perm
+
+
+def test_shard_frames_partition():
+    n, world = 503, 8
+    allf = []
+    for r in range(world):
+        f = sharding.shard_frames(n, r, world)
+        assert all(i % world == r for i in f)
+        allf += f
+    assert sorted(allf) == list(range(n))
+
+
+def test_grad_bucket_views_alias_the_flat_buffer():
+    shapes = sharding.gaussian_grad_shapes(7)
+    b = sharding.GradBucket(shapes, "cpu")
+    assert b.nbytes() == 7 * 59 * 4  # 236 bytes per Gaussian
+    b.views()["shs"].fill_(2.0)
+    assert float(b.flat.sum()) == 7 * 48 * 2.0
+    b.accumulate({"means3D": torch.ones(7, 3), "ignored": torch.ones(1)})
+    assert float(b.views()["means3D"].sum()) == 21.0
+    b.zero_()
+    assert float(b.flat.abs().sum()) == 0.0
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    P = 50
+    shapes = sharding.gaussian_grad_shapes(P)
+    bucket = sharding.GradBucket(shapes, "cpu")
+    perm = list(range(6))
+    # every rank accumulates a deterministic "gradient" per view it owns
+    for step in range(2):
+        for v in sharding.shard_views(perm, step, rank, world, 1):
+            g = {k: torch.full(s, float(v + 1)) for k, s in shapes.items()}
+            bucket.accumulate(g)
+    h = bucket.all_reduce(async_op=True)
+    h.wait()
+    mx = sharding.all_reduce_max(float(rank + 1), "cpu")
+    if rank == 0:
+        torch.save({"flat": bucket.flat.clone(), "max": mx}, out)
+    dist.destroy_process_group()
+
+
+def test_allreduce_over_gloo_world2(tmp_path):
+    world = 2
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    res = torch.load(out)
+    # steps 0,1 x ranks 0,1 consume views 0,1,2,3 -> values 1+2+3+4 = 10 everywhere
+    assert torch.all(res["flat"] == 10.0)
+    assert res["max"] == 2.0
