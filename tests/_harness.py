@@ -208,8 +208,9 @@ def rel_err(a, b) -> float:
     return float(np.abs(a - b).max() / denom)
 
 
-def compare_forward(ours: dict, ref: dict, P: int) -> dict:
-    """Mismatch counts / max errors between the new path and a reference-layout dict (run_ref or run_oracle)."""
+def compare_forward(ours: dict, ref: dict, P: int, has_sh: bool = True) -> dict:
+    """Mismatch counts / max errors between the new path and a reference-layout dict (run_ref or run_oracle).
+    has_sh=False (colors_precomp given): the reference never writes its rgb / clamped arrays, so they are not compared."""
     r = {}
     r["radii_mismatch"] = int((np_(ours["radii"]) != np_(ref["radii"])).sum())
     r["color_maxabs"] = float(np.abs(np_(ours["color"]) - np_(ref["color"])).max())
@@ -222,12 +223,14 @@ def compare_forward(ours: dict, ref: dict, P: int) -> dict:
     r["xy_mismatch"] = int((rec[vis, 0:2] != np_(ref["xy"])[vis]).sum())
     r["depth_mismatch"] = int((rec[vis, 11] != np_(ref["depths"])[vis]).sum())
     r["conic_mismatch"] = int((rec[vis, 4:8] != np_(ref["conic_opacity"])[vis]).sum())
-    rgb_ref = np_(ref["rgb"])[vis]
-    r["rgb_maxabs"] = float(np.abs(rec[vis, 8:11] - rgb_ref).max()) if vis.any() else 0.0
-    cl = np_(ours["clamped"])[vis]
-    clr = np_(ref["clamped"])[vis]
-    ours_bits = np.stack([(cl >> c) & 1 for c in range(3)], axis=1)
-    r["clamped_mismatch"] = int((ours_bits != (clr != 0)).sum())
+    r["rgb_maxabs"] = 0.0
+    if has_sh:
+        rgb_ref = np_(ref["rgb"])[vis]
+        r["rgb_maxabs"] = float(np.abs(rec[vis, 8:11] - rgb_ref).max()) if vis.any() else 0.0
+        cl = np_(ours["clamped"])[vis]
+        clr = np_(ref["clamped"])[vis]
+        ours_bits = np.stack([(cl >> c) & 1 for c in range(3)], axis=1)
+        r["clamped_mismatch"] = int((ours_bits != (clr != 0)).sum())
     r["ranges_mismatch"] = int((np_(ours["ranges"]).astype(np.int64) != np_(ref["ranges"]).astype(np.int64)).sum())
     if r["num_rendered"][0] == r["num_rendered"][1] and r["num_rendered"][0] > 0:
         r["point_list_mismatch"] = int((np_(ours["point_list"]).astype(np.int64) !=

@@ -55,7 +55,7 @@ def test_case_against_reference_cuda(name, dev):
     ours = Hn.run_ours(vd, dL.to(dev), debug=True)
     ref = Hn.run_ref(vd, dL.to(dev))
     P = vi["means3D"].shape[0]
-    assert_forward(Hn.compare_forward(ours, ref, P), name, exact_floats=True)
+    assert_forward(Hn.compare_forward(ours, ref, P, has_sh=vi.get("shs") is not None), name, exact_floats=True)
     assert_grads(Hn.compare_grads(ours["grads"], ref["grads"]), name)
 
 
@@ -65,7 +65,7 @@ def test_case_against_c_oracle(name, dev):
     ours = Hn.run_ours(Hn.to_dev(vi, dev), dL.to(dev), debug=True)
     orc = Hn.run_oracle(vi, dL)
     P = vi["means3D"].shape[0]
-    assert_forward(Hn.compare_forward(ours, orc, P), name, exact_floats=False)
+    assert_forward(Hn.compare_forward(ours, orc, P, has_sh=vi.get("shs") is not None), name, exact_floats=False)
     assert_grads(Hn.compare_grads(ours["grads"], orc["grads"]), name)
     # additive surface: depth and alpha
     assert float(np.abs(Hn.np_(ours["depth"]) - orc["depth"]).max()) <= Hn.FWD_TOL
