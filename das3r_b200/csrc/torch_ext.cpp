@@ -173,8 +173,10 @@ backward_impl(const torch::Tensor& background, const torch::Tensor& means3D_,
     auto radii = radii_.contiguous();
     TORCH_CHECK(radii.scalar_type() == torch::kInt32, "radii must be int32");
 
+    // rasterize_points.cu:145-149 takes M from sh.size(1) only when sh.size(0) != 0; an [0, M, 3] tensor (no Gaussians)
+    // must still get an [0, M, 3] gradient or autograd rejects it, so the row length is read whenever sh is 3-D
     int M = 0;
-    if (sh.defined() && sh.numel() > 0) M = sh.size(1);
+    if (sh_.defined() && sh_.dim() == 3) M = sh_.size(1);
 
     auto o = means3D.options();
     // torch::empty, not zeros: the backward kernels write every element (incl. the zeros of invisible Gaussians).

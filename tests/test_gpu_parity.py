@@ -140,8 +140,11 @@ def _crowded_case(n, W=64, H=64, same_depth=False, seed=0):
     means = torch.stack([xy[:, 0] * z, xy[:, 1] * z, z], dim=1).contiguous()
     vi, _ = make_case("sh3_small")
     vi = dict(vi)
-    vi.update(means3D=means, opacities=torch.full((n, 1), 0.01), scales=torch.full((n, 3), 0.002),
-              rotations=torch.tensor([[1.0, 0, 0, 0]]).repeat(n, 1).contiguous(),
+    # anisotropic scales and generic rotations: with isotropic Gaussians the rotation gradient is pure cancellation noise
+    rot = torch.randn(n, 4, generator=g)
+    rot = (rot / rot.norm(dim=1, keepdim=True)).contiguous()
+    vi.update(means3D=means, opacities=torch.full((n, 1), 0.01),
+              scales=(0.002 * torch.tensor([1.0, 1.6, 0.6])).repeat(n, 1).contiguous(), rotations=rot,
               shs=(torch.rand(n, 16, 3, generator=g) - 0.5).contiguous(), image_width=W, image_height=H)
     dL = torch.randn(3, H, W, generator=g) / (W * H)
     return vi, dL
@@ -218,16 +221,26 @@ def test_accumulate_mode_and_optional_outputs(dev):
              R, binning, img, False)
     fresh = C.rasterize_gaussians_backward(*bargs)
     P = vi["means3D"].shape[0]
-    outs = [e, e, torch.full((P, 1), 7.0, device=dev), torch.full((P, 3), 7.0, device=dev), e,
-            torch.full((P, 16, 3), 7.0, device=dev), torch.full((P, 3), 7.0, device=dev),
-            torch.full((P, 4), 7.0, device=dev)]
+    def bufs(fill):
+        return [e, e, torch.full((P, 1), fill, device=dev), torch.full((P, 3), fill, device=dev), e,
+                torch.full((P, 16, 3), fill, device=dev), torch.full((P, 3), fill, device=dev),
+                torch.full((P, 4), fill, device=dev)]
+
+    outs = bufs(0.0)
     C.rasterize_gaussians_backward_into(*bargs, outs, True)
     C.rasterize_gaussians_backward_into(*bargs, outs, True)
     for i in (2, 3, 5, 6, 7):
-        want = 7.0 + 2.0 * fresh[i]
-        assert Hn.rel_err(outs[i] - 7.0, want - 7.0) <= 1e-4, i
+        assert Hn.rel_err(outs[i], 2.0 * fresh[i]) <= 1e-5, i
+    marked = bufs(7.0)
+    C.rasterize_gaussians_backward_into(*bargs, marked, True)
     invisible = (radii == 0)
-    assert bool(invisible.any()) and bool(torch.all(outs[3][invisible] == 7.0))
+    assert bool(invisible.any())
+    for i in (2, 3, 5, 6, 7):
+        assert bool(torch.all(marked[i][invisible] == 7.0)), i   # unrendered Gaussians are left untouched
+    over = bufs(7.0)
+    C.rasterize_gaussians_backward_into(*bargs, over, False)     # overwrite mode: same as the fresh tensors
+    for i in (2, 3, 5, 6, 7):
+        assert torch.equal(over[i].view(-1), fresh[i].view(-1)) or Hn.rel_err(over[i], fresh[i]) <= 1e-5, i
 
 
 class _Params(ctypes.Structure):
