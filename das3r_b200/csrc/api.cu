@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 #include <atomic>
+#include <mutex>
 
 using namespace das3r;
 
@@ -379,6 +380,49 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     a.accumulate = g->accumulate;
     STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd", ST_PREPROCESS_BWD, 1);
     return DAS3R_OK;
+}
+
+// ---- backward without any device allocation (see include/das3r_raster.h) ---------------------------------------
+// The gradient accumulators live in this fixed array: one copy per GPU that loads the library, held until exit.
+// In host code the name below is only a handle: kernels must be given the address cudaGetSymbolAddress returns.
+static __device__ __align__(256) float g_static_accumulators[(size_t)DAS3R_STATIC_MAX_GAUSSIANS * ACC_STRIDE];
+
+int das3r_raster_backward_static(const das3r_raster_params* params, const das3r_raster_inputs* in,
+                                 const int32_t* radii, const das3r_raster_state* state, const float* dL_dpix,
+                                 const das3r_raster_grads* grads, void* stream_v) {
+    g_err.clear();
+    if (!params || !grads) return fail_msg(DAS3R_EINVAL, "backward_static: null argument");
+    if (params->P > DAS3R_STATIC_MAX_GAUSSIANS) {
+        char buf[200];
+        snprintf(buf, sizeof(buf),
+                 "backward_static: %d Gaussians exceed the built-in scratch of %d (use das3r_raster_backward with "
+                 "caller-provided scratch)",
+                 params->P, DAS3R_STATIC_MAX_GAUSSIANS);
+        return fail_msg(DAS3R_ELIMIT, buf);
+    }
+    // One-time set-up per device, with that device current: resolve the array's device address.
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static float* device_ptr[kMaxDevices] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "backward_static: cudaGetDevice", e);
+    if (dev < 0 || dev >= kMaxDevices) return fail_msg(DAS3R_ELIMIT, "backward_static: device ordinal out of range");
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (device_ptr[dev] == nullptr) {
+            float* ptr = nullptr;
+            e = cudaGetSymbolAddress((void**)&ptr, g_static_accumulators);
+            if (e != cudaSuccess || ptr == nullptr)
+                return fail(DAS3R_ECUDA, "backward_static: cudaGetSymbolAddress", e);
+            device_ptr[dev] = ptr;
+        }
+        scratch = device_ptr[dev];
+    }
+    das3r_raster_grads g = *grads;
+    g.scratch = scratch;  // the regular backward clears the P*48 bytes it uses before accumulating into them
+    return das3r_raster_backward(params, in, radii, state, dL_dpix, &g, stream_v);
 }
 
 int das3r_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

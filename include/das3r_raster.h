@@ -127,6 +127,29 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
                           const int32_t* radii, const das3r_raster_state* state,
                           const float* dL_dpix, const das3r_raster_grads* grads, void* stream);
 
+/* Backward for hosts that cannot allocate device memory. It has no counterpart in the reference.
+ *
+ * das3r_raster_backward needs `grads->scratch`, a P*48-byte device buffer the caller normally takes from its allocator
+ * (the torch binding borrows it from torch's caching allocator). Some callers have no such source: a C or plugin host
+ * that owns no device allocator at all, a process whose whole device was handed to another framework's memory pool at
+ * start-up (so a cudaMalloc here would fail or carve up that pool), or a frame/step loop that may not risk the
+ * device-wide stall a cudaMalloc/cudaFree can cause. For them this variant keeps the scratch inside the library, in a
+ * fixed array in device memory that exists once per GPU from the moment the library is loaded there until the process
+ * exits (DAS3R_STATIC_MAX_GAUSSIANS * 48 bytes = 6 MiB). `grads->scratch` is ignored; everything else - inputs, state
+ * blobs, gradient outputs - is passed exactly as for das3r_raster_backward, and the results are the same.
+ *
+ *  - P above DAS3R_STATIC_MAX_GAUSSIANS is refused with DAS3R_ELIMIT before any work is enqueued.
+ *  - Neither this call nor anything it runs calls cudaMalloc/cudaFree or an allocating library routine.
+ *  - The first call on a device looks up the array's device address (a one-time set-up with that device current);
+ *    make that first call before starting any stream capture.
+ *  - All calls on a device share the one array and it keeps whatever the last call left in it; the part a call uses is
+ *    cleared at its start, in stream order. Two calls whose GPU work can overlap (different streams, no dependency)
+ *    would race on it: serialise them. */
+#define DAS3R_STATIC_MAX_GAUSSIANS 131072
+int das3r_raster_backward_static(const das3r_raster_params* params, const das3r_raster_inputs* in,
+                                 const int32_t* radii, const das3r_raster_state* state,
+                                 const float* dL_dpix, const das3r_raster_grads* grads, void* stream);
+
 /* Bytes of device scratch the backward needs for P Gaussians (screen-space gradient accumulators; they replace
  * the reference's separate zero-filled dL_dconic/dL_dmean2D/dL_dcolor/dL_dopacity tensors, rasterize_points.cu:151-155). */
 size_t das3r_raster_backward_scratch_bytes(int32_t P);
