@@ -54,6 +54,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-views", type=int, default=4, help="views timed for the CPU baseline sample")
+    ap.add_argument("--streams", type=int, default=3,
+                    help="CUDA streams the views of a step are spread over (the reference arm always uses 1: its "
+                         "kernels are hard-wired to the legacy default stream)")
     return ap.parse_args()
 
 
@@ -154,6 +157,7 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout for the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     if args.impl == "ours":
@@ -189,8 +193,14 @@ def main():
     S = shared
 
     shapes = sharding.gaussian_grad_shapes(P, 16)
-    buckets = [sharding.GradBucket(shapes, dev) for _ in range(2 if world > 1 else 1)]
-    handles = [None, None]
+    # The views of a step are independent, so they are spread over S streams: the HBM-bound stages of one view
+    # (preprocess, binning, gather) overlap with the issue-bound blend kernels of another. Every stream sums into its
+    # own bucket (a shared one would be a read-modify-write race); the step ends by folding them into bucket 0.
+    S_ = 1 if args.impl != "ours" else max(1, min(args.streams, vps))
+    nbuf = 2 if world > 1 else 1
+    buckets = [[sharding.GradBucket(shapes, dev) for _ in range(S_)] for _ in range(nbuf)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(S_)] if S_ > 1 else [None]
+    handles = [None] * nbuf
     last_R = [0]
 
     def fwd(pv):
@@ -198,31 +208,49 @@ def main():
                                      S["view"], S["proj"], S["tanx"], S["tany"], H, W, S["shs"], D, S["campos"], False,
                                      False)
 
+    def one_view(pv, bk):
+        g = bk.views()
+        R, color, radii, geom, binning, img = fwd(pv)
+        last_R[0] = R
+        bargs = (S["bg"], pv["means"], radii, empty, S["scales"], pv["rots"], 1.0, empty, S["view"], S["proj"],
+                 S["tanx"], S["tany"], dL, S["shs"], D, S["campos"], geom, R, binning, img, False)
+        if args.impl == "ours":
+            outs = [empty, empty, g["opacities"], g["means3D"], empty, g["shs"], g["scales"], g["rotations"]]
+            C.rasterize_gaussians_backward_into(*bargs, outs, True)
+        else:
+            (_m2d, _dc, d_op, d_m3, _dcov, d_sh, d_sc, d_rot) = C.rasterize_gaussians_backward(*bargs)
+            g["opacities"].add_(d_op)
+            g["means3D"].add_(d_m3)
+            g["shs"].add_(d_sh)
+            g["scales"].add_(d_sc)
+            g["rotations"].add_(d_rot)
+
+    single_stream = [False]  # the per-stage profiling pass runs the views back to back on one stream
+
     def step(i):
-        b = i % len(buckets)
-        bk = buckets[b]
+        b = i % nbuf
         if handles[b] is not None:
             handles[b].wait()
             handles[b] = None
-        bk.zero_()
-        g = bk.views()
-        for pv in pool:
-            R, color, radii, geom, binning, img = fwd(pv)
-            last_R[0] = R
-            bargs = (S["bg"], pv["means"], radii, empty, S["scales"], pv["rots"], 1.0, empty, S["view"], S["proj"],
-                     S["tanx"], S["tany"], dL, S["shs"], D, S["campos"], geom, R, binning, img, False)
-            if args.impl == "ours":
-                outs = [empty, empty, g["opacities"], g["means3D"], empty, g["shs"], g["scales"], g["rotations"]]
-                C.rasterize_gaussians_backward_into(*bargs, outs, True)
-            else:
-                (_m2d, _dc, d_op, d_m3, _dcov, d_sh, d_sc, d_rot) = C.rasterize_gaussians_backward(*bargs)
-                g["opacities"].add_(d_op)
-                g["means3D"].add_(d_m3)
-                g["shs"].add_(d_sh)
-                g["scales"].add_(d_sc)
-                g["rotations"].add_(d_rot)
+        if S_ == 1 or single_stream[0]:
+            buckets[b][0].zero_()
+            for pv in pool:
+                one_view(pv, buckets[b][0])
+        else:
+            main = torch.cuda.current_stream()
+            for si, st in enumerate(streams):
+                st.wait_stream(main)
+                with torch.cuda.stream(st):
+                    buckets[b][si].zero_()
+            for j, pv in enumerate(pool):
+                with torch.cuda.stream(streams[j % S_]):
+                    one_view(pv, buckets[b][j % S_])
+            for si, st in enumerate(streams):
+                main.wait_stream(st)
+            for si in range(1, S_):
+                buckets[b][0].flat.add_(buckets[b][si].flat)
         if world > 1:
-            handles[b] = bk.all_reduce(async_op=True)
+            handles[b] = buckets[b][0].all_reduce(async_op=True)
 
     def drain():
         for b in range(len(handles)):
@@ -268,9 +296,10 @@ def main():
         "config": {
             "workload": f"C2-shaped synthetic scene: {P} Gaussians from {args.V} pointmap views, {W}x{H}, SH degree {D}, "
                         f"shs+scales/rotations inputs; step = {vps} views/rank (fwd+bwd, dense dL), gradients summed "
-                        f"in place into a {buckets[0].nbytes() // (1 << 20)} MiB fp32 bucket"
+                        f"in place into a {buckets[0][0].nbytes() // (1 << 20)} MiB fp32 bucket, views spread over {S_} CUDA "
+                        f"stream(s)"
                         + (", one NCCL all-reduce of the bucket per step (overlapped)" if world > 1 else ""),
-            "views_per_step_per_rank": vps, "P": P, "W": W, "H": H, "sh_degree": D, "num_rendered": R,
+            "views_per_step_per_rank": vps, "streams": S_, "P": P, "W": W, "H": H, "sh_degree": D, "num_rendered": R,
             "l2_policy": "inputs larger than L2 (per step each rank streams ~%d MB of distinct inputs; L2 is 126 MB)" %
                          ((P * (28 * vps + 208)) // 1_000_000),
             "parallelism": f"views sharded over {world} rank(s), Gaussians replicated",
@@ -294,11 +323,13 @@ def main():
     # ---- per-stage device times (CUDA events on the launching stream), profiled pass right after the timed region ---
     C.prof_collect(True)
     C.prof_enable(True)
+    single_stream[0] = True
     prof_steps = max(2, min(args.steps, 10))
     for i in range(prof_steps):
         step(i)
     drain()
     torch.cuda.synchronize()
+    single_stream[0] = False
     stages = {name: (ms / max(calls, 1)) for name, ms, calls in C.prof_collect(True) if calls > 0}
     C.prof_enable(False)
     peak, peak_src = hbm_peak()
@@ -312,8 +343,8 @@ def main():
         "bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": sb[dom], "avg_launch_ms": round(kern[dom], 5),
-        "timing": f"CUDA events around every stage on the launching stream, {prof_steps} steps right after the timed "
-                  "region",
+        "timing": f"CUDA events around every stage on the launching stream, {prof_steps} single-stream steps right "
+                  "after the timed region",
         "stage_ms": {k: round(v, 5) for k, v in stages.items()},
         "stage_frac_of_hbm_peak": {k: round(sb[k] / (v * 1e-3) / 1e9 / peak, 4) for k, v in kern.items()},
         "view": {"algorithmic_bytes": vb, "achieved_gbs": round(vb / (per_view_ms * 1e-3) / 1e9, 1),

@@ -18,7 +18,7 @@ namespace das3r {
 // holds a DIFFERENT (pixel, Gaussian) pair that really contributes, evaluates backward.cu:490-554 for it and adds the 9
 // partial gradients to the Gaussian's 48-byte accumulator with two 128-bit and one 32-bit no-return atomics
 // (REDG.E.ADD.F32x4) instead of the reference's nine scalar ones.
-__global__ void __launch_bounds__(32 * BLEND_WARPS) blend_bwd_kernel(
+__global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
     unsigned gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, float* __restrict__ acc_out) {
@@ -78,7 +78,10 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_bwd_kernel(
                 if (!(alpha < 1.0f / 255.0f)) {
                     const float4 col4 = r.C;
                     const float col[3] = {col4.x, col4.y, col4.z};
-                    T = T / (1.f - alpha);
+                    // one IEEE reciprocal of (1 - alpha) serves both divisions of backward.cu:503,:534 (gradients are
+                    // compared at 1e-3; the forward's T and alpha decisions are not touched by this)
+                    const float inv_1ma = __frcp_rn(1.f - alpha);
+                    T = T * inv_1ma;
                     const float dchannel_dcolor = alpha * T;
                     float dL_dalpha = 0.0f;
                     float gcol[3];
@@ -93,7 +96,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_bwd_kernel(
                     }
                     dL_dalpha *= T;
                     last_alpha = alpha;
-                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                    dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
                     const float dL_dG = con_o.w * dL_dalpha;
                     const float gdx = G * d.x;
                     const float gdy = G * d.y;
