@@ -76,6 +76,9 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
     L->b_sA = c.take(n * 16);  // float4[R]  {x, y, h, -tau'}
     L->b_sB = c.take(n * 32);  // float4[R][2] {conic, opacity} {rgb, gaussian index}
     L->b_sC = L->b_sB + 16;
+    L->b_rect_off = c.take((size_t)T * 8 * 4);   // uint32[T*8] start of each rectangle's list
+    L->b_rect_cnt = c.take((size_t)T * 8 * 4);   // uint32[T*8] its length
+    L->b_rect_list = c.take(n * 8 * 4);          // uint32, capacity 8 per instance (an entry reaches <= 8 rectangles)
     L->b_keys_sorted = with_keys ? c.take(n * 8) : (size_t)0;
     X->fallback_bytes = with_fallback ? tile_sort_fallback_bytes(R, T) : 0;
     X->b_fallback = with_fallback ? c.take(X->fallback_bytes) : 0;
@@ -85,10 +88,10 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
 // ---- optional per-stage CUDA-event timing + kernel launch counter (bench.py's roofline leg) ------------------------
 enum Stage {
     ST_PREPROCESS_FWD = 0, ST_TILE_SCAN, ST_SCATTER, ST_TILE_SORT, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
-    ST_MEMSET, ST_COUNT
+    ST_MEMSET, ST_RECT_LISTS, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "blend_fwd",
-                                           "blend_bwd", "preprocess_bwd", "memset"};
+                                           "blend_bwd", "preprocess_bwd", "memset", "rect_lists"};
 struct Pending {
     int stage;
     cudaEvent_t a, b;
@@ -302,6 +305,9 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     uint32_t* point_list = reinterpret_cast<uint32_t*>(bin + L.b_point_list);
     float4* sA = reinterpret_cast<float4*>(bin + L.b_sA);
     float4* sBC = reinterpret_cast<float4*>(bin + L.b_sB);
+    uint32_t* rect_off = reinterpret_cast<uint32_t*>(bin + L.b_rect_off);
+    uint32_t* rect_cnt = reinterpret_cast<uint32_t*>(bin + L.b_rect_cnt);
+    uint32_t* rect_list = reinterpret_cast<uint32_t*>(bin + L.b_rect_list);
     uint64_t* keys_sorted = params->debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
 
     if (R > 0) {
@@ -314,7 +320,10 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
                                             bin + X.b_fallback, X.fallback_bytes, stream),
                   "tile_sort_fallback", ST_TILE_SORT, 3);
     }
-    STAGE(launch_blend_fwd(gx, gy, ranges, sA, sBC, rec, W, H, params->background, final_T, n_contrib, out->out_color,
+    if (R > 0)
+        STAGE(launch_rect_lists(T, gx, ranges, sA, rect_off, rect_cnt, rect_list, stream), "rect_lists",
+              ST_RECT_LISTS, 1);
+    STAGE(launch_blend_fwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, rec, W, H, params->background, final_T, n_contrib, out->out_color,
                            out->out_depth, out->out_alpha, stream),
           "blend_fwd", ST_BLEND_FWD, 1);
     return R;
@@ -359,7 +368,10 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     if (R > 0) {
         const float4* sA = reinterpret_cast<const float4*>(state->binning + L.b_sA);
         const float4* sBC = reinterpret_cast<const float4*>(state->binning + L.b_sB);
-        STAGE(launch_blend_bwd(gx, gy, ranges, sA, sBC, W, H, params->background, final_T, n_contrib,
+        const uint32_t* rect_off = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_off);
+        const uint32_t* rect_cnt = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_cnt);
+        const uint32_t* rect_list = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_list);
+        STAGE(launch_blend_bwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, params->background, final_T, n_contrib,
                                dL_dpix, g->scratch, stream),
               "blend_bwd", ST_BLEND_BWD, 1);
     }

@@ -13,27 +13,27 @@
 
 namespace das3r {
 
-// Walks the tile list back to front with the same three levels as blend_fwd (warp-rectangle ballot + ring compaction,
-// per-lane power >= -tau' scan into a register queue, lockstep drain), every warp on its own. In the drain every lane
-// holds a DIFFERENT (pixel, Gaussian) pair that really contributes, evaluates backward.cu:490-554 for it and adds the 9
-// partial gradients to the Gaussian's 48-byte accumulator with two 128-bit and one 32-bit no-return atomics
-// (REDG.E.ADD.F32x4) instead of the reference's nine scalar ones.
+// blend_bwd (replaces renderCUDA, backward.cu:399-557): walks the rectangle's list back to front (see
+// blend_common.cuh) from the warp's highest `n_contrib`. In the blend step every lane holds a DIFFERENT
+// (pixel, Gaussian) pair that really contributes, evaluates backward.cu:490-554 for it and adds the 9 partial gradients
+// to the Gaussian's 48-byte accumulator with two 128-bit and one 32-bit no-return atomics (REDG.E.ADD.F32x4) instead of
+// the reference's nine scalar ones.
 __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
-    const uint2* __restrict__ ranges, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
+    const uint32_t* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
     unsigned gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, float* __restrict__ acc_out) {
-    __shared__ __align__(16) RingRec ring_all[BLEND_WARPS][RING];
-    const int lane = threadIdx.x & 31;
-    RingRec* ring = ring_all[threadIdx.x >> 5];
+    __shared__ __align__(16) BlendSmem sm;
+    const int warp = threadIdx.x >> 5;
     const WarpRect wr = warp_rect(W, H, gx);
     const uint2 range = ranges[wr.tile];
-    const int n = (int)(range.y - range.x);
-    if (n == 0) return;
+    if (range.y == range.x) return;
+    const int cnt = (int)rect_cnt[wr.tile * 8 + wr.rect];
+    if (cnt == 0) return;
+    const uint32_t off = rect_off[wr.tile * 8 + wr.rect];
     const int pix_id = W * wr.py + wr.px;
     const bool inside = wr.inside;
     const float2 pixf = {(float)wr.px, (float)wr.py};
-    const float rx0 = (float)wr.wx0, rx1 = (float)(wr.wx0 + 7), ry0 = (float)wr.wy0, ry1 = (float)(wr.wy0 + 3);
-    const unsigned lt_mask = (1u << lane) - 1u;
 
     // backward.cu:431-458
     const float T_final = inside ? final_Ts[pix_id] : 0;
@@ -53,127 +53,65 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
     for (int i = 0; i < 3; i++) bg_dot_dpixel += bg[i] * dL_dpixel[i];
 
     // Highest list position any pixel of this warp still needs: everything behind it is skipped.
-    uint32_t wmax = last_contributor;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
     if (wmax == 0) return;
 
-    uint64_t q = 0;
-    int cnt = 0;
-    uint32_t ring_head = 0, ring_free_from = 0;
-
-    auto drain = [&]() {
-#pragma unroll 1
-        for (int k = 0; k < QCAP; k++) {
-            if (__ballot_sync(0xffffffffu, k < cnt) == 0) break;
-            if (k < cnt) {
-                const RingRec& r = ring[(uint32_t)(q >> (8 * k)) & 0xffu];
-                // backward.cu:490-554
-                const float4 A = r.A;
-                const float4 con_o = r.B;
-                const float2 d = {A.x - pixf.x, A.y - pixf.y};
-                const float power = splat_power(con_o, d);
-                const float G = expf(power);
-                const float alpha = min(0.99f, __fmul_rn(con_o.w, G));
-                if (!(alpha < 1.0f / 255.0f)) {
-                    const float4 col4 = r.C;
-                    const float col[3] = {col4.x, col4.y, col4.z};
-                    // one IEEE reciprocal of (1 - alpha) serves both divisions of backward.cu:503,:534 (gradients are
-                    // compared at 1e-3; the forward's T and alpha decisions are not touched by this)
-                    const float inv_1ma = __frcp_rn(1.f - alpha);
-                    T = T * inv_1ma;
-                    const float dchannel_dcolor = alpha * T;
-                    float dL_dalpha = 0.0f;
-                    float gcol[3];
-#pragma unroll
-                    for (int ch = 0; ch < 3; ch++) {
-                        const float c = col[ch];
-                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                        last_color[ch] = c;
-                        const float dL_dchannel = dL_dpixel[ch];
-                        dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
-                        gcol[ch] = dchannel_dcolor * dL_dchannel;
-                    }
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
-                    const float dL_dG = con_o.w * dL_dalpha;
-                    const float gdx = G * d.x;
-                    const float gdy = G * d.y;
-                    const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-                    const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-                    float* dst = acc_out + (size_t)__float_as_uint(col4.w) * ACC_STRIDE;
-                    atomicAdd(reinterpret_cast<float4*>(dst),
-                              make_float4(dL_dG * dG_ddelx * ddelx_dx, dL_dG * dG_ddely * ddely_dy,
-                                          -0.5f * gdx * d.x * dL_dG, -0.5f * gdx * d.y * dL_dG));
-                    atomicAdd(reinterpret_cast<float4*>(dst) + 1,
-                              make_float4(-0.5f * gdy * d.y * dL_dG, G * dL_dalpha, gcol[0], gcol[1]));
-                    atomicAdd(dst + 8, gcol[2]);
-                }
-            }
-        }
-        q = 0;
-        cnt = 0;
-    };
-
-    const float4* gA = sA + range.x;
-    const float4* gBC = sBC + 2 * (size_t)range.x;
-    const int nn = min(n, (int)wmax);  // list positions >= wmax are behind every pixel's last contributor
-    int c0 = ((nn - 1) / 32) * 32;
-    float4 a_next = make_float4(0.f, 0.f, -1.f, 0.f);
-    if (c0 + lane < nn) a_next = gA[c0 + lane];
-    for (; c0 >= 0; c0 -= 32) {
-        const float4 a = a_next;
-        const int g = c0 + lane;
-        if (c0 >= 32) a_next = gA[g - 32];
-        const bool ov = (g < nn) && (a.z >= 0.f) && (a.x + a.z >= rx0) && (a.x - a.z <= rx1) && (a.y + a.z >= ry0) &&
-                        (a.y - a.z <= ry1);
-        const unsigned m = __ballot_sync(0xffffffffu, ov);
-        if (m == 0) continue;
-        const int ns = __popc(m);
-        if (ring_head + (uint32_t)ns - ring_free_from > (uint32_t)RING) {
-            drain();
-            ring_free_from = ring_head;
-        }
-        if (ov) {
-            // back to front: the highest list position of the chunk goes first
-            RingRec& r = ring[(ring_head + (uint32_t)(ns - 1 - __popc(m & lt_mask))) % RING];
-            r.A = make_float4(a.x, a.y, __uint_as_float((uint32_t)g), a.w);
-            cp_async_16(&r.B, gBC + 2 * g);
-            cp_async_16(&r.C, gBC + 2 * g + 1);
-        }
-        cp_async_commit();
-        cp_async_wait_all();
-        __syncwarp();
-        for (int s_ = 0; s_ < ns; s_++) {
-            const uint32_t slot = (ring_head + (uint32_t)s_) % RING;
-            const float4 A = ring[slot].A;
-            const float4 con_o = ring[slot].B;
+    walk_rect_list<true>(
+        sm.ring[warp], sm.qpower[warp], sm.qslot[warp], rect_list + off, cnt, sA + range.x,
+        sBC + 2 * (size_t)range.x, pixf, wmax, [&](uint32_t pos) { return pos < last_contributor; },
+        [&](const RingRec& r, const float power) {
+            // backward.cu:490-554
+            const float4 A = r.A;
+            const float4 con_o = r.B;
             const float2 d = {A.x - pixf.x, A.y - pixf.y};
-            const float power = splat_power(con_o, d);
-            if (__float_as_uint(A.z) < last_contributor && !(power > 0.0f) && power >= A.w) {
-                q |= (uint64_t)slot << (8 * cnt);
-                cnt++;
+            const float G = expf(power);
+            const float alpha = min(0.99f, __fmul_rn(con_o.w, G));
+            if (alpha < 1.0f / 255.0f) return;
+            const float4 col4 = r.C;
+            const float col[3] = {col4.x, col4.y, col4.z};
+            // one IEEE reciprocal of (1 - alpha) serves both divisions of backward.cu:503,:534 (gradients are
+            // compared at 1e-3; the forward's T and alpha decisions are not touched by this)
+            const float inv_1ma = __frcp_rn(1.f - alpha);
+            T = T * inv_1ma;
+            const float dchannel_dcolor = alpha * T;
+            float dL_dalpha = 0.0f;
+            float gcol[3];
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) {
+                const float c = col[ch];
+                accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                last_color[ch] = c;
+                const float dL_dchannel = dL_dpixel[ch];
+                dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
+                gcol[ch] = dchannel_dcolor * dL_dchannel;
             }
-            if (__ballot_sync(0xffffffffu, cnt == QCAP) != 0) {
-                drain();
-                ring_free_from = ring_head;
-            }
-        }
-        ring_head += (uint32_t)ns;
-        __syncwarp();
-    }
-    drain();
+            dL_dalpha *= T;
+            last_alpha = alpha;
+            dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
+            const float dL_dG = con_o.w * dL_dalpha;
+            const float gdx = G * d.x;
+            const float gdy = G * d.y;
+            const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
+            const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
+            float* dst = acc_out + (size_t)__float_as_uint(col4.w) * ACC_STRIDE;
+            atomicAdd(reinterpret_cast<float4*>(dst),
+                      make_float4(dL_dG * dG_ddelx * ddelx_dx, dL_dG * dG_ddely * ddely_dy, -0.5f * gdx * d.x * dL_dG,
+                                  -0.5f * gdx * d.y * dL_dG));
+            atomicAdd(reinterpret_cast<float4*>(dst) + 1,
+                      make_float4(-0.5f * gdy * d.y * dL_dG, G * dL_dalpha, gcol[0], gcol[1]));
+            atomicAdd(dst + 8, gcol[2]);
+        },
+        [&]() { return false; });
 }
 
-cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC, int W,
-                             int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
+cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
+                             const uint32_t* rect_cnt, const uint32_t* rect_list, const float4* sA, const float4* sBC,
+                             int W, int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
                              const float* dL_dpix, float* acc, cudaStream_t s) {
     const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)blocks, 32 * BLEND_WARPS,
-                                       sizeof(RingRec) * BLEND_WARPS * RING);
-    blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, sA, sBC, W, H, gx, bg, final_T, n_contrib, dL_dpix,
-                                                           acc);
+    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)blocks, 32 * BLEND_WARPS, sizeof(BlendSmem));
+    blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, gx, bg,
+                                                           final_T, n_contrib, dL_dpix, acc);
     return cudaGetLastError();
 }
 

@@ -789,127 +789,104 @@ cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// blend_fwd. Every warp owns one 8x4 pixel rectangle of one tile (one lane per pixel) and streams through the tile's
-// depth-sorted list on its own - no block-level barrier anywhere, so a warp never waits for a neighbour whose pixels
-// happen to see more Gaussians (depth order correlates with screen position, which made lock-step batches lopsided).
-// The list is walked in three levels so that the expensive part only runs on pairs that contribute:
-//   1. warp level: 32 list entries at a time, one per lane, read with one coalesced 512-byte load of the compact
-//      {x, y, h, -tau'} stream (next chunk prefetched in registers), are tested against the warp's rectangle with the
-//      conservative radius h -> ballot. Survivors' remaining 32 bytes are fetched by their own lanes and the records
-//      are compacted, in list order, into a per-warp shared-memory ring;
-//   2. lane level ("scan"): for each survivor every lane evaluates only the quadratic form `power` (bit-identical
-//      to the reference expression) and keeps the ring slot iff power >= -tau', i.e. iff alpha >= 1/255 is possible
-//      (tau' = ln(255*opacity) with a safety margin): a pair rejected here is one the reference skips at forward.cu:340;
-//   3. lane level ("drain"): kept slots sit in an 8-entry per-lane register queue and are blended, in list order, by
-//      all lanes in lockstep - exp, alpha clamp, transmittance test and colour accumulation exactly as forward.cu:330-361.
-// The front-to-back recurrence per pixel, `n_contrib` (list positions) and the early termination are unchanged.
+// rect_lists: for every tile and each of its eight 8x4 pixel rectangles, the ordered list of tile-list positions of
+// the Gaussians whose conservative radius reaches the rectangle. One block per tile, warp w builds rectangle w's list
+// by ballot compaction in a single pass (four chunks of 32 entries in flight per round); rectangle w of a tile with n
+// entries owns the n slots starting at 8*range.x + w*n of the output array, so no counting pass or atomics are needed.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rect_lists_kernel(const uint2* __restrict__ ranges,
+                                                         const float4* __restrict__ sA, unsigned gx,
+                                                         uint32_t* __restrict__ rect_off,
+                                                         uint32_t* __restrict__ rect_cnt,
+                                                         uint32_t* __restrict__ rect_list) {
+    const int tile = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+    const int tx = tile % gx, ty = tile / gx;
+    const float4* gA = sA + range.x;
+    const uint32_t off = 8u * range.x + (uint32_t)w * (uint32_t)n;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    uint32_t run = 0;
+    for (int c0 = 0; c0 < n; c0 += 128) {
+        float4 a[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int g = c0 + 32 * u + lane;
+            a[u] = (g < n) ? gA[g] : make_float4(0.f, 0.f, -1.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const bool ov = reaches_rect(a[u], tx, ty, w);
+            const unsigned m = __ballot_sync(0xffffffffu, ov);
+            if (ov) rect_list[off + run + __popc(m & lt_mask)] = (uint32_t)(c0 + 32 * u + lane);
+            run += __popc(m);
+        }
+    }
+    if (lane == 0) {
+        rect_off[tile * 8 + w] = off;
+        rect_cnt[tile * 8 + w] = run;
+    }
+}
+
+cudaError_t launch_rect_lists(int T, unsigned gx, const uint2* ranges, const float4* sA, uint32_t* rect_off,
+                              uint32_t* rect_cnt, uint32_t* rect_list, cudaStream_t s) {
+    rect_lists_kernel<<<T, 256, 0, s>>>(ranges, sA, gx, rect_off, rect_cnt, rect_list);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// blend_fwd (replaces renderCUDA, forward.cu:261-374): see blend_common.cuh for the walk. The blend step is exactly
+// forward.cu:330-361 - exp, alpha clamp at 0.99, skip below 1/255, stop when T would drop under 1e-4, colour
+// accumulation - with the reference's FMA contraction pinned, so the front-to-back recurrence per pixel, `final_T`,
+// `n_contrib` (list positions) and the image are bit-identical; the early termination is per warp (ballot).
 // ---------------------------------------------------------------------------------------------------------------
 template <bool EXTRAS>
 __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
-    const uint2* __restrict__ ranges, const float4* __restrict__ sA, const float4* __restrict__ sBC,
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
+    const uint32_t* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC,
     const GaussRec* __restrict__ rec_by_id, int W, int H, unsigned gx, const float* __restrict__ bg,
     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
     float* __restrict__ out_depth, float* __restrict__ out_alpha) {
-    __shared__ __align__(16) RingRec ring_all[BLEND_WARPS][RING];
-    const int lane = threadIdx.x & 31;
-    RingRec* ring = ring_all[threadIdx.x >> 5];
+    __shared__ __align__(16) BlendSmem sm;
+    const int warp = threadIdx.x >> 5;
     const WarpRect wr = warp_rect(W, H, gx);
     const uint2 range = ranges[wr.tile];
-    const int n = (int)(range.y - range.x);
+    const int cnt = (range.y > range.x) ? (int)rect_cnt[wr.tile * 8 + wr.rect] : 0;
+    const uint32_t off = cnt ? rect_off[wr.tile * 8 + wr.rect] : 0u;
     const float2 pixf = {(float)wr.px, (float)wr.py};
-    const float rx0 = (float)wr.wx0, rx1 = (float)(wr.wx0 + 7), ry0 = (float)wr.wy0, ry1 = (float)(wr.wy0 + 3);
-    const unsigned lt_mask = (1u << lane) - 1u;
 
     bool done = !wr.inside;
     float T = 1.0f;
     uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     float Dz = 0.f;
-    uint64_t q = 0;  // up to QCAP ring slots, 8 bits each, oldest in the low byte
-    int cnt = 0;
-    uint32_t ring_head = 0, ring_free_from = 0;  // slots [ring_free_from, ring_head) may still be queued
 
-    auto drain = [&]() {
-#pragma unroll 1
-        for (int i = 0; i < QCAP; i++) {
-            if (__ballot_sync(0xffffffffu, i < cnt) == 0) break;
-            if (i < cnt && !done) {
-                const RingRec& r = ring[(uint32_t)(q >> (8 * i)) & 0xffu];
-                const float4 A = r.A;
-                const float4 con_o = r.B;
-                const float2 d = {A.x - pixf.x, A.y - pixf.y};
-                const float power = splat_power(con_o, d);
-                // forward.cu:339-361 (power <= 0 is guaranteed by the scan)
-                const float alpha = min(0.99f, __fmul_rn(con_o.w, expf(power)));
-                if (!(alpha < 1.0f / 255.0f)) {
-                    const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-                    if (test_T < 0.0001f) {
-                        done = true;
-                    } else {
-                        const float4 col = r.C;
-                        C[0] = __fmaf_rn(T, __fmul_rn(col.x, alpha), C[0]);
-                        C[1] = __fmaf_rn(T, __fmul_rn(col.y, alpha), C[1]);
-                        C[2] = __fmaf_rn(T, __fmul_rn(col.z, alpha), C[2]);
-                        if (EXTRAS) {
-                            const float z = rec_by_id[__float_as_uint(col.w)].C.w;
-                            Dz = __fmaf_rn(T, __fmul_rn(z, alpha), Dz);
-                        }
-                        T = test_T;
-                        last_contributor = __float_as_uint(A.z) + 1u;
-                    }
-                }
+    walk_rect_list<false>(
+        sm.ring[warp], sm.qpower[warp], sm.qslot[warp], rect_list + off, cnt, sA + range.x,
+        sBC + 2 * (size_t)range.x, pixf, 0xffffffffu, [&](uint32_t) { return !done; },
+        [&](const RingRec& r, const float power) {
+            if (done) return;
+            const float4 con_o = r.B;
+            // forward.cu:339-361 (power <= 0 is guaranteed by the scan)
+            const float alpha = min(0.99f, __fmul_rn(con_o.w, expf(power)));
+            if (alpha < 1.0f / 255.0f) return;
+            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+            if (test_T < 0.0001f) {
+                done = true;
+                return;
             }
-        }
-        q = 0;
-        cnt = 0;
-    };
-
-    const float4* gA = sA + range.x;
-    const float4* gBC = sBC + 2 * (size_t)range.x;
-    float4 a_next = make_float4(0.f, 0.f, -1.f, 0.f);
-    if (lane < n) a_next = gA[lane];
-    for (int c0 = 0; c0 < n; c0 += 32) {
-        const float4 a = a_next;
-        const int g = c0 + lane;
-        if (g + 32 < n) a_next = gA[g + 32];
-        const bool ov = (g < n) && (a.z >= 0.f) && (a.x + a.z >= rx0) && (a.x - a.z <= rx1) && (a.y + a.z >= ry0) &&
-                        (a.y - a.z <= ry1);
-        const unsigned m = __ballot_sync(0xffffffffu, ov);
-        if (m == 0) continue;
-        const int ns = __popc(m);
-        if (ring_head + (uint32_t)ns - ring_free_from > (uint32_t)RING) {
-            drain();  // frees every slot written before this chunk
-            ring_free_from = ring_head;
-        }
-        if (ov) {
-            RingRec& r = ring[(ring_head + __popc(m & lt_mask)) % RING];
-            r.A = make_float4(a.x, a.y, __uint_as_float((uint32_t)g), a.w);
-            cp_async_16(&r.B, gBC + 2 * g);  // LDGSTS: global -> ring without a register round trip
-            cp_async_16(&r.C, gBC + 2 * g + 1);
-        }
-        cp_async_commit();
-        cp_async_wait_all();
-        __syncwarp();
-        for (int s = 0; s < ns; s++) {
-            const uint32_t slot = (ring_head + (uint32_t)s) % RING;
-            const float4 A = ring[slot].A;
-            const float4 con_o = ring[slot].B;
-            const float2 d = {A.x - pixf.x, A.y - pixf.y};
-            const float power = splat_power(con_o, d);
-            if (!done && !(power > 0.0f) && power >= A.w) {
-                q |= (uint64_t)slot << (8 * cnt);
-                cnt++;
+            const float4 col = r.C;
+            C[0] = __fmaf_rn(T, __fmul_rn(col.x, alpha), C[0]);
+            C[1] = __fmaf_rn(T, __fmul_rn(col.y, alpha), C[1]);
+            C[2] = __fmaf_rn(T, __fmul_rn(col.z, alpha), C[2]);
+            if (EXTRAS) {
+                const float z = rec_by_id[__float_as_uint(col.w)].C.w;
+                Dz = __fmaf_rn(T, __fmul_rn(z, alpha), Dz);
             }
-            if (__ballot_sync(0xffffffffu, cnt == QCAP) != 0) {
-                drain();
-                ring_free_from = ring_head;  // this chunk's slots stay live
-            }
-        }
-        ring_head += (uint32_t)ns;
-        if (__ballot_sync(0xffffffffu, !done) == 0) break;  // forward.cu:309-311, per warp
-        __syncwarp();
-    }
-    drain();
+            T = test_T;
+            last_contributor = __float_as_uint(r.A.z) + 1u;
+        },
+        [&]() { return __ballot_sync(0xffffffffu, !done) == 0; });
 
     if (wr.inside) {
         const int pix_id = W * wr.py + wr.px;
@@ -924,20 +901,24 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     }
 }
 
-cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const float4* sA, const float4* sBC,
+cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
+                             const uint32_t* rect_cnt, const uint32_t* rect_list, const float4* sA, const float4* sBC,
                              const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
                              uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
                              cudaStream_t s) {
     const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    const size_t ring_bytes = sizeof(RingRec) * BLEND_WARPS * RING;
     if (out_depth || out_alpha) {
-        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<true>, (int)blocks, 32 * BLEND_WARPS, ring_bytes);
-        blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
-                                                                     n_contrib, out_color, out_depth, out_alpha);
+        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<true>, (int)blocks, 32 * BLEND_WARPS,
+                                           sizeof(BlendSmem));
+        blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
+                                                                     rec_by_id, W, H, gx, bg, final_T, n_contrib,
+                                                                     out_color, out_depth, out_alpha);
     } else {
-        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS, ring_bytes);
-        blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, sA, sBC, rec_by_id, W, H, gx, bg, final_T,
-                                                                      n_contrib, out_color, out_depth, out_alpha);
+        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS,
+                                           sizeof(BlendSmem));
+        blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
+                                                                      rec_by_id, W, H, gx, bg, final_T, n_contrib,
+                                                                      out_color, out_depth, out_alpha);
     }
     return cudaGetLastError();
 }
