@@ -78,7 +78,7 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
     L->b_sC = L->b_sB + 16;
     L->b_rect_off = c.take((size_t)T * 8 * 4);   // uint32[T*8] start of each rectangle's list
     L->b_rect_cnt = c.take((size_t)T * 8 * 4);   // uint32[T*8] its length
-    L->b_rect_list = c.take(n * 8 * 4);          // uint32, capacity 8 per instance (an entry reaches <= 8 rectangles)
+    L->b_rect_list = c.take(n * 8 * 8);          // uint2 {position, pixel mask}, capacity 8 per instance (<= 8 rectangles)
     L->b_keys_sorted = with_keys ? c.take(n * 8) : (size_t)0;
     X->fallback_bytes = with_fallback ? tile_sort_fallback_bytes(R, T) : 0;
     X->b_fallback = with_fallback ? c.take(X->fallback_bytes) : 0;
@@ -307,7 +307,7 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     float4* sBC = reinterpret_cast<float4*>(bin + L.b_sB);
     uint32_t* rect_off = reinterpret_cast<uint32_t*>(bin + L.b_rect_off);
     uint32_t* rect_cnt = reinterpret_cast<uint32_t*>(bin + L.b_rect_cnt);
-    uint32_t* rect_list = reinterpret_cast<uint32_t*>(bin + L.b_rect_list);
+    uint2* rect_list = reinterpret_cast<uint2*>(bin + L.b_rect_list);
     uint64_t* keys_sorted = params->debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
 
     if (R > 0) {
@@ -321,7 +321,7 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
                   "tile_sort_fallback", ST_TILE_SORT, 3);
     }
     if (R > 0)
-        STAGE(launch_rect_lists(T, gx, ranges, sA, rect_off, rect_cnt, rect_list, stream), "rect_lists",
+        STAGE(launch_rect_lists(T, gx, W, H, ranges, sA, sBC, rect_off, rect_cnt, rect_list, stream), "rect_lists",
               ST_RECT_LISTS, 1);
     STAGE(launch_blend_fwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, rec, W, H, params->background, final_T, n_contrib, out->out_color,
                            out->out_depth, out->out_alpha, stream),
@@ -370,7 +370,7 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
         const float4* sBC = reinterpret_cast<const float4*>(state->binning + L.b_sB);
         const uint32_t* rect_off = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_off);
         const uint32_t* rect_cnt = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_cnt);
-        const uint32_t* rect_list = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_list);
+        const uint2* rect_list = reinterpret_cast<const uint2*>(state->binning + L.b_rect_list);
         STAGE(launch_blend_bwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, params->background, final_T, n_contrib,
                                dL_dpix, g->scratch, stream),
               "blend_bwd", ST_BLEND_BWD, 1);

@@ -20,10 +20,10 @@ namespace das3r {
 // the reference's nine scalar ones.
 __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
-    const uint32_t* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
+    const uint2* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
     unsigned gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, float* __restrict__ acc_out) {
-    __shared__ __align__(16) BlendSmem sm;
+    __shared__ __align__(16) BlendSmem<BWD_K> sm;
     const int warp = threadIdx.x >> 5;
     const WarpRect wr = warp_rect(W, H, gx);
     const uint2 range = ranges[wr.tile];
@@ -56,14 +56,16 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
     if (wmax == 0) return;
 
-    walk_rect_list<true>(
-        sm.ring[warp], sm.qpower[warp], sm.qslot[warp], rect_list + off, cnt, sA + range.x,
-        sBC + 2 * (size_t)range.x, pixf, wmax, [&](uint32_t pos) { return pos < last_contributor; },
-        [&](const RingRec& r, const float power) {
+    walk_rect_list<true, BWD_K>(
+        sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, wmax,
+        [&]() { return last_contributor != 0u; },
+        [&](const RingRec& r) {
             // backward.cu:490-554
             const float4 A = r.A;
+            if (__float_as_uint(A.z) >= last_contributor) return;  // behind this pixel's last contributor
             const float4 con_o = r.B;
             const float2 d = {A.x - pixf.x, A.y - pixf.y};
+            const float power = splat_power(con_o, d);
             const float G = expf(power);
             const float alpha = min(0.99f, __fmul_rn(con_o.w, G));
             if (alpha < 1.0f / 255.0f) return;
@@ -100,16 +102,15 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
             atomicAdd(reinterpret_cast<float4*>(dst) + 1,
                       make_float4(-0.5f * gdy * d.y * dL_dG, G * dL_dalpha, gcol[0], gcol[1]));
             atomicAdd(dst + 8, gcol[2]);
-        },
-        [&]() { return false; });
+        });
 }
 
 cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint32_t* rect_list, const float4* sA, const float4* sBC,
+                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
                              int W, int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
                              const float* dL_dpix, float* acc, cudaStream_t s) {
     const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)blocks, 32 * BLEND_WARPS, sizeof(BlendSmem));
+    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)blocks, 32 * BLEND_WARPS, sizeof(BlendSmem<BWD_K>));
     blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, gx, bg,
                                                            final_T, n_contrib, dL_dpix, acc);
     return cudaGetLastError();

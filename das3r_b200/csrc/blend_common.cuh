@@ -1,33 +1,34 @@
 // Pieces shared by the forward and backward blend kernels.
 //
 // Work decomposition: every 16x16 tile is cut into eight 8x4 pixel rectangles; one warp owns one rectangle (one lane
-// per pixel) and walks, on its own (no block barrier), the RECT LIST of that rectangle: the positions, in the tile's
-// depth-sorted list, of the Gaussians whose conservative radius h reaches the rectangle. The lists are built once per
-// forward by rect_lists_kernel and used by both the forward and the backward blend (before, each of the 8 warps of a
-// tile re-derived its list by scanning the whole tile list in both passes).
+// per pixel) and walks, on its own (no block barrier), the RECT LIST of that rectangle. rect_lists_kernel builds the
+// lists once per forward; both blend passes use them. A list entry is {position in the tile's depth-sorted list,
+// 32-bit PIXEL MASK}: bit p is set iff the pair (entry, pixel p of the rectangle) can reach alpha >= 1/255, decided with
+// the blend's own fp32 `power` expression (power <= 0 and power >= -tau', tau' = ln(255*opacity) plus a margin). A pair
+// whose bit is clear is one the reference skips at forward.cu:340 / backward.cu:499; entries with an empty mask are not
+// listed at all.
 //
-// Walking a list:
-//   gather  - 32 entries at a time, every lane fetches one entry's record into a per-warp shared-memory ring
-//             ({x, y, position, -tau'} through registers, the other 32 bytes with cp.async);
-//   scan    - for each ring entry every lane evaluates only the quadratic form `power` (bit-identical to the reference
-//             expression) and appends the entry to ITS OWN list iff power >= -tau', i.e. iff alpha >= 1/255 is possible
-//             for its pixel (tau' = ln(255*opacity) with a safety margin): a pair rejected here is one the reference
-//             skips at forward.cu:340 / backward.cu:499;
-//   blend   - listed (slot, power) pairs sit in a per-lane queue of 8 entries in shared memory; when a lane's queue is
-//             full, or the ring is about to be overwritten, all lanes blend their queued entries in lockstep, in list
-//             order. (Depth order correlates with screen position, so at any moment only a few pixels of the rectangle
-//             receive entries and the lockstep blend runs at ~20 % lane utilisation. A variant with 64-entry per-lane
-//             lists blended once at the end reaches ~78 % but has to re-fetch every record per lane from L1/L2 and
-//             measured 40 % slower; see DESIGN.md.)
+// Walking a list (walk_rect_list):
+//   gather   - 32 entries at a time, every lane starts the copy of one entry's 48-byte record into a per-warp
+//              shared-memory ring of K chunks with cp.async (LDGSTS, no register round trip) and the warp transposes
+//              the 32 pixel masks (5 shuffle stages), so that every lane ends up with the bitmask of the chunk's
+//              entries that touch ITS pixel; the masks go to a small per-lane table in shared memory;
+//   blend    - every lane pops the lowest set bit of its current mask and blends that ring record; lanes move on to
+//              their next chunk on their own, so a pixel with many contributions in one chunk does not hold the others
+//              back as long as the ring (a sliding window of K chunks) still has records for them. One chunk is always
+//              in flight while the others are blended.
+// History: per-pixel evaluation of `power` for every ring entry inside the blend kernels plus an
+// 8-entry per-lane queue spent ~half of the instructions on the test and ran the blend at ~20 % lane utilisation,
+// because depth order correlates with screen position.
 #pragma once
 #include "common.cuh"
 
 namespace das3r {
 
 constexpr int BLEND_WARPS = 2;   // warps per block
-constexpr int CHUNK = 32;        // list entries gathered and scanned per round (one per lane)
-constexpr int RING = 2 * CHUNK;  // per-warp ring of gathered records: the current chunk and the previous one
-constexpr int QCAP = 8;          // per-lane queue capacity (ring slots waiting for the blend step)
+constexpr int CHUNK = 32;        // list entries gathered per round (one per lane)
+constexpr int FWD_K = 4;         // ring depth (chunks) of the forward / backward blend
+constexpr int BWD_K = 4;
 
 struct RingRec {
     float4 A;  // {x, y, tile-list position (bits), -tau'}
@@ -35,10 +36,10 @@ struct RingRec {
     float4 C;  // {r, g, b, gaussian index (bits)}
 };
 
+template <int K>
 struct BlendSmem {
-    RingRec ring[BLEND_WARPS][RING];
-    float qpower[BLEND_WARPS][QCAP * 32];  // [entry][lane]: the pair's `power`, evaluated once in the scan
-    uint8_t qslot[BLEND_WARPS][QCAP * 32];  // [entry][lane]: ring slot of the queued entry
+    RingRec ring[BLEND_WARPS][K * CHUNK];
+    uint32_t qmask[BLEND_WARPS][K * 32];  // [chunk slot][lane]: which of the chunk's entries touch the lane's pixel
 };
 
 // power = -0.5f*(c.x*d.x*d.x + c.z*d.y*d.y) - c.y*d.x*d.y with the contraction ptxas chose for the reference's
@@ -77,94 +78,108 @@ __device__ __forceinline__ bool reaches_rect(const float4& A, int tx, int ty, in
            (A.y - A.z <= ry0 + 3.f);
 }
 
+// Transposes the 32x32 bit matrix held one row per lane: on return, bit e of lane p's word is bit p of lane e's input.
+__device__ __forceinline__ uint32_t transpose_bits(uint32_t x, int lane) {
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        const uint32_t msk = (j == 16) ? 0x0000ffffu : (j == 8) ? 0x00ff00ffu : (j == 4) ? 0x0f0f0f0fu
+                           : (j == 2) ? 0x33333333u : 0x55555555u;
+        const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+        x = (lane & j) ? ((x & ~msk) | ((y >> j) & msk)) : ((x & msk) | ((y & msk) << j));
+    }
+    return x;
+}
+
 // Walks list[0..cnt) (REVERSE: from the end) as described at the top of this file.
-//   keep(pos)           per-lane extra condition for queueing tile-list position `pos` (forward: pixel not finished;
-//                       backward: pos < the pixel's last contributor)
-//   blend(rec, power)   per-lane blend step for one queued record; `power` is the value the scan computed
-//   finished()          warp-uniform early exit test, evaluated after every chunk
-//   pos_limit           no lane needs list positions >= pos_limit: chunks entirely beyond it are skipped (backward)
-template <bool REVERSE, typename Keep, typename Blend, typename Finished>
-__device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, float* __restrict__ qpower,
-                                               uint8_t* __restrict__ qslot, const uint32_t* __restrict__ list, int cnt,
+//   keep()        per-lane: does this lane still want records? (forward: pixel not finished)
+//   blend(rec)    per-lane blend step for one record whose mask bit is set for this lane's pixel
+//   pos_limit     no lane needs tile-list positions >= pos_limit (backward: the warp's highest n_contrib)
+// Chunks are numbered in walk order; `iss` chunks have been started, `vis` of them have landed (records readable, masks
+// stored), at most one is in flight. A lane holds the unblended rest `m` of its mask of chunk nx-1. Chunk c lives in
+// ring slot c % K, so chunk `iss` may be started as soon as no lane needs chunk iss-K any more.
+template <bool REVERSE, int K, typename Keep, typename Blend>
+__device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint32_t* __restrict__ qmask,
+                                               const uint2* __restrict__ list, int cnt,
                                                const float4* __restrict__ gA, const float4* __restrict__ gBC,
-                                               const float2 pixf, const uint32_t pos_limit, Keep keep, Blend blend,
-                                               Finished finished) {
+                                               const uint32_t pos_limit, Keep keep, Blend blend) {
+    static_assert((K & (K - 1)) == 0, "K must be a power of two");
     const int lane = threadIdx.x & 31;
-    uint32_t qn = 0;          // this lane's queue length * 32 (offset of its next entry row)
-    bool prev_live = false;   // may the previous chunk's half of the ring still be referenced by a queue?
-
-    auto drain = [&]() {
-        const uint32_t qmax = __reduce_max_sync(0xffffffffu, qn);
-        for (uint32_t i = 0; i < qmax; i += 32) {
-            if (i < qn) blend(ring[qslot[i + lane]], qpower[i + lane]);
-        }
-        qn = 0;
-        prev_live = false;
-    };
-
     const int nchunks = (cnt + CHUNK - 1) / CHUNK;
     if (nchunks == 0) return;
-    int c = REVERSE ? nchunks - 1 : 0;
-    const int step = REVERSE ? -1 : 1;
-    // software pipeline: list entries two chunks ahead, record heads one chunk ahead
-    uint32_t li = (c * CHUNK + lane < cnt) ? list[c * CHUNK + lane] : 0u;
-    float4 a = gA[li];
-    int cn = c + step;
-    uint32_t li_n = (cn >= 0 && cn < nchunks && cn * CHUNK + lane < cnt) ? list[cn * CHUNK + lane] : 0u;
-    uint32_t half = 0;  // which half of the ring the current chunk uses
-    for (int it = 0; it < nchunks; it++, c += step) {
-        const uint32_t li_c = li;
-        const float4 a_c = a;
-        li = li_n;
-        if (it + 1 < nchunks) a = gA[li];
-        cn = c + 2 * step;
-        li_n = (cn >= 0 && cn < nchunks && cn * CHUNK + lane < cnt) ? list[cn * CHUNK + lane] : 0u;
-
+    constexpr int step = REVERSE ? -1 : 1;
+    // this lane's entry of list chunk c, in walk order; {~0, 0} where there is none
+    auto load_entry = [&](int c) -> uint2 {
+        if (c < 0 || c >= nchunks) return make_uint2(0xffffffffu, 0u);
         const int ns = min(CHUNK, cnt - c * CHUNK);
-        if (__all_sync(0xffffffffu, lane >= ns || li_c >= pos_limit)) continue;  // nothing in this chunk is needed
-        RingRec* cur = ring + half * CHUNK;
-        if (lane < ns) {
-            // scan order = list order (REVERSE: descending positions)
-            RingRec& r = cur[REVERSE ? ns - 1 - lane : lane];
-            r.A = make_float4(a_c.x, a_c.y, __uint_as_float(li_c), a_c.w);
-            cp_async_16(&r.B, gBC + 2 * (size_t)li_c);  // LDGSTS: global -> ring, no register round trip
-            cp_async_16(&r.C, gBC + 2 * (size_t)li_c + 1);
+        return (lane < ns) ? list[c * CHUNK + (REVERSE ? ns - 1 - lane : lane)] : make_uint2(0xffffffffu, 0u);
+    };
+    int lc = REVERSE ? nchunks - 1 : 0;  // list chunk to start next
+    int left = nchunks;                  // list chunks not started yet
+    uint2 e_cur = load_entry(lc);
+    uint2 e_nxt = load_entry(lc + step);
+
+    uint32_t m = 0;
+    int nx = 0, vis = 0, iss = 0;
+    uint32_t pend_mask = 0, pend_pos = 0xffffffffu;
+
+    for (;;) {
+        if (!keep()) {
+            m = 0;
+            nx = vis;
         }
-        cp_async_commit();
-        cp_async_wait_all();
-        __syncwarp();
-        const uint32_t slot0 = half * CHUNK;
-        for (int s = 0; s < ns; s += 2) {
-            // up to two entries are queued per lane and round: keep two free slots in every lane's queue
-            if (__reduce_max_sync(0xffffffffu, qn) > (uint32_t)(QCAP - 2) * 32u) drain();
-#pragma unroll
-            for (int u = 0; u < 2; u++) {
-                if (s + u < ns) {
-                    const float4 A = cur[s + u].A;
-                    const float4 con_o = cur[s + u].B;
-                    const float2 d = {A.x - pixf.x, A.y - pixf.y};
-                    const float power = splat_power(con_o, d);
-                    if (!(power > 0.0f) && power >= A.w && keep(__float_as_uint(A.z))) {
-                        qslot[qn + lane] = (uint8_t)(slot0 + s + u);
-                        qpower[qn + lane] = power;
-                        qn += 32;
-                    }
-                }
+        while (m == 0 && nx < vis) {
+            m = qmask[(nx & (K - 1)) * 32 + lane];
+            nx++;
+        }
+        const bool idle = (m == 0);  // nothing landed is left for this lane
+        if (__all_sync(0xffffffffu, !keep())) break;
+        const int oldest = __reduce_min_sync(0xffffffffu, idle ? vis : nx - 1);  // lowest chunk still needed
+        const bool can_start = left > 0 && (iss - oldest < K);
+        if (iss > vis) {
+            if (can_start || oldest == vis) {
+                // land the chunk in flight
+                cp_async_wait_all();
+                const int slot = (vis & (K - 1)) * 32 + lane;
+                if (pend_pos != 0xffffffffu) ring[slot].A.z = __uint_as_float(pend_pos);
+                qmask[slot] = pend_mask;
+                __syncwarp();
+                vis++;
+                continue;
             }
+        } else if (can_start) {
+            // start the next list chunk that somebody needs
+            const bool valid = e_cur.x < pos_limit;
+            if (__any_sync(0xffffffffu, valid)) {
+                RingRec& r = ring[(iss & (K - 1)) * 32 + lane];
+                if (valid) {
+                    cp_async_16(&r.A, gA + e_cur.x);
+                    cp_async_16(&r.B, gBC + 2 * (size_t)e_cur.x);
+                    cp_async_16(&r.C, gBC + 2 * (size_t)e_cur.x + 1);
+                }
+                cp_async_commit();
+                pend_mask = transpose_bits(valid ? e_cur.y : 0u, lane);
+                pend_pos = valid ? e_cur.x : 0xffffffffu;
+                iss++;
+            }
+            lc += step;
+            left--;
+            e_cur = e_nxt;
+            e_nxt = load_entry(lc + step);
+            continue;
+        } else if (oldest == vis) {
+            break;  // nothing landed, nothing in flight, nothing left to start
         }
-        if (finished()) break;
-        // The next chunk overwrites the other half of the ring, i.e. the previous chunk's records: entries of that
-        // chunk that are still queued have to be blended first. Entries queued during this chunk may wait one more
-        // round (drain() empties every queue, so after it nothing of either chunk is pending).
-        if (prev_live) {
-            drain();
-        } else {
-            prev_live = true;
-        }
-        half ^= 1u;
-        __syncwarp();
+        // blend until a lane that had work runs out of it (only then can `oldest` move)
+        do {
+            if (m) {
+                const int bit = __ffs(m) - 1;
+                m &= m - 1;
+                blend(ring[((nx - 1) & (K - 1)) * 32 + bit]);
+                if (!keep()) m = 0;
+            }
+        } while (!__any_sync(0xffffffffu, m == 0 && !idle));
     }
-    drain();
+    cp_async_wait_all();  // never leave with a copy into this block's shared memory in flight
 }
 
 }  // namespace das3r

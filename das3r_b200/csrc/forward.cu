@@ -795,18 +795,63 @@ cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_
 // entries owns the n slots starting at 8*range.x + w*n of the output array, so no counting pass or atomics are needed.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) rect_lists_kernel(const uint2* __restrict__ ranges,
-                                                         const float4* __restrict__ sA, unsigned gx,
-                                                         uint32_t* __restrict__ rect_off,
+                                                         const float4* __restrict__ sA, const float4* __restrict__ sBC,
+                                                         unsigned gx, int W, int H, uint32_t* __restrict__ rect_off,
                                                          uint32_t* __restrict__ rect_cnt,
-                                                         uint32_t* __restrict__ rect_list) {
+                                                         uint2* __restrict__ rect_list) {
+    __shared__ uint32_t cand_s[8][256];  // per warp: circular buffer of tile-list positions that reach the rectangle
     const int tile = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
     const int tx = tile % gx, ty = tile / gx;
     const float4* gA = sA + range.x;
+    const float4* gBC = sBC + 2 * (size_t)range.x;
+    uint32_t* cand = cand_s[w];
     const uint32_t off = 8u * range.x + (uint32_t)w * (uint32_t)n;
     const unsigned lt_mask = (1u << lane) - 1u;
-    uint32_t run = 0;
+    const int rx0 = tx * TILE_X + (w & 1) * 8, ry0 = ty * TILE_Y + (w >> 1) * 4;
+    // pixels of the rectangle that exist in the image
+    uint32_t pix_valid = 0;
+    for (int r = 0; r < 4; r++)
+        for (int j = 0; j < 8; j++)
+            if (rx0 + j < W && ry0 + r < H) pix_valid |= 1u << (r * 8 + j);
+
+    uint32_t head = 0, tail = 0, run = 0;
+    // Pixel masks of `k` (<= 32) buffered candidates, one per lane; entries with a non-empty mask are appended.
+    auto emit = [&](int k) {
+        uint32_t pos = 0, mask = 0;
+        if (lane < k) {
+            pos = cand[(head + lane) & 255u];
+            const float4 A = gA[pos];
+            const float4 con_o = gBC[2 * (size_t)pos];
+            // splat_power() for the 32 pixels with the column / row factors hoisted (same operations, same rounding)
+            float dx[8], ax[8], bx[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                dx[j] = A.x - (float)(rx0 + j);
+                ax[j] = __fmul_rn(con_o.x, dx[j]);
+                bx[j] = __fmul_rn(con_o.y, dx[j]);
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const float dy = A.y - (float)(ry0 + r);
+                const float zz = __fmul_rn(__fmul_rn(con_o.z, dy), dy);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float sq = __fmaf_rn(ax[j], dx[j], zz);
+                    const float u = __fmul_rn(bx[j], dy);
+                    const float power = __fmaf_rn(sq, -0.5f, -u);
+                    if (!(power > 0.0f) && power >= A.w) mask |= 1u << (r * 8 + j);
+                }
+            }
+            mask &= pix_valid;
+        }
+        const unsigned b = __ballot_sync(0xffffffffu, mask != 0u);
+        if (mask) rect_list[off + run + __popc(b & lt_mask)] = make_uint2(pos, mask);
+        run += __popc(b);
+        head += (uint32_t)k;
+    };
+
     for (int c0 = 0; c0 < n; c0 += 128) {
         float4 a[4];
 #pragma unroll
@@ -818,19 +863,24 @@ __global__ void __launch_bounds__(256) rect_lists_kernel(const uint2* __restrict
         for (int u = 0; u < 4; u++) {
             const bool ov = reaches_rect(a[u], tx, ty, w);
             const unsigned m = __ballot_sync(0xffffffffu, ov);
-            if (ov) rect_list[off + run + __popc(m & lt_mask)] = (uint32_t)(c0 + 32 * u + lane);
-            run += __popc(m);
+            if (ov) cand[(tail + __popc(m & lt_mask)) & 255u] = (uint32_t)(c0 + 32 * u + lane);
+            tail += __popc(m);
         }
+        __syncwarp();
+        while (tail - head >= 32u) emit(32);
+        __syncwarp();
     }
+    if (tail != head) emit((int)(tail - head));
     if (lane == 0) {
         rect_off[tile * 8 + w] = off;
         rect_cnt[tile * 8 + w] = run;
     }
 }
 
-cudaError_t launch_rect_lists(int T, unsigned gx, const uint2* ranges, const float4* sA, uint32_t* rect_off,
-                              uint32_t* rect_cnt, uint32_t* rect_list, cudaStream_t s) {
-    rect_lists_kernel<<<T, 256, 0, s>>>(ranges, sA, gx, rect_off, rect_cnt, rect_list);
+cudaError_t launch_rect_lists(int T, unsigned gx, int W, int H, const uint2* ranges, const float4* sA,
+                              const float4* sBC, uint32_t* rect_off, uint32_t* rect_cnt, uint2* rect_list,
+                              cudaStream_t s) {
+    rect_lists_kernel<<<T, 256, 0, s>>>(ranges, sA, sBC, gx, W, H, rect_off, rect_cnt, rect_list);
     return cudaGetLastError();
 }
 
@@ -843,11 +893,11 @@ cudaError_t launch_rect_lists(int T, unsigned gx, const uint2* ranges, const flo
 template <bool EXTRAS>
 __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
-    const uint32_t* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC,
+    const uint2* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC,
     const GaussRec* __restrict__ rec_by_id, int W, int H, unsigned gx, const float* __restrict__ bg,
     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
     float* __restrict__ out_depth, float* __restrict__ out_alpha) {
-    __shared__ __align__(16) BlendSmem sm;
+    __shared__ __align__(16) BlendSmem<FWD_K> sm;
     const int warp = threadIdx.x >> 5;
     const WarpRect wr = warp_rect(W, H, gx);
     const uint2 range = ranges[wr.tile];
@@ -861,13 +911,14 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     float C[3] = {0.f, 0.f, 0.f};
     float Dz = 0.f;
 
-    walk_rect_list<false>(
-        sm.ring[warp], sm.qpower[warp], sm.qslot[warp], rect_list + off, cnt, sA + range.x,
-        sBC + 2 * (size_t)range.x, pixf, 0xffffffffu, [&](uint32_t) { return !done; },
-        [&](const RingRec& r, const float power) {
-            if (done) return;
+    walk_rect_list<false, FWD_K>(
+        sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, 0xffffffffu,
+        [&]() { return !done; },
+        [&](const RingRec& r) {
+            const float4 A = r.A;
             const float4 con_o = r.B;
-            // forward.cu:339-361 (power <= 0 is guaranteed by the scan)
+            const float power = splat_power(con_o, make_float2(A.x - pixf.x, A.y - pixf.y));
+            // forward.cu:339-361 (power <= 0 is guaranteed by the pixel mask)
             const float alpha = min(0.99f, __fmul_rn(con_o.w, expf(power)));
             if (alpha < 1.0f / 255.0f) return;
             const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
@@ -884,9 +935,8 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
                 Dz = __fmaf_rn(T, __fmul_rn(z, alpha), Dz);
             }
             T = test_T;
-            last_contributor = __float_as_uint(r.A.z) + 1u;
-        },
-        [&]() { return __ballot_sync(0xffffffffu, !done) == 0; });
+            last_contributor = __float_as_uint(A.z) + 1u;
+        });
 
     if (wr.inside) {
         const int pix_id = W * wr.py + wr.px;
@@ -902,20 +952,20 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
 }
 
 cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint32_t* rect_list, const float4* sA, const float4* sBC,
+                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
                              const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
                              uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
                              cudaStream_t s) {
     const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
     if (out_depth || out_alpha) {
         const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<true>, (int)blocks, 32 * BLEND_WARPS,
-                                           sizeof(BlendSmem));
+                                           sizeof(BlendSmem<FWD_K>));
         blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
                                                                      rec_by_id, W, H, gx, bg, final_T, n_contrib,
                                                                      out_color, out_depth, out_alpha);
     } else {
         const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS,
-                                           sizeof(BlendSmem));
+                                           sizeof(BlendSmem<FWD_K>));
         blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
                                                                       rec_by_id, W, H, gx, bg, final_T, n_contrib,
                                                                       out_color, out_depth, out_alpha);

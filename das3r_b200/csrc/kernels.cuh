@@ -70,10 +70,11 @@ size_t tile_sort_fallback_bytes(int R, int T);
 cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
                                       uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted, void* temp,
                                       size_t temp_bytes, cudaStream_t s);
-cudaError_t launch_rect_lists(int T, unsigned gx, const uint2* ranges, const float4* sA, uint32_t* rect_off,
-                              uint32_t* rect_cnt, uint32_t* rect_list, cudaStream_t s);
+cudaError_t launch_rect_lists(int T, unsigned gx, int W, int H, const uint2* ranges, const float4* sA,
+                              const float4* sBC, uint32_t* rect_off, uint32_t* rect_cnt, uint2* rect_list,
+                              cudaStream_t s);
 cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint32_t* rect_list, const float4* sA, const float4* sBC,
+                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
                              const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
                              uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
                              cudaStream_t s);
@@ -82,7 +83,7 @@ cudaError_t launch_mark_visible(int P, const float* means, const float* view, co
 
 // backward.cu
 cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint32_t* rect_list, const float4* sA, const float4* sBC,
+                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
                              int W, int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
                              const float* dL_dpix, float* acc, cudaStream_t s);
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);

@@ -189,7 +189,7 @@ typedef struct das3r_raster_state_layout {
     size_t b_sA;                     /* float4[R] tile-ordered {x, y, h, -tau'} */
     size_t b_sB, b_sC;               /* float4[R][2] tile-ordered, interleaved {conic, opacity} {rgb, gaussian index} */
     size_t b_rect_off, b_rect_cnt;   /* uint32[T*8]: start / length of the list of each 8x4 pixel rectangle */
-    size_t b_rect_list;              /* uint32[8*R] capacity: tile-list positions, per rectangle, in list order */
+    size_t b_rect_list;              /* uint2[8*R] capacity: {tile-list position, pixel mask} per rectangle, in list order */
     size_t binning_bytes;
 } das3r_raster_state_layout;
 int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
