@@ -18,6 +18,12 @@ namespace das3r {
 // (pixel, Gaussian) pair that really contributes, evaluates backward.cu:490-554 for it and adds the 9 partial gradients
 // to the Gaussian's 48-byte accumulator with two 128-bit and one 32-bit no-return atomics (REDG.E.ADD.F32x4) instead of
 // the reference's nine scalar ones.
+struct BwdPair {
+    float2 d;
+    float G, alpha, inv_1ma;
+    bool skip;
+};
+
 __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
     const uint2* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
@@ -60,20 +66,28 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
         sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, wmax,
         [&]() { return last_contributor != 0u; },
         [&](const RingRec& r) {
-            // backward.cu:490-554
+            // backward.cu:490-500: everything that does not depend on the pixel's running state
+            BwdPair x;
             const float4 A = r.A;
-            if (__float_as_uint(A.z) >= last_contributor) return;  // behind this pixel's last contributor
             const float4 con_o = r.B;
-            const float2 d = {A.x - pixf.x, A.y - pixf.y};
-            const float power = splat_power(con_o, d);
-            const float G = expf(power);
-            const float alpha = min(0.99f, __fmul_rn(con_o.w, G));
-            if (alpha < 1.0f / 255.0f) return;
-            const float4 col4 = r.C;
-            const float col[3] = {col4.x, col4.y, col4.z};
+            x.d = make_float2(A.x - pixf.x, A.y - pixf.y);
+            const float power = splat_power(con_o, x.d);
+            x.G = expf(power);
+            x.alpha = min(0.99f, __fmul_rn(con_o.w, x.G));
             // one IEEE reciprocal of (1 - alpha) serves both divisions of backward.cu:503,:534 (gradients are
             // compared at 1e-3; the forward's T and alpha decisions are not touched by this)
-            const float inv_1ma = __frcp_rn(1.f - alpha);
+            x.inv_1ma = __frcp_rn(1.f - x.alpha);
+            x.skip = __float_as_uint(A.z) >= last_contributor || x.alpha < 1.0f / 255.0f;
+            return x;
+        },
+        [&](const RingRec& r, const BwdPair& x) {
+            // backward.cu:501-554
+            if (x.skip) return;  // behind this pixel's last contributor, or alpha < 1/255
+            const float4 con_o = r.B;
+            const float2 d = x.d;
+            const float G = x.G, alpha = x.alpha, inv_1ma = x.inv_1ma;
+            const float4 col4 = r.C;
+            const float col[3] = {col4.x, col4.y, col4.z};
             T = T * inv_1ma;
             const float dchannel_dcolor = alpha * T;
             float dL_dalpha = 0.0f;

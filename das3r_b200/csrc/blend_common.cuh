@@ -27,8 +27,19 @@ namespace das3r {
 
 constexpr int BLEND_WARPS = 2;   // warps per block
 constexpr int CHUNK = 32;        // list entries gathered per round (one per lane)
-constexpr int FWD_K = 4;         // ring depth (chunks) of the forward / backward blend
-constexpr int BWD_K = 4;
+// Tunables (overridable at compile time for experiments: tools/variants.sh)
+#ifndef DAS3R_FWD_K
+#define DAS3R_FWD_K 4
+#endif
+#ifndef DAS3R_BWD_K
+#define DAS3R_BWD_K 4
+#endif
+#ifndef DAS3R_BLEND_BURST
+#define DAS3R_BLEND_BURST 8
+#endif
+constexpr int FWD_K = DAS3R_FWD_K;  // ring depth (chunks) of the forward / backward blend
+constexpr int BWD_K = DAS3R_BWD_K;
+constexpr int BLEND_BURST = DAS3R_BLEND_BURST;  // blend rounds between two checks of the gather side
 
 struct RingRec {
     float4 A;  // {x, y, tile-list position (bits), -tau'}
@@ -92,16 +103,19 @@ __device__ __forceinline__ uint32_t transpose_bits(uint32_t x, int lane) {
 
 // Walks list[0..cnt) (REVERSE: from the end) as described at the top of this file.
 //   keep()        per-lane: does this lane still want records? (forward: pixel not finished)
-//   blend(rec)    per-lane blend step for one record whose mask bit is set for this lane's pixel
+//   prep(rec)     per-lane, order-independent part of the blend step for one record whose mask bit is set for this
+//                 lane's pixel (power, exp, alpha); returns what apply() needs
+//   apply(rec, x) per-lane, the part that carries the pixel's recurrence (T, colour sums); called in list order.
+//                 Two records are prepared per round so that their independent chains overlap.
 //   pos_limit     no lane needs tile-list positions >= pos_limit (backward: the warp's highest n_contrib)
 // Chunks are numbered in walk order; `iss` chunks have been started, `vis` of them have landed (records readable, masks
 // stored), at most one is in flight. A lane holds the unblended rest `m` of its mask of chunk nx-1. Chunk c lives in
 // ring slot c % K, so chunk `iss` may be started as soon as no lane needs chunk iss-K any more.
-template <bool REVERSE, int K, typename Keep, typename Blend>
+template <bool REVERSE, int K, typename Keep, typename Prep, typename Apply>
 __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint32_t* __restrict__ qmask,
                                                const uint2* __restrict__ list, int cnt,
                                                const float4* __restrict__ gA, const float4* __restrict__ gBC,
-                                               const uint32_t pos_limit, Keep keep, Blend blend) {
+                                               const uint32_t pos_limit, Keep keep, Prep prep, Apply apply) {
     static_assert((K & (K - 1)) == 0, "K must be a power of two");
     const int lane = threadIdx.x & 31;
     const int nchunks = (cnt + CHUNK - 1) / CHUNK;
@@ -169,15 +183,33 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
         } else if (oldest == vis) {
             break;  // nothing landed, nothing in flight, nothing left to start
         }
-        // blend until a lane that had work runs out of it (only then can `oldest` move)
-        do {
-            if (m) {
-                const int bit = __ffs(m) - 1;
-                m &= m - 1;
-                blend(ring[((nx - 1) & (K - 1)) * 32 + bit]);
-                if (!keep()) m = 0;
+        // blend: a few rounds between two looks at the gather side; lanes step to their next landed chunk on their own
+#pragma unroll 1
+        for (int round = 0; round < BLEND_BURST; round++) {
+            if (m == 0 && nx < vis) {
+                m = qmask[(nx & (K - 1)) * 32 + lane];
+                nx++;
             }
-        } while (!__any_sync(0xffffffffu, m == 0 && !idle));
+            if (m) {
+                const RingRec* base = ring + ((nx - 1) & (K - 1)) * 32;
+                const int bit0 = __ffs(m) - 1;
+                m &= m - 1;
+                const bool two = (m != 0);
+                const int bit1 = two ? __ffs(m) - 1 : bit0;
+                m &= m - 1;
+                const RingRec& r0 = base[bit0];
+                const RingRec& r1 = base[bit1];
+                const auto x0 = prep(r0);
+                const auto x1 = prep(r1);
+                apply(r0, x0);
+                if (two && keep()) apply(r1, x1);
+                if (!keep()) {
+                    m = 0;
+                    nx = vis;
+                }
+            }
+            if (!__any_sync(0xffffffffu, m != 0 || nx < vis)) break;  // nothing landed is left for anybody
+        }
     }
     cp_async_wait_all();  // never leave with a copy into this block's shared memory in flight
 }

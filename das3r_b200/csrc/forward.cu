@@ -918,8 +918,11 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
             const float4 A = r.A;
             const float4 con_o = r.B;
             const float power = splat_power(con_o, make_float2(A.x - pixf.x, A.y - pixf.y));
-            // forward.cu:339-361 (power <= 0 is guaranteed by the pixel mask)
-            const float alpha = min(0.99f, __fmul_rn(con_o.w, expf(power)));
+            // forward.cu:339-340 (power <= 0 is guaranteed by the pixel mask)
+            return min(0.99f, __fmul_rn(con_o.w, expf(power)));
+        },
+        [&](const RingRec& r, const float alpha) {
+            // forward.cu:341-361
             if (alpha < 1.0f / 255.0f) return;
             const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
             if (test_T < 0.0001f) {
@@ -935,7 +938,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
                 Dz = __fmaf_rn(T, __fmul_rn(z, alpha), Dz);
             }
             T = test_T;
-            last_contributor = __float_as_uint(A.z) + 1u;
+            last_contributor = __float_as_uint(r.A.z) + 1u;
         });
 
     if (wr.inside) {
