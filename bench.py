@@ -22,6 +22,7 @@ reference algorithm on the host cores (rank 0 only). Only this file's cpu_baseli
 from __future__ import annotations
 
 import argparse
+from concurrent.futures import ThreadPoolExecutor
 import json
 import os
 import subprocess
@@ -202,6 +203,7 @@ def main():
     streams = [torch.cuda.Stream(device=dev) for _ in range(S_)] if S_ > 1 else [None]
     handles = [None] * nbuf
     last_R = [0]
+    workers = ThreadPoolExecutor(max_workers=S_) if S_ > 1 else None
 
     def fwd(pv):
         return C.rasterize_gaussians(S["bg"], pv["means"], empty, S["opac"], S["scales"], pv["rots"], 1.0, empty,
@@ -237,14 +239,23 @@ def main():
             for pv in pool:
                 one_view(pv, buckets[b][0])
         else:
+            # one host thread per stream: the forward blocks its thread on the 16-byte read-back of num_rendered, the
+            # other threads keep their streams fed meanwhile
             main = torch.cuda.current_stream()
-            for si, st in enumerate(streams):
-                st.wait_stream(main)
+            ev = torch.cuda.Event()
+            ev.record(main)
+
+            def work(si):
+                torch.cuda.set_device(dev)
+                st = streams[si]
                 with torch.cuda.stream(st):
+                    st.wait_event(ev)
                     buckets[b][si].zero_()
-            for j, pv in enumerate(pool):
-                with torch.cuda.stream(streams[j % S_]):
-                    one_view(pv, buckets[b][j % S_])
+                    for j in range(si, len(pool), S_):
+                        one_view(pool[j], buckets[b][si])
+
+            for f in [workers.submit(work, si) for si in range(S_)]:
+                f.result()
             for si, st in enumerate(streams):
                 main.wait_stream(st)
             for si in range(1, S_):

@@ -890,6 +890,18 @@ cudaError_t launch_rect_lists(int T, unsigned gx, int W, int H, const uint2* ran
 // accumulation - with the reference's FMA contraction pinned, so the front-to-back recurrence per pixel, `final_T`,
 // `n_contrib` (list positions) and the image are bit-identical; the early termination is per warp (ballot).
 // ---------------------------------------------------------------------------------------------------------------
+#ifdef DAS3R_BLEND_TIMING  // developer instrumentation (tools/variants.sh), never in the shipped library
+__device__ unsigned long long g_blend_dbg[4 * 65536];
+extern "C" int das3r_debug_blend_timing(unsigned long long* host_out, int n_words) {
+    return (int)cudaMemcpyFromSymbol(host_out, g_blend_dbg, sizeof(unsigned long long) * n_words);
+}
+__device__ __forceinline__ unsigned long long dbg_globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
+
 template <bool EXTRAS>
 __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
@@ -904,6 +916,10 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     const int cnt = (range.y > range.x) ? (int)rect_cnt[wr.tile * 8 + wr.rect] : 0;
     const uint32_t off = cnt ? rect_off[wr.tile * 8 + wr.rect] : 0u;
     const float2 pixf = {(float)wr.px, (float)wr.py};
+#ifdef DAS3R_BLEND_TIMING
+    const unsigned long long dbg_t0 = dbg_globaltimer();
+    const long long dbg_c0 = clock64();
+#endif
 
     bool done = !wr.inside;
     float T = 1.0f;
@@ -941,6 +957,20 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
             last_contributor = __float_as_uint(r.A.z) + 1u;
         });
 
+#ifdef DAS3R_BLEND_TIMING
+    {
+        const unsigned wmaxc = __reduce_max_sync(0xffffffffu, last_contributor);
+        if ((threadIdx.x & 31) == 0) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            unsigned long long* o = g_blend_dbg + 4 * (size_t)(blockIdx.x * BLEND_WARPS + warp);
+            o[0] = dbg_t0;
+            o[1] = dbg_globaltimer();
+            o[2] = (unsigned long long)(clock64() - dbg_c0);
+            o[3] = ((unsigned long long)smid << 48) | ((unsigned long long)wmaxc << 24) | (unsigned long long)cnt;
+        }
+    }
+#endif
     if (wr.inside) {
         const int pix_id = W * wr.py + wr.px;
         final_T[pix_id] = T;

@@ -330,10 +330,12 @@ torch::Tensor distCUDA2(const torch::Tensor& points_) {
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
-    m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
-    m.def("rasterize_gaussians_ex", &RasterizeGaussiansExCUDA);
-    m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
-    m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardIntoCUDA);
+    // The GIL is released around every call into the library: a host that drives several CUDA streams from several
+    // threads (bench.py) must not serialise on the forward's read-back of num_rendered.
+    m.def("rasterize_gaussians", &RasterizeGaussiansCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_ex", &RasterizeGaussiansExCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardIntoCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
     m.def("prof_collect", [](bool reset) {
         int n = das3r_prof_num_stages();
@@ -345,7 +347,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         return out;
     });
     m.def("launch_count", []() { return das3r_launch_count(); });
-    m.def("mark_visible", &markVisible);
-    m.def("distCUDA2", &distCUDA2);
+    m.def("mark_visible", &markVisible, py::call_guard<py::gil_scoped_release>());
+    m.def("distCUDA2", &distCUDA2, py::call_guard<py::gil_scoped_release>());
     m.def("abi_version", []() { return das3r_abi_version(); });
 }
