@@ -34,11 +34,16 @@ constexpr int CHUNK = 32;        // list entries gathered per round (one per lan
 #ifndef DAS3R_BWD_K
 #define DAS3R_BWD_K 4
 #endif
+#ifndef DAS3R_BLEND_INFLIGHT
+#define DAS3R_BLEND_INFLIGHT 2
+#endif
 #ifndef DAS3R_BLEND_BURST
 #define DAS3R_BLEND_BURST 8
 #endif
 constexpr int FWD_K = DAS3R_FWD_K;  // ring depth (chunks) of the forward / backward blend
 constexpr int BWD_K = DAS3R_BWD_K;
+constexpr int BLEND_INFLIGHT = DAS3R_BLEND_INFLIGHT;  // chunks whose record copies may be in flight (1..3)
+static_assert(BLEND_INFLIGHT >= 1 && BLEND_INFLIGHT <= 3, "wait_group immediates below cover 1..3");
 constexpr int BLEND_BURST = DAS3R_BLEND_BURST;  // blend rounds between two checks of the gather side
 
 struct RingRec {
@@ -109,7 +114,7 @@ __device__ __forceinline__ uint32_t transpose_bits(uint32_t x, int lane) {
 //                 Two records are prepared per round so that their independent chains overlap.
 //   pos_limit     no lane needs tile-list positions >= pos_limit (backward: the warp's highest n_contrib)
 // Chunks are numbered in walk order; `iss` chunks have been started, `vis` of them have landed (records readable, masks
-// stored), at most one is in flight. A lane holds the unblended rest `m` of its mask of chunk nx-1. Chunk c lives in
+// stored), up to BLEND_INFLIGHT are in flight. A lane holds the unblended rest `m` of its mask of chunk nx-1. Chunk c lives in
 // ring slot c % K, so chunk `iss` may be started as soon as no lane needs chunk iss-K any more.
 template <bool REVERSE, int K, typename Keep, typename Prep, typename Apply>
 __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint32_t* __restrict__ qmask,
@@ -134,7 +139,13 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
 
     uint32_t m = 0;
     int nx = 0, vis = 0, iss = 0;
-    uint32_t pend_mask = 0, pend_pos = 0xffffffffu;
+    // chunks in flight, oldest first: their transposed masks and this lane's entry position wait in registers
+    uint32_t pend_mask[BLEND_INFLIGHT], pend_pos[BLEND_INFLIGHT];
+#pragma unroll
+    for (int f = 0; f < BLEND_INFLIGHT; f++) {
+        pend_mask[f] = 0;
+        pend_pos[f] = 0xffffffffu;
+    }
 
     for (;;) {
         if (!keep()) {
@@ -148,19 +159,8 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
         const bool idle = (m == 0);  // nothing landed is left for this lane
         if (__all_sync(0xffffffffu, !keep())) break;
         const int oldest = __reduce_min_sync(0xffffffffu, idle ? vis : nx - 1);  // lowest chunk still needed
-        const bool can_start = left > 0 && (iss - oldest < K);
-        if (iss > vis) {
-            if (can_start || oldest == vis) {
-                // land the chunk in flight
-                cp_async_wait_all();
-                const int slot = (vis & (K - 1)) * 32 + lane;
-                if (pend_pos != 0xffffffffu) ring[slot].A.z = __uint_as_float(pend_pos);
-                qmask[slot] = pend_mask;
-                __syncwarp();
-                vis++;
-                continue;
-            }
-        } else if (can_start) {
+        const int nfly = iss - vis;
+        if (left > 0 && nfly < BLEND_INFLIGHT && iss - oldest < K) {
             // start the next list chunk that somebody needs
             const bool valid = e_cur.x < pos_limit;
             if (__any_sync(0xffffffffu, valid)) {
@@ -171,8 +171,13 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
                     cp_async_16(&r.C, gBC + 2 * (size_t)e_cur.x + 1);
                 }
                 cp_async_commit();
-                pend_mask = transpose_bits(valid ? e_cur.y : 0u, lane);
-                pend_pos = valid ? e_cur.x : 0xffffffffu;
+                const uint32_t tm = transpose_bits(valid ? e_cur.y : 0u, lane);
+#pragma unroll
+                for (int f = 0; f < BLEND_INFLIGHT; f++)
+                    if (f == nfly) {
+                        pend_mask[f] = tm;
+                        pend_pos[f] = valid ? e_cur.x : 0xffffffffu;
+                    }
                 iss++;
             }
             lc += step;
@@ -180,9 +185,26 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
             e_cur = e_nxt;
             e_nxt = load_entry(lc + step);
             continue;
-        } else if (oldest == vis) {
-            break;  // nothing landed, nothing in flight, nothing left to start
         }
+        if (nfly > 0 && (oldest == vis || nfly == BLEND_INFLIGHT || left == 0)) {
+            // land the oldest chunk in flight: the pipeline is full, or everybody is out of work, or nothing is left
+            // to start
+            if (nfly == 1) cp_async_wait_group<0>();
+            else if (nfly == 2) cp_async_wait_group<1>();
+            else cp_async_wait_group<2>();
+            const int slot = (vis & (K - 1)) * 32 + lane;
+            if (pend_pos[0] != 0xffffffffu) ring[slot].A.z = __uint_as_float(pend_pos[0]);
+            qmask[slot] = pend_mask[0];
+#pragma unroll
+            for (int f = 0; f + 1 < BLEND_INFLIGHT; f++) {
+                pend_mask[f] = pend_mask[f + 1];
+                pend_pos[f] = pend_pos[f + 1];
+            }
+            __syncwarp();
+            vis++;
+            continue;
+        }
+        if (oldest == vis) break;  // nothing landed, nothing in flight, nothing left to start
         // blend: a few rounds between two looks at the gather side; lanes step to their next landed chunk on their own
 #pragma unroll 1
         for (int round = 0; round < BLEND_BURST; round++) {

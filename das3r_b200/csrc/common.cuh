@@ -244,5 +244,9 @@ __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() {  // all but the N most recent groups have landed
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 
 }  // namespace das3r

@@ -664,18 +664,72 @@ static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const ui
     return cudaGetLastError();
 }
 
+// Two auxiliary streams per device for the crowded size classes of the tile sort (created on first use, never
+// destroyed; cudaStreamNonBlocking, ordered against the caller's stream with per-call events).
+namespace {
+constexpr int kMaxDevices = 64;
+struct SideStreams {
+    cudaStream_t st[2] = {nullptr, nullptr};
+    bool ready = false;
+};
+cudaError_t side_streams(cudaStream_t out[2]) {
+    static std::mutex mu;
+    static SideStreams per_dev[kMaxDevices];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    SideStreams& ss = per_dev[dev];
+    if (!ss.ready) {
+        for (int i = 0; i < 2; i++) {
+            e = cudaStreamCreateWithFlags(&ss.st[i], cudaStreamNonBlocking);
+            if (e != cudaSuccess) return e;
+        }
+        ss.ready = true;
+    }
+    out[0] = ss.st[0];
+    out[1] = ss.st[1];
+    return cudaSuccess;
+}
+}  // namespace
+
 cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
                              const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                              cudaStream_t s) {
     if (max_count > (uint32_t)tile_sort_capacity()) return cudaErrorInvalidValue;
-    // Tiles are sorted by the cheapest variant that fits them: every launch covers all tiles, and a block whose tile
-    // belongs to another size class exits at once, so a few crowded tiles do not drag the whole grid to the
-    // 128-register variant.
+    // Tiles are sorted by the cheapest variant that fits them (<= 4096, <= 8192, <= 16384 entries): every launch covers
+    // all tiles and a block whose tile belongs to another size class exits at once. The crowded classes (one block
+    // per SM, a few dozen tiles) run on auxiliary streams next to the common one instead of in front of it.
+    const bool need16 = max_count > SORT_THREADS * 8, need32 = max_count > SORT_THREADS * 16;
     cudaError_t e = cudaSuccess;
-    if (max_count > SORT_THREADS * 8)  // the few crowded tiles first: they are the long pole
-        e = launch_tile_sort_variant<32, SORT_THREADS * 8>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
-    if (e != cudaSuccess) return e;
-    e = launch_tile_sort_variant<8, 0>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    cudaStream_t side[2] = {nullptr, nullptr};
+    cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
+    if (need16) {
+        if ((e = side_streams(side)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+        e = cudaEventRecord(fork, s);
+        for (int c = 0; c < 2 && e == cudaSuccess; c++) {
+            if (c == 1 && !need32) break;
+            e = cudaStreamWaitEvent(side[c], fork, 0);
+            if (e != cudaSuccess) break;
+            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8>(T, ranges, unsorted, rec, point_list, sA, sBC,
+                                                                         keys_sorted, side[c])
+                         : launch_tile_sort_variant<32, SORT_THREADS * 16>(T, ranges, unsorted, rec, point_list, sA, sBC,
+                                                                          keys_sorted, side[c]);
+            if (e != cudaSuccess) break;
+            if ((e = cudaEventCreateWithFlags(&join[c], cudaEventDisableTiming)) != cudaSuccess) break;
+            e = cudaEventRecord(join[c], side[c]);
+        }
+    }
+    if (e == cudaSuccess)
+        e = launch_tile_sort_variant<8, 0>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    for (int c = 0; c < 2; c++)
+        if (join[c]) {
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(s, join[c], 0);
+            cudaEventDestroy(join[c]);  // released once the recorded work has completed
+        }
+    if (fork) cudaEventDestroy(fork);
     if (e != cudaSuccess) return e;
     gather_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, point_list, rec, sA, sBC);
     return cudaGetLastError();
