@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-views", type=int, default=4, help="views timed for the CPU baseline sample")
+    ap.add_argument("--per-view-backward", action="store_true",
+                    help="sum the views with the per-view accumulating backward instead of the fused multi-view pass")
     ap.add_argument("--streams", type=int, default=3,
                     help="CUDA streams the views of a step are spread over (the reference arm always uses 1: its "
                          "kernels are hard-wired to the legacy default stream)")
@@ -119,9 +121,16 @@ def hbm_peak() -> tuple[float, str]:
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def stage_bytes(P, R, N, T, s):
+def stage_bytes(P, R, N, T, s, fused_views=0):
     """Algorithmic bytes per launch of each stage (SURVEY.md §8d / DESIGN.md §4): compulsory traffic, each array counted
-    once per pass that semantically needs it. s = 12*(D+1)^2 bytes of active SH per Gaussian."""
+    once per pass that semantically needs it. s = 12*(D+1)^2 bytes of active SH per Gaussian. With the fused multi-view
+    backward one preprocess_bwd launch serves `fused_views` views: per view it must read radii 4, the accumulator row
+    48, mean 12, scale 12, rotation 16, clamp bits 1 (= 93 B per Gaussian); once per launch the SH rows (s) and the
+    gradient rows it writes (opacity 4, mean 12, scale 12, rotation 16, SH s)."""
+    if fused_views:
+        pre_bwd = P * (93 * fused_views + 2 * s + 44)
+    else:
+        pre_bwd = P * (199 + 2 * s)
     return {
         "preprocess_fwd": P * (119 + s),
         "tile_scan": 8 * T,
@@ -129,7 +138,7 @@ def stage_bytes(P, R, N, T, s):
         "tile_sort": 24 * R,
         "blend_fwd": 48 * R + 20 * N,
         "blend_bwd": 40 * R + 20 * N,
-        "preprocess_bwd": P * (199 + 2 * s),
+        "preprocess_bwd": pre_bwd,
     }
 
 
@@ -211,6 +220,7 @@ def main():
                                      False)
 
     def one_view(pv, bk):
+        """fwd + bwd of one view with the per-view API (reference arm; ours with --per-view-backward)."""
         g = bk.views()
         R, color, radii, geom, binning, img = fwd(pv)
         last_R[0] = R
@@ -227,6 +237,22 @@ def main():
             g["scales"].add_(d_sc)
             g["rotations"].add_(d_rot)
 
+    def view_blend(pv):
+        """fwd + first half of the backward (backward blend) of one view; returns what the fused second half needs."""
+        R, color, radii, geom, binning, img = fwd(pv)
+        last_R[0] = R
+        acc = C.rasterize_gaussians_backward_blend(S["bg"], dL, P, geom, R, binning, img, False)
+        return (pv["means"], radii, S["scales"], pv["rots"], S["view"], S["proj"], float(S["tanx"]), float(S["tany"]),
+                S["campos"], geom, acc, H, W)
+
+    def finish(fviews, bk):
+        """second half of the backward for all views of the step: one pass, gradients summed over the views."""
+        g = bk.views()
+        C.rasterize_gaussians_backward_finish(fviews, S["shs"], D, 1.0,
+                                              [g["opacities"], g["means3D"], g["shs"], g["scales"], g["rotations"]],
+                                              False, False)
+
+    fused_bwd = args.impl == "ours" and not args.per_view_backward
     single_stream = [False]  # the per-stage profiling pass runs the views back to back on one stream
 
     def step(i):
@@ -235,31 +261,46 @@ def main():
             handles[b].wait()
             handles[b] = None
         if S_ == 1 or single_stream[0]:
-            buckets[b][0].zero_()
-            for pv in pool:
-                one_view(pv, buckets[b][0])
+            if fused_bwd:
+                finish([view_blend(pv) for pv in pool], buckets[b][0])
+            else:
+                buckets[b][0].zero_()
+                for pv in pool:
+                    one_view(pv, buckets[b][0])
         else:
             # one host thread per stream: the forward blocks its thread on the 16-byte read-back of num_rendered, the
             # other threads keep their streams fed meanwhile
             main = torch.cuda.current_stream()
             ev = torch.cuda.Event()
             ev.record(main)
+            fviews = [None] * len(pool)
 
             def work(si):
                 torch.cuda.set_device(dev)
                 st = streams[si]
                 with torch.cuda.stream(st):
                     st.wait_event(ev)
-                    buckets[b][si].zero_()
+                    if not fused_bwd:
+                        buckets[b][si].zero_()
                     for j in range(si, len(pool), S_):
-                        one_view(pool[j], buckets[b][si])
+                        if fused_bwd:
+                            fviews[j] = view_blend(pool[j])
+                        else:
+                            one_view(pool[j], buckets[b][si])
 
             for f in [workers.submit(work, si) for si in range(S_)]:
                 f.result()
             for si, st in enumerate(streams):
                 main.wait_stream(st)
-            for si in range(1, S_):
-                buckets[b][0].flat.add_(buckets[b][si].flat)
+            if fused_bwd:
+                finish(fviews, buckets[b][0])
+                for fv in fviews:  # the per-view tensors were allocated on side streams and are last read on `main`
+                    for t in fv:
+                        if isinstance(t, torch.Tensor):
+                            t.record_stream(main)
+            else:
+                for si in range(1, S_):
+                    buckets[b][0].flat.add_(buckets[b][si].flat)
         if world > 1:
             handles[b] = buckets[b][0].all_reduce(async_op=True)
 
@@ -307,8 +348,8 @@ def main():
         "config": {
             "workload": f"C2-shaped synthetic scene: {P} Gaussians from {args.V} pointmap views, {W}x{H}, SH degree {D}, "
                         f"shs+scales/rotations inputs; step = {vps} views/rank (fwd+bwd, dense dL), gradients summed "
-                        f"in place into a {buckets[0][0].nbytes() // (1 << 20)} MiB fp32 bucket, views spread over {S_} CUDA "
-                        f"stream(s)"
+                        f"{'by the fused multi-view backward pass' if fused_bwd else 'in place (per-view accumulate)'} into a "
+                        f"{buckets[0][0].nbytes() // (1 << 20)} MiB fp32 bucket, views spread over {S_} CUDA stream(s)"
                         + (", one NCCL all-reduce of the bucket per step (overlapped)" if world > 1 else ""),
             "views_per_step_per_rank": vps, "streams": S_, "P": P, "W": W, "H": H, "sh_degree": D, "num_rendered": R,
             "l2_policy": "inputs larger than L2 (per step each rank streams ~%d MB of distinct inputs; L2 is 126 MB)" %
@@ -341,12 +382,14 @@ def main():
     drain()
     torch.cuda.synchronize()
     single_stream[0] = False
-    stages = {name: (ms / max(calls, 1)) for name, ms, calls in C.prof_collect(True) if calls > 0}
+    collected = [(name, ms, calls) for name, ms, calls in C.prof_collect(True) if calls > 0]
+    stages = {name: (ms / calls) for name, ms, calls in collected}
+    stage_total = {name: ms for name, ms, calls in collected}
     C.prof_enable(False)
     peak, peak_src = hbm_peak()
-    sb = stage_bytes(P, R, N, T, s_bytes)
+    sb = stage_bytes(P, R, N, T, s_bytes, fused_views=vps if fused_bwd else 0)
     kern = {k: v for k, v in stages.items() if k in sb}
-    dom = max(kern, key=kern.get)
+    dom = max(kern, key=lambda k: stage_total[k])  # the kernel with the largest share of the step
     achieved = sb[dom] / (kern[dom] * 1e-3) / 1e9
     vb = view_bytes(P, R, N, T, s_bytes)
     per_view_ms = elapsed_ms / (vps * args.steps)
@@ -357,6 +400,7 @@ def main():
         "timing": f"CUDA events around every stage on the launching stream, {prof_steps} single-stream steps right "
                   "after the timed region",
         "stage_ms": {k: round(v, 5) for k, v in stages.items()},
+        "stage_share_of_step": {k: round(v / sum(stage_total.values()), 4) for k, v in stage_total.items()},
         "stage_frac_of_hbm_peak": {k: round(sb[k] / (v * 1e-3) / 1e9 / peak, 4) for k, v in kern.items()},
         "view": {"algorithmic_bytes": vb, "achieved_gbs": round(vb / (per_view_ms * 1e-3) / 1e9, 1),
                  "frac": round(vb / (per_view_ms * 1e-3) / 1e9 / peak, 4),

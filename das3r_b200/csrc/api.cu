@@ -8,6 +8,7 @@
 #include <string.h>
 #include <string>
 #include <vector>
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 
@@ -23,7 +24,7 @@ int fail(int code, const char* where, cudaError_t e) {
     g_err = buf;
     return code;
 }
-int fail_msg(int code, const char* msg) {
+int fail_msg(int code, const std::string& msg) {
     g_err = std::string("[das3r_raster] ") + msg;
     return code;
 }
@@ -333,21 +334,15 @@ size_t das3r_raster_backward_scratch_bytes(int32_t P) {
     return align_up((size_t)(P > 0 ? P : 0) * ACC_STRIDE * sizeof(float), 256);
 }
 
-int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in, const int32_t* radii,
-                          const das3r_raster_state* state, const float* dL_dpix, const das3r_raster_grads* g,
-                          void* stream_v) {
-    g_err.clear();
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
-    if (!check_params(params) || !in || !state || !g) return fail_msg(DAS3R_EINVAL, "backward: null or invalid argument");
+// The two halves of the backward, shared by das3r_raster_backward and the split / multi-view entry points.
+static int backward_blend_impl(const char* who, const das3r_raster_params* params, const das3r_raster_state* state,
+                               const float* dL_dpix, float* scratch, cudaStream_t stream,
+                               das3r_raster_state_layout* L_out) {
     const int P = params->P, W = params->width, H = params->height;
-    if (P == 0) return DAS3R_OK;
-    if (!radii || !dL_dpix || !state->geom || !state->image || !g->dL_dopacity || !g->dL_dmeans3D || !g->dL_dscales ||
-        !g->dL_drotations || !g->scratch)
-        return fail_msg(DAS3R_EINVAL, "backward: null buffer");
-    if (in->shs && !g->dL_dsh) return fail_msg(DAS3R_EINVAL, "backward: dL_dsh is null although shs is given");
+    if (!dL_dpix || !state->geom || !state->image || !scratch)
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": null buffer");
     const int R = state->num_rendered;
-    if (R > 0 && !state->binning) return fail_msg(DAS3R_EINVAL, "backward: binning blob is null");
-
+    if (R > 0 && !state->binning) return fail_msg(DAS3R_EINVAL, std::string(who) + ": binning blob is null");
     const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int T = (int)(gx * gy);
     das3r_raster_state_layout L;
@@ -357,14 +352,13 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     BinExtra X;
     binning_layout(R, T, params->debug != 0, false, &L, &X);
     if (state->geom_bytes < L.geom_bytes || state->image_bytes < L.image_bytes)
-        return fail_msg(DAS3R_EINVAL, "backward: state blobs are smaller than the forward's layout");
-
-    const uint8_t* clamped = reinterpret_cast<const uint8_t*>(state->geom + L.g_clamped);
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": state blobs are smaller than the forward's layout");
+    if (L_out) *L_out = L;
     const float* final_T = reinterpret_cast<const float*>(state->image + L.i_final_T);
     const uint32_t* n_contrib = reinterpret_cast<const uint32_t*>(state->image + L.i_n_contrib);
     const uint2* ranges = reinterpret_cast<const uint2*>(state->image + L.i_ranges);
 
-    STAGE(cudaMemsetAsync(g->scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)", ST_MEMSET, 0);
+    STAGE(cudaMemsetAsync(scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)", ST_MEMSET, 0);
     if (R > 0) {
         const float4* sA = reinterpret_cast<const float4*>(state->binning + L.b_sA);
         const float4* sBC = reinterpret_cast<const float4*>(state->binning + L.b_sB);
@@ -372,12 +366,18 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
         const uint32_t* rect_cnt = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_cnt);
         const uint2* rect_list = reinterpret_cast<const uint2*>(state->binning + L.b_rect_list);
         STAGE(launch_blend_bwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, params->background, final_T, n_contrib,
-                               dL_dpix, g->scratch, stream),
+                               dL_dpix, scratch, stream),
               "blend_bwd", ST_BLEND_BWD, 1);
     }
-    PreBwdArgs a;
+    return DAS3R_OK;
+}
+
+static void fill_prebwd_args(PreBwdArgs& a, const das3r_raster_params* params, const das3r_raster_inputs* in,
+                             const int32_t* radii, const uint8_t* clamped, const float* acc,
+                             const das3r_raster_grads* g, int accumulate) {
     memset(&a, 0, sizeof(a));
-    a.P = P; a.D = params->D; a.M = in->shs ? params->M : 0; a.W = W; a.H = H;
+    const int W = params->width, H = params->height;
+    a.P = params->P; a.D = params->D; a.M = in->shs ? params->M : 0; a.W = W; a.H = H;
     a.tan_fovx = params->tan_fovx; a.tan_fovy = params->tan_fovy;
     a.focal_y = H / (2.0f * params->tan_fovy);
     a.focal_x = W / (2.0f * params->tan_fovx);
@@ -385,12 +385,124 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     a.means = in->means3D; a.shs = in->shs; a.scales = in->scales; a.rots = in->rotations;
     a.cov3D_precomp = in->cov3D_precomp;
     a.view = params->viewmatrix; a.proj = params->projmatrix; a.campos = params->campos;
-    a.radii = radii; a.clamped = clamped; a.acc = g->scratch;
+    a.radii = radii; a.clamped = clamped; a.acc = acc;
     a.dL_dmeans2D = g->dL_dmeans2D; a.dL_dcolors = g->dL_dcolors; a.dL_dopacity = g->dL_dopacity;
     a.dL_dmeans3D = g->dL_dmeans3D; a.dL_dcov3D = g->dL_dcov3D; a.dL_dsh = in->shs ? g->dL_dsh : nullptr;
     a.dL_dscales = g->dL_dscales; a.dL_drots = g->dL_drotations;
-    a.accumulate = g->accumulate;
+    a.accumulate = accumulate;
+}
+
+int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in, const int32_t* radii,
+                          const das3r_raster_state* state, const float* dL_dpix, const das3r_raster_grads* g,
+                          void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!check_params(params) || !in || !state || !g) return fail_msg(DAS3R_EINVAL, "backward: null or invalid argument");
+    const int P = params->P;
+    if (P == 0) return DAS3R_OK;
+    if (!radii || !g->dL_dopacity || !g->dL_dmeans3D || !g->dL_dscales || !g->dL_drotations)
+        return fail_msg(DAS3R_EINVAL, "backward: null buffer");
+    if (in->shs && !g->dL_dsh) return fail_msg(DAS3R_EINVAL, "backward: dL_dsh is null although shs is given");
+    das3r_raster_state_layout L;
+    int rc = backward_blend_impl("backward", params, state, dL_dpix, g->scratch, stream, &L);
+    if (rc != DAS3R_OK) return rc;
+    const uint8_t* clamped = reinterpret_cast<const uint8_t*>(state->geom + L.g_clamped);
+    PreBwdArgs a;
+    fill_prebwd_args(a, params, in, radii, clamped, g->scratch, g, g->accumulate);
     STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd", ST_PREPROCESS_BWD, 1);
+    return DAS3R_OK;
+}
+
+// ---- split / multi-view backward (see include/das3r_raster.h) ----------------------------------------------------
+int das3r_raster_backward_blend(const das3r_raster_view* view, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!view || !check_params(view->params) || !view->state)
+        return fail_msg(DAS3R_EINVAL, "backward_blend: null or invalid argument");
+    const das3r_raster_params* params = view->params;  // the STAGE macro reads params->debug
+    if (params->P == 0) return DAS3R_OK;
+    return backward_blend_impl("backward_blend", params, view->state, view->dL_dpix, view->scratch, stream, nullptr);
+}
+
+int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* g,
+                                 void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (n_views < 1 || !views || !g) return fail_msg(DAS3R_EINVAL, "backward_finish: null or invalid argument");
+    for (int v = 0; v < n_views; v++) {
+        const das3r_raster_view& V = views[v];
+        if (!check_params(V.params) || !V.in || !V.state)
+            return fail_msg(DAS3R_EINVAL, "backward_finish: null or invalid view");
+        if (V.params->P != views[0].params->P || V.params->D != views[0].params->D || V.params->M != views[0].params->M)
+            return fail_msg(DAS3R_EINVAL, "backward_finish: the views differ in P, D or M");
+        if ((V.in->shs != nullptr) != (views[0].in->shs != nullptr))
+            return fail_msg(DAS3R_EINVAL, "backward_finish: the views differ in their colour input");
+    }
+    const das3r_raster_params* params = views[0].params;  // for the STAGE macro
+    const int P = params->P;
+    if (P == 0) return DAS3R_OK;
+    for (int v = 0; v < n_views; v++)
+        if (!views[v].radii || !views[v].scratch || !views[v].state->geom)
+            return fail_msg(DAS3R_EINVAL, "backward_finish: null buffer in a view");
+    if (!g->dL_dopacity || !g->dL_dmeans3D || !g->dL_dscales || !g->dL_drotations)
+        return fail_msg(DAS3R_EINVAL, "backward_finish: null gradient buffer");
+    if (views[0].in->shs && !g->dL_dsh)
+        return fail_msg(DAS3R_EINVAL, "backward_finish: dL_dsh is null although shs is given");
+    if (n_views > 1 && (g->dL_dmeans2D || g->dL_dcolors || g->dL_dcov3D))
+        return fail_msg(DAS3R_EINVAL, "backward_finish: dL_dmeans2D / dL_dcolors / dL_dcov3D are per-view quantities; pass "
+                                      "NULL for them when summing several views");
+    das3r_raster_state_layout L;
+    memset(&L, 0, sizeof(L));
+    geom_layout(P, &L);
+
+    // One fused pass when the views share their SH rows (degree 3) and use scale / rotation inputs; otherwise one
+    // accumulating pass per view, which gives the same sums.
+    bool fused = params->D == 3 && params->M == 16 && views[0].in->shs != nullptr &&
+                 ((reinterpret_cast<uintptr_t>(views[0].in->shs) & 15) == 0) &&
+                 ((reinterpret_cast<uintptr_t>(g->dL_dsh) & 15) == 0) &&
+                 ((reinterpret_cast<uintptr_t>(g->dL_drotations) & 15) == 0) && n_views > 1;
+    for (int v = 0; v < n_views && fused; v++) {
+        const das3r_raster_inputs* in = views[v].in;
+        fused = in->shs == views[0].in->shs && in->scales && in->rotations && !in->cov3D_precomp && !in->colors_precomp &&
+                ((reinterpret_cast<uintptr_t>(in->rotations) & 15) == 0) &&
+                views[v].state->geom_bytes >= L.geom_bytes;
+    }
+    if (fused) {
+        for (int v0 = 0; v0 < n_views; v0 += MV_MAX_VIEWS) {
+            MultiBwdArgs a;
+            memset(&a, 0, sizeof(a));
+            a.P = P;
+            a.n_views = std::min(MV_MAX_VIEWS, n_views - v0);
+            a.accumulate = (v0 == 0) ? g->accumulate : 1;
+            a.shs = views[0].in->shs;
+            a.dL_dopacity = g->dL_dopacity; a.dL_dmeans3D = g->dL_dmeans3D; a.dL_dsh = g->dL_dsh;
+            a.dL_dscales = g->dL_dscales; a.dL_drots = g->dL_drotations;
+            for (int i = 0; i < a.n_views; i++) {
+                const das3r_raster_view& V = views[v0 + i];
+                MultiBwdView& m = a.v[i];
+                m.means = V.in->means3D; m.scales = V.in->scales; m.rots = V.in->rotations;
+                m.view = V.params->viewmatrix; m.proj = V.params->projmatrix; m.campos = V.params->campos;
+                m.radii = V.radii;
+                m.clamped = reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped);
+                m.acc = V.scratch;
+                m.tan_fovx = V.params->tan_fovx; m.tan_fovy = V.params->tan_fovy;
+                m.focal_x = V.params->width / (2.0f * V.params->tan_fovx);
+                m.focal_y = V.params->height / (2.0f * V.params->tan_fovy);
+                m.scale_mod = V.params->scale_modifier;
+            }
+            STAGE(launch_preprocess_bwd_multi(a, stream), "preprocess_bwd_multi", ST_PREPROCESS_BWD, 1);
+        }
+        return DAS3R_OK;
+    }
+    for (int v = 0; v < n_views; v++) {
+        const das3r_raster_view& V = views[v];
+        if (V.state->geom_bytes < L.geom_bytes)
+            return fail_msg(DAS3R_EINVAL, "backward_finish: geom blob is smaller than the forward's layout");
+        PreBwdArgs a;
+        fill_prebwd_args(a, V.params, V.in, V.radii, reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped),
+                         V.scratch, g, v == 0 ? g->accumulate : 1);
+        STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd", ST_PREPROCESS_BWD, 1);
+    }
     return DAS3R_OK;
 }
 

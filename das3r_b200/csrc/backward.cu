@@ -195,6 +195,149 @@ __device__ __forceinline__ float3 sh_backward(int deg, float3 pos, float3 campos
     return dnormvdv3(dir_orig, dd);
 }
 
+// Gradients of one (view, Gaussian) pair with respect to the Gaussian's 3D mean, scale and rotation, given the
+// screen-space gradients the backward blend accumulated: computeCov2DCUDA (backward.cu:144-274), the projection part of
+// preprocessCUDA (:366-395) and computeCov3D (:278-341). Shared by the one-view and the multi-view kernel.
+struct ViewConst {
+    const float *view, *proj;
+    float focal_x, focal_y, tan_fovx, tan_fovy, scale_mod;
+};
+struct GeomGrad {
+    float3 dmean;   // without the SH (view direction) part
+    float3 dscale;  // valid if has_sr
+    float4 drot;    // valid if has_sr
+    float dcov[6];  // dL/dcov3D
+};
+__device__ __forceinline__ void geom_backward(const ViewConst& vc, const float3 mean, const float* cov3D, const bool has_sr,
+                                              const float3 sc, const float4 rq, const float dL_dmean2D_x,
+                                              const float dL_dmean2D_y, const float3 dL_dconic, GeomGrad& g) {
+    // ---- computeCov2DCUDA, backward.cu:162-273 ----
+    const float h_x = vc.focal_x, h_y = vc.focal_y;
+    Ewa e = ewa_project(mean, h_x, h_y, vc.tan_fovx, vc.tan_fovy, cov3D, vc.view);
+    const float3 t = e.t;
+    const float x_grad_mul = e.txtz < -e.limx || e.txtz > e.limx ? 0 : 1;
+    const float y_grad_mul = e.tytz < -e.limy || e.tytz > e.limy ? 0 : 1;
+    const Mat3& T = e.T;
+    const Mat3& Vrk = e.Vrk;
+    const float ca = e.a, cb = e.b, cc = e.c;
+    float denom = ca * cc - cb * cb;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float dL_dcov[6];
+    if (denom2inv != 0) {
+        dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
+        dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
+        dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
+        dL_dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+        dL_dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+        dL_dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+        dL_dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+                     2 * T.m[1][0] * T.m[1][1] * dL_dc;
+        dL_dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+                     2 * T.m[1][0] * T.m[1][2] * dL_dc;
+        dL_dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+                     2 * T.m[1][1] * T.m[1][2] * dL_dc;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 6; i++) dL_dcov[i] = 0;
+    }
+#pragma unroll
+    for (int i = 0; i < 6; i++) g.dcov[i] = dL_dcov[i];
+
+    float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
+                    (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
+    float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
+                    (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
+    float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
+                    (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
+    float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
+                    (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
+    float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
+                    (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
+    float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
+                    (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
+
+    // W as built in ewa_project: W.m[c][r] = view[4*r + c]  (glm::mat3(view[0], view[4], view[8], ...))
+    const float* vm = vc.view;
+    const float W00 = vm[0], W01 = vm[4], W02 = vm[8];
+    const float W10 = vm[1], W11 = vm[5], W12 = vm[9];
+    const float W20 = vm[2], W21 = vm[6], W22 = vm[10];
+    float dL_dJ00 = W00 * dL_dT00 + W01 * dL_dT01 + W02 * dL_dT02;
+    float dL_dJ02 = W20 * dL_dT00 + W21 * dL_dT01 + W22 * dL_dT02;
+    float dL_dJ11 = W10 * dL_dT10 + W11 * dL_dT11 + W12 * dL_dT12;
+    float dL_dJ12 = W20 * dL_dT10 + W21 * dL_dT11 + W22 * dL_dT12;
+
+    float tz = 1.f / t.z;
+    float tz2 = tz * tz;
+    float tz3 = tz2 * tz;
+    float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                   (2 * h_y * t.y) * tz3 * dL_dJ12;
+    float3 dL_dmean_acc = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, vc.view);
+
+    // ---- preprocessCUDA (backward.cu:366-395) ----
+    const float* proj = vc.proj;
+    float4 m_hom = xform_point_4x4(mean, proj);
+    float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+    float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+    float3 dL_dmean;
+    dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D_y;
+    dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D_y;
+    dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D_y;
+    dL_dmean_acc.x += dL_dmean.x;
+    dL_dmean_acc.y += dL_dmean.y;
+    dL_dmean_acc.z += dL_dmean.z;
+    g.dmean = dL_dmean_acc;
+
+    // ---- computeCov3D backward (backward.cu:278-341) ----
+    if (has_sr) {
+        float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
+        Mat3 R = mat3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                      2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                      2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+        Mat3 S = mat3(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+        float3 s = {vc.scale_mod * sc.x, vc.scale_mod * sc.y, vc.scale_mod * sc.z};
+        S.m[0][0] = s.x;
+        S.m[1][1] = s.y;
+        S.m[2][2] = s.z;
+        Mat3 M = mul(S, R);
+        Mat3 dL_dSigma = mat3(dL_dcov[0], 0.5f * dL_dcov[1], 0.5f * dL_dcov[2], 0.5f * dL_dcov[1], dL_dcov[3],
+                              0.5f * dL_dcov[4], 0.5f * dL_dcov[2], 0.5f * dL_dcov[4], dL_dcov[5]);
+        // dL_dM = 2.0f * M * dL_dSigma  (glm: scalar*mat first, then the product)
+        Mat3 M2;
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int rr = 0; rr < 3; rr++) M2.m[c][rr] = 2.0f * M.m[c][rr];
+        Mat3 dL_dM = mul(M2, dL_dSigma);
+        Mat3 Rt = transpose(R);
+        Mat3 dL_dMt = transpose(dL_dM);
+        float3 dsc;
+        dsc.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+        dsc.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+        dsc.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+        g.dscale = dsc;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            dL_dMt.m[0][k] *= s.x;
+            dL_dMt.m[1][k] *= s.y;
+            dL_dMt.m[2][k] *= s.z;
+        }
+        float4 dq;
+        dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+               2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
+        dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+               2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
+        dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
+               2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
+        dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
+               2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
+        g.drot = dq;
+    }
+}
+
 constexpr int PB_THREADS = 256;
 constexpr int PB_ROW_F4 = 12;      // a degree-3 SH row: 48 floats
 constexpr int PB_ROW_PAD_F4 = 13;  // padded pitch in shared memory (odd number of float4: conflict-free LDS/STS.128)
@@ -297,132 +440,18 @@ __global__ void __launch_bounds__(PB_THREADS, 3) preprocess_bwd_kernel(const Pre
             cov3d_from_scale_rot(sc, a.scale_mod, rq, cov3D);  // recomputed instead of stored (same code as forward)
         }
 
-        // ---- computeCov2DCUDA, backward.cu:162-273 ----
-        const float h_x = a.focal_x, h_y = a.focal_y;
-        Ewa e = ewa_project(mean, h_x, h_y, a.tan_fovx, a.tan_fovy, cov3D, a.view);
-        const float3 t = e.t;
-        const float x_grad_mul = e.txtz < -e.limx || e.txtz > e.limx ? 0 : 1;
-        const float y_grad_mul = e.tytz < -e.limy || e.tytz > e.limy ? 0 : 1;
-        const Mat3& T = e.T;
-        const Mat3& Vrk = e.Vrk;
-        const float ca = e.a, cb = e.b, cc = e.c;
-        float denom = ca * cc - cb * cb;
-        float dL_da = 0, dL_db = 0, dL_dc = 0;
-        float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-        float dL_dcov[6];
-        if (denom2inv != 0) {
-            dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
-            dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
-            dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
-            dL_dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
-            dL_dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
-            dL_dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
-            dL_dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
-                         2 * T.m[1][0] * T.m[1][1] * dL_dc;
-            dL_dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
-                         2 * T.m[1][0] * T.m[1][2] * dL_dc;
-            dL_dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
-                         2 * T.m[1][1] * T.m[1][2] * dL_dc;
-        } else {
-#pragma unroll
-            for (int i = 0; i < 6; i++) dL_dcov[i] = 0;
-        }
+        ViewConst vc{a.view, a.proj, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, a.scale_mod};
+        GeomGrad gg;
+        geom_backward(vc, mean, cov3D, a.scales != nullptr, sc, rq, dL_dmean2D_x, dL_dmean2D_y, dL_dconic, gg);
+        dL_dmean_acc = gg.dmean;
         if (a.dL_dcov3D)
 #pragma unroll
-            for (int i = 0; i < 6; i++) put1(&a.dL_dcov3D[6 * idx + i], dL_dcov[i]);
-
-        float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
-                        (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
-        float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
-                        (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
-        float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
-                        (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
-        float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
-                        (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
-        float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
-                        (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
-        float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
-                        (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
-
-        // W as built in ewa_project: W.m[c][r] = view[4*r + c]  (glm::mat3(view[0], view[4], view[8], ...))
-        const float* vm = a.view;
-        const float W00 = vm[0], W01 = vm[4], W02 = vm[8];
-        const float W10 = vm[1], W11 = vm[5], W12 = vm[9];
-        const float W20 = vm[2], W21 = vm[6], W22 = vm[10];
-        float dL_dJ00 = W00 * dL_dT00 + W01 * dL_dT01 + W02 * dL_dT02;
-        float dL_dJ02 = W20 * dL_dT00 + W21 * dL_dT01 + W22 * dL_dT02;
-        float dL_dJ11 = W10 * dL_dT10 + W11 * dL_dT11 + W12 * dL_dT12;
-        float dL_dJ12 = W20 * dL_dT10 + W21 * dL_dT11 + W22 * dL_dT12;
-
-        float tz = 1.f / t.z;
-        float tz2 = tz * tz;
-        float tz3 = tz2 * tz;
-        float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
-        float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-        float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
-                       (2 * h_y * t.y) * tz3 * dL_dJ12;
-        dL_dmean_acc = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, a.view);
-
-        // ---- preprocessCUDA (backward.cu:366-395) ----
-        const float* proj = a.proj;
-        float4 m_hom = xform_point_4x4(mean, proj);
-        float m_w = 1.0f / (m_hom.w + 0.0000001f);
-        float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
-        float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
-        float3 dL_dmean;
-        dL_dmean.x = (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D_y;
-        dL_dmean.y = (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D_y;
-        dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D_y;
-        dL_dmean_acc.x += dL_dmean.x;
-        dL_dmean_acc.y += dL_dmean.y;
-        dL_dmean_acc.z += dL_dmean.z;
-
-        // ---- computeCov3D backward (backward.cu:278-341) ----
+            for (int i = 0; i < 6; i++) put1(&a.dL_dcov3D[6 * idx + i], gg.dcov[i]);
         if (a.scales != nullptr) {
-            float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
-            Mat3 R = mat3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                          2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                          2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-            Mat3 S = mat3(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
-            float3 s = {a.scale_mod * sc.x, a.scale_mod * sc.y, a.scale_mod * sc.z};
-            S.m[0][0] = s.x;
-            S.m[1][1] = s.y;
-            S.m[2][2] = s.z;
-            Mat3 M = mul(S, R);
-            Mat3 dL_dSigma = mat3(dL_dcov[0], 0.5f * dL_dcov[1], 0.5f * dL_dcov[2], 0.5f * dL_dcov[1], dL_dcov[3],
-                                  0.5f * dL_dcov[4], 0.5f * dL_dcov[2], 0.5f * dL_dcov[4], dL_dcov[5]);
-            // dL_dM = 2.0f * M * dL_dSigma  (glm: scalar*mat first, then the product)
-            Mat3 M2;
-#pragma unroll
-            for (int c = 0; c < 3; c++)
-#pragma unroll
-                for (int rr = 0; rr < 3; rr++) M2.m[c][rr] = 2.0f * M.m[c][rr];
-            Mat3 dL_dM = mul(M2, dL_dSigma);
-            Mat3 Rt = transpose(R);
-            Mat3 dL_dMt = transpose(dL_dM);
-            float3 dsc;
-            dsc.x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
-            dsc.y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
-            dsc.z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
-            put1(&a.dL_dscales[3 * idx + 0], dsc.x);
-            put1(&a.dL_dscales[3 * idx + 1], dsc.y);
-            put1(&a.dL_dscales[3 * idx + 2], dsc.z);
-#pragma unroll
-            for (int k = 0; k < 3; k++) {
-                dL_dMt.m[0][k] *= s.x;
-                dL_dMt.m[1][k] *= s.y;
-                dL_dMt.m[2][k] *= s.z;
-            }
-            float4 dq;
-            dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
-                   2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
-            dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
-                   2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
-            dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) +
-                   2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
-            dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) +
-                   2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
-            put4(&reinterpret_cast<float4*>(a.dL_drots)[idx], dq);
+            put1(&a.dL_dscales[3 * idx + 0], gg.dscale.x);
+            put1(&a.dL_dscales[3 * idx + 1], gg.dscale.y);
+            put1(&a.dL_dscales[3 * idx + 2], gg.dscale.z);
+            put4(&reinterpret_cast<float4*>(a.dL_drots)[idx], gg.drot);
         } else if (!accum) {
             a.dL_dscales[3 * idx + 0] = 0.f;
             a.dL_dscales[3 * idx + 1] = 0.f;
@@ -508,6 +537,140 @@ __global__ void __launch_bounds__(PB_THREADS, 3) preprocess_bwd_kernel(const Pre
         put1(&a.dL_dmeans3D[3 * idx + 1], dL_dmean_acc.y);
         put1(&a.dL_dmeans3D[3 * idx + 2], dL_dmean_acc.z);
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// preprocess_bwd_multi: the same gradients for SEVERAL views of one step in one pass, summed over the views in
+// registers / shared memory. What the views share - the SH rows (192 B per Gaussian at degree 3) - is read once, and
+// every gradient row is written (or added to the caller's buffer) once instead of once per view; per view only the
+// 48-byte accumulator row, mean, rotation, scale, radius and clamp bits are read. A Gaussian invisible in a view
+// contributes nothing for it. Sums are formed in view order. Fast path only: degree 3, M == 16, scale/rotation inputs.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int MV_THREADS = 128;
+constexpr int MV_OUT_PITCH = MV_THREADS + 1;  // [coefficient][thread] accumulators, odd pitch: conflict-free both ways
+
+__global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(const __grid_constant__ MultiBwdArgs a) {
+    extern __shared__ __align__(16) unsigned char mv_smem[];
+    float4* in_rows = reinterpret_cast<float4*>(mv_smem);                                     // [MV_THREADS][13]
+    float* out_acc = reinterpret_cast<float*>(mv_smem + (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16);  // [48][MV_OUT_PITCH]
+    __shared__ uint8_t row_vis[MV_THREADS];
+    const int tid = threadIdx.x;
+    const int base = blockIdx.x * MV_THREADS;
+    const int idx = base + tid;
+    const bool in_range = idx < a.P;
+    const bool accum = a.accumulate != 0;
+    const int nvalid = min(MV_THREADS, a.P - base);
+    {
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)base * PB_ROW_F4;
+        const int total = nvalid * PB_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < PB_ROW_F4; k++) {
+            const int e = tid + k * MV_THREADS;
+            if (e < total) {
+                const int g = e / PB_ROW_F4, j = e - g * PB_ROW_F4;
+                cp_async_16(&in_rows[g * PB_ROW_PAD_F4 + j], src + e);
+            }
+        }
+        cp_async_commit();
+    }
+#pragma unroll
+    for (int k = 0; k < 48; k++) out_acc[k * MV_OUT_PITCH + tid] = 0.f;
+
+    float3 s_mean = {0.f, 0.f, 0.f}, s_scale = {0.f, 0.f, 0.f};
+    float4 s_rot = {0.f, 0.f, 0.f, 0.f};
+    float s_opac = 0.f;
+    bool any_vis = false;
+
+    cp_async_wait_all();
+    __syncthreads();
+    float f[48];
+    {
+        const float4* myrow = &in_rows[tid * PB_ROW_PAD_F4];
+#pragma unroll
+        for (int j = 0; j < PB_ROW_F4; j++) {
+            const float4 v = myrow[j];
+            f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
+        }
+    }
+
+#pragma unroll 1
+    for (int v = 0; v < a.n_views; v++) {
+        const MultiBwdView& V = a.v[v];
+        if (!in_range || V.radii[idx] <= 0) continue;
+        any_vis = true;
+        const float4* acc4 = reinterpret_cast<const float4*>(V.acc + (size_t)idx * ACC_STRIDE);
+        const float4 q0 = acc4[0], q1 = acc4[1], q2 = acc4[2];
+        const float3 mean = {V.means[3 * idx], V.means[3 * idx + 1], V.means[3 * idx + 2]};
+        const float3 sc = {V.scales[3 * idx], V.scales[3 * idx + 1], V.scales[3 * idx + 2]};
+        const float4 rq = __ldg(reinterpret_cast<const float4*>(V.rots) + idx);
+        const uint8_t cl = V.clamped[idx];
+        float cov3D[6];
+        cov3d_from_scale_rot(sc, V.scale_mod, rq, cov3D);
+        const ViewConst vc{V.view, V.proj, V.focal_x, V.focal_y, V.tan_fovx, V.tan_fovy, V.scale_mod};
+        GeomGrad gg;
+        geom_backward(vc, mean, cov3D, true, sc, rq, q0.x, q0.y, make_float3(q0.z, q0.w, q1.x), gg);
+        const float3 cam = {V.campos[0], V.campos[1], V.campos[2]};
+        const float3 dm = sh_backward(
+            3, mean, cam, cl, make_float3(q1.z, q1.w, q2.x),
+            [&](int k) { return make_float3(f[3 * k], f[3 * k + 1], f[3 * k + 2]); },
+            [&](int k, float3 g) {
+                out_acc[(3 * k + 0) * MV_OUT_PITCH + tid] += g.x;
+                out_acc[(3 * k + 1) * MV_OUT_PITCH + tid] += g.y;
+                out_acc[(3 * k + 2) * MV_OUT_PITCH + tid] += g.z;
+            });
+        s_mean.x += gg.dmean.x + dm.x; s_mean.y += gg.dmean.y + dm.y; s_mean.z += gg.dmean.z + dm.z;
+        s_scale.x += gg.dscale.x; s_scale.y += gg.dscale.y; s_scale.z += gg.dscale.z;
+        s_rot.x += gg.drot.x; s_rot.y += gg.drot.y; s_rot.z += gg.drot.z; s_rot.w += gg.drot.w;
+        s_opac += q1.y;
+    }
+
+    row_vis[tid] = any_vis ? 1 : 0;
+    if (in_range && (any_vis || !accum)) {
+        auto put1 = [accum](float* p, float v) { *p = accum ? *p + v : v; };
+        put1(&a.dL_dopacity[idx], s_opac);
+        put1(&a.dL_dmeans3D[3 * idx + 0], s_mean.x);
+        put1(&a.dL_dmeans3D[3 * idx + 1], s_mean.y);
+        put1(&a.dL_dmeans3D[3 * idx + 2], s_mean.z);
+        put1(&a.dL_dscales[3 * idx + 0], s_scale.x);
+        put1(&a.dL_dscales[3 * idx + 1], s_scale.y);
+        put1(&a.dL_dscales[3 * idx + 2], s_scale.z);
+        float4* dr = reinterpret_cast<float4*>(a.dL_drots) + idx;
+        if (accum) {
+            const float4 o = *dr;
+            s_rot.x += o.x; s_rot.y += o.y; s_rot.z += o.z; s_rot.w += o.w;
+        }
+        *dr = s_rot;
+    }
+    __syncthreads();
+    {
+        const int total = nvalid * PB_ROW_F4;
+        float4* dst = reinterpret_cast<float4*>(a.dL_dsh) + (size_t)base * PB_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < PB_ROW_F4; k++) {
+            const int e = tid + k * MV_THREADS;
+            if (e < total) {
+                const int g = e / PB_ROW_F4, j = e - g * PB_ROW_F4;
+                if (accum && !row_vis[g]) continue;  // nothing to add
+                float4 o = make_float4(out_acc[(4 * j + 0) * MV_OUT_PITCH + g], out_acc[(4 * j + 1) * MV_OUT_PITCH + g],
+                                       out_acc[(4 * j + 2) * MV_OUT_PITCH + g], out_acc[(4 * j + 3) * MV_OUT_PITCH + g]);
+                if (accum) {
+                    const float4 p = dst[e];
+                    o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+                }
+                dst[e] = o;
+            }
+        }
+    }
+}
+
+cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s) {
+    const int blocks = (a.P + MV_THREADS - 1) / MV_THREADS;
+    const size_t smem = (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 + (size_t)48 * MV_OUT_PITCH * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    preprocess_bwd_multi_kernel<<<blocks, MV_THREADS, smem, s>>>(a);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s) {

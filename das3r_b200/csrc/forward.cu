@@ -810,8 +810,11 @@ static size_t spread_pad_smem_uncached(const void* kernel, int grid, int block_t
     size_t dyn = per_block - static_smem - 1024;
     dyn = dyn / 256 * 256;
     if (dyn + static_smem > (size_t)smem_optin) dyn = (size_t)smem_optin - static_smem;
+    // The attribute belongs to the kernel, not to this grid size: always raise it to the device limit, never to `dyn`
+    // (a later, smaller request would otherwise lower it under a cached larger one).
     if (dyn > 48 * 1024 - static_smem)
-        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn) != cudaSuccess)
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)((size_t)smem_optin - static_smem)) != cudaSuccess)
             return 0;
     return dyn;
 }

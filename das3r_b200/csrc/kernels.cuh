@@ -53,6 +53,23 @@ struct PreBwdArgs {
     int accumulate;  // 1: outputs += gradient, invisible Gaussians untouched; 0: outputs = gradient (zeros if invisible)
 };
 
+// Multi-view preprocess backward (backward.cu): per-view inputs + what the views share.
+constexpr int MV_MAX_VIEWS = 16;
+struct MultiBwdView {
+    const float *means, *scales, *rots, *view, *proj, *campos;
+    const int* radii;
+    const uint8_t* clamped;
+    const float* acc;  // [P][ACC_STRIDE], filled by this view's backward blend
+    float tan_fovx, tan_fovy, focal_x, focal_y, scale_mod;
+    int pad_;
+};
+struct MultiBwdArgs {
+    int P, n_views, accumulate, pad_;
+    const float* shs;  // [P,16,3], shared by all views
+    float *dL_dopacity, *dL_dmeans3D, *dL_dsh, *dL_dscales, *dL_drots;
+    MultiBwdView v[MV_MAX_VIEWS];
+};
+
 // forward.cu
 cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
 cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,
@@ -87,6 +104,7 @@ cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, cons
                              int W, int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
                              const float* dL_dpix, float* acc, cudaStream_t s);
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
+cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s);
 
 // One-wave launches must be spread evenly: the hardware block scheduler fills an SM up to its occupancy limit before
 // moving on, so a grid smaller than one full wave leaves some SMs empty while others run at the limit (measured on

@@ -329,6 +329,121 @@ torch::Tensor distCUDA2(const torch::Tensor& points_) {
 
 }  // namespace
 
+// ---- split / multi-view backward (das3r_raster_backward_blend / _finish; no reference counterpart) --------------
+// First half for one view: returns the [P,12] float32 accumulator tensor the finish half reads.
+static torch::Tensor BackwardBlendCUDA(const torch::Tensor& background, const torch::Tensor& dL_dout_color_, const int P,
+                                       const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
+                                       const torch::Tensor& imageBuffer, const bool debug) {
+    TORCH_CHECK(dL_dout_color_.is_cuda(), "dL_dout_color must be a CUDA tensor: this rasterizer has no CPU path");
+    const auto dev = dL_dout_color_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    auto bg = prep(background, "bg", dev);
+    auto dL_dout = prep(dL_dout_color_, "dL_dout_color", dev);
+    torch::Tensor scratch = torch::empty({(long long)P, 12}, torch::TensorOptions().dtype(torch::kFloat32).device(dev));
+    if (P == 0) return scratch;
+    das3r_raster_params p;
+    memset(&p, 0, sizeof(p));
+    p.P = P;
+    p.height = dL_dout_color_.size(1);
+    p.width = dL_dout_color_.size(2);
+    p.debug = debug;
+    p.background = fptr(bg);
+    das3r_raster_state st;
+    st.geom = reinterpret_cast<char*>(geomBuffer.data_ptr());
+    st.geom_bytes = geomBuffer.numel();
+    st.binning = binningBuffer.numel() > 0 ? reinterpret_cast<char*>(binningBuffer.data_ptr()) : nullptr;
+    st.binning_bytes = binningBuffer.numel();
+    st.image = reinterpret_cast<char*>(imageBuffer.data_ptr());
+    st.image_bytes = imageBuffer.numel();
+    st.num_rendered = R;
+    das3r_raster_view v;
+    memset(&v, 0, sizeof(v));
+    v.params = &p;
+    v.state = &st;
+    v.dL_dpix = dL_dout.data_ptr<float>();
+    v.scratch = scratch.data_ptr<float>();
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    check(das3r_raster_backward_blend(&v, stream), "rasterize_gaussians_backward_blend");
+    return scratch;
+}
+
+// (means3D, radii, scales, rotations, viewmatrix, projmatrix, tan_fovx, tan_fovy, campos, geomBuffer, accumulators,
+//  image_height, image_width) per view
+using FinishView = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+                              float, float, torch::Tensor, torch::Tensor, torch::Tensor, int, int>;
+
+// Second half for all views of a step: outs = {dL_dopacity [P,1], dL_dmeans3D [P,3], dL_dsh [P,M,3], dL_dscales [P,3],
+// dL_drotations [P,4]} receive (accumulate: are increased by) the sum over the views.
+static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch::Tensor& sh_, const int degree,
+                               const float scale_modifier, const std::vector<torch::Tensor>& outs,
+                               const bool accumulate, const bool debug) {
+    TORCH_CHECK(!views.empty(), "no views");
+    TORCH_CHECK(outs.size() == 5, "expected 5 gradient tensors (opacity, means3D, sh, scales, rotations)");
+    const auto dev = std::get<0>(views[0]).device();
+    TORCH_CHECK(dev.is_cuda(), "means3D must be a CUDA tensor: this rasterizer has no CPU path");
+    c10::cuda::CUDAGuard guard(dev);
+    const int P = std::get<0>(views[0]).size(0);
+    int M = 0;
+    if (sh_.defined() && sh_.dim() == 3) M = sh_.size(1);
+    const int64_t want[5] = {(int64_t)P, 3LL * P, 3LL * M * P, 3LL * P, 4LL * P};
+    for (int i = 0; i < 5; i++)
+        TORCH_CHECK(outs[i].is_cuda() && outs[i].device() == dev && outs[i].scalar_type() == torch::kFloat32 &&
+                        outs[i].is_contiguous() && outs[i].numel() == want[i],
+                    "gradient buffer ", i, " must be a contiguous float32 CUDA tensor of ", want[i], " elements");
+    if (P == 0) return;
+    auto sh = prep(sh_, "shs", dev);
+    const size_t n = views.size();
+    std::vector<das3r_raster_params> ps(n);
+    std::vector<das3r_raster_inputs> ins(n);
+    std::vector<das3r_raster_state> sts(n);
+    std::vector<das3r_raster_view> vs(n);
+    std::vector<torch::Tensor> keep;  // contiguous copies must outlive the launch
+    for (size_t i = 0; i < n; i++) {
+        const auto& V = views[i];
+        TORCH_CHECK(std::get<0>(V).size(0) == P, "the views differ in the number of Gaussians");
+        auto means3D = prep(std::get<0>(V), "means3D", dev);
+        auto radii = std::get<1>(V).contiguous();
+        TORCH_CHECK(radii.scalar_type() == torch::kInt32, "radii must be int32");
+        auto scales = prep(std::get<2>(V), "scales", dev);
+        auto rotations = prep(std::get<3>(V), "rotations", dev);
+        auto view = prep(std::get<4>(V), "viewmatrix", dev);
+        auto proj = prep(std::get<5>(V), "projmatrix", dev);
+        auto campos = prep(std::get<8>(V), "campos", dev);
+        const auto& geom = std::get<9>(V);
+        const auto& acc = std::get<10>(V);
+        TORCH_CHECK(acc.is_cuda() && acc.scalar_type() == torch::kFloat32 && acc.is_contiguous() &&
+                        acc.numel() == 12LL * P,
+                    "accumulators must be the tensor rasterize_gaussians_backward_blend returned");
+        for (const auto& t : {means3D, radii, scales, rotations, view, proj, campos}) keep.push_back(t);
+        memset(&ps[i], 0, sizeof(ps[i]));
+        ps[i].P = P; ps[i].D = degree; ps[i].M = M;
+        ps[i].height = std::get<11>(V); ps[i].width = std::get<12>(V);
+        ps[i].tan_fovx = std::get<6>(V); ps[i].tan_fovy = std::get<7>(V);
+        ps[i].scale_modifier = scale_modifier;
+        ps[i].debug = debug;
+        ps[i].viewmatrix = fptr(view); ps[i].projmatrix = fptr(proj); ps[i].campos = fptr(campos);
+        memset(&ins[i], 0, sizeof(ins[i]));
+        ins[i].means3D = fptr(means3D); ins[i].shs = fptr(sh); ins[i].scales = fptr(scales);
+        ins[i].rotations = fptr(rotations);
+        memset(&sts[i], 0, sizeof(sts[i]));
+        sts[i].geom = reinterpret_cast<char*>(geom.data_ptr());
+        sts[i].geom_bytes = geom.numel();
+        memset(&vs[i], 0, sizeof(vs[i]));
+        vs[i].params = &ps[i]; vs[i].in = &ins[i]; vs[i].radii = radii.data_ptr<int>(); vs[i].state = &sts[i];
+        vs[i].scratch = acc.data_ptr<float>();
+    }
+    das3r_raster_grads g;
+    memset(&g, 0, sizeof(g));
+    g.dL_dopacity = outs[0].data_ptr<float>();
+    g.dL_dmeans3D = outs[1].data_ptr<float>();
+    g.dL_dsh = M > 0 ? outs[2].data_ptr<float>() : nullptr;
+    g.dL_dscales = outs[3].data_ptr<float>();
+    g.dL_drotations = outs[4].data_ptr<float>();
+    g.accumulate = accumulate ? 1 : 0;
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    check(das3r_raster_backward_finish((int32_t)n, vs.data(), &g, stream), "rasterize_gaussians_backward_finish");
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     // The GIL is released around every call into the library: a host that drives several CUDA streams from several
     // threads (bench.py) must not serialise on the forward's read-back of num_rendered.
@@ -336,6 +451,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians_ex", &RasterizeGaussiansExCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardIntoCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_backward_blend", &BackwardBlendCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_backward_finish", &BackwardFinishCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
     m.def("prof_collect", [](bool reset) {
         int n = das3r_prof_num_stages();

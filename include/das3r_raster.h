@@ -127,6 +127,39 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
                           const int32_t* radii, const das3r_raster_state* state,
                           const float* dL_dpix, const das3r_raster_grads* grads, void* stream);
 
+/* The backward in two halves, so that a training step over several views reads what the views share only once.
+ * It has no counterpart in the reference, whose Rasterizer::backward (rasterizer_impl.cu:340-434) handles one view per
+ * call and leaves the sum over views to autograd.
+ *
+ *   das3r_raster_backward_blend(view, stream)      first half for ONE view: the backward blend (replaces renderCUDA,
+ *                                                  backward.cu:399-557). Fills view->scratch
+ *                                                  (das3r_raster_backward_scratch_bytes(P) bytes, one buffer per view)
+ *                                                  with the screen-space gradient sums. Views are independent: issue
+ *                                                  them on as many streams as you like.
+ *   das3r_raster_backward_finish(n, views, grads, stream)
+ *                                                  second half for n >= 1 views at once (computeCov2DCUDA,
+ *                                                  preprocessCUDA, SH and cov3D backward: backward.cu:20-396):
+ *                                                  grads = (grads->accumulate ? grads : 0) + sum over the views, i.e.
+ *                                                  what n das3r_raster_backward calls with accumulate would leave,
+ *                                                  summed in view order. All blend halves must have completed on
+ *                                                  `stream` (or be ordered before it by events). grads->scratch is
+ *                                                  not used. With n > 1, dL_dmeans2D / dL_dcolors / dL_dcov3D must be
+ *                                                  NULL (per-view quantities).
+ * When the views use the same `shs` array at degree 3 with scale / rotation inputs (DAS3R's default: the pose moves
+ * means and rotations, not the appearance), the SH rows are read once and every gradient row is written once for the
+ * whole step; otherwise the call runs one accumulating pass per view. All views must agree in P, D and M. */
+typedef struct das3r_raster_view {
+    const das3r_raster_params* params;
+    const das3r_raster_inputs* in;
+    const int32_t* radii;              /* the forward's output */
+    const das3r_raster_state* state;   /* the forward's state blobs */
+    const float* dL_dpix;              /* [3,H,W] (blend half only) */
+    float* scratch;                    /* per-view, written by the blend half, read by the finish half */
+} das3r_raster_view;
+int das3r_raster_backward_blend(const das3r_raster_view* view, void* stream);
+int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* grads,
+                                 void* stream);
+
 /* Backward for hosts that cannot allocate device memory. It has no counterpart in the reference.
  *
  * das3r_raster_backward needs `grads->scratch`, a P*48-byte device buffer the caller normally takes from its allocator

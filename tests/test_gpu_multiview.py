@@ -1,0 +1,122 @@
+"""das3r_raster_backward_blend + das3r_raster_backward_finish: the backward split in two halves so that the views of a
+training step share one pass over the Gaussians (no counterpart in the reference; its backward handles one view per
+call, rasterizer_impl.cu:340-434, and autograd sums).
+
+Bar: the sum the fused pass leaves equals the sum of the per-view gradients of the regular backward (which the other
+parity tests pin to the reference) within the gradient tolerance - run-to-run atomic order and the order of the float
+additions are the only differences. Covered: the fused path (degree 3, shared SH rows), the per-view fallback (degree 1),
+accumulate on / off, one view, more views than one launch takes, Gaussians invisible in some or all views.
+"""
+import pytest
+import torch
+
+import _harness as Hn
+from das3r_b200 import load_native
+from das3r_b200.synth import synth_scene, view_inputs
+
+pytestmark = pytest.mark.gpu
+
+NAMES = ("dL_dopacity", "dL_dmeans3D", "dL_dsh", "dL_dscales", "dL_drotations")
+IDX = (2, 3, 5, 6, 7)  # their position in the 8-tuple of rasterize_gaussians_backward
+
+
+def _scene_views(P, V, W, H, D, seed, dev):
+    sc = synth_scene(P=P, V=max(V, 2), W=W, H=H, seed=seed, sh_degree=D)
+    views = []
+    for v in range(V):
+        vi = view_inputs(sc, v, sh_degree=D)
+        views.append({k: (x.contiguous().to(dev) if isinstance(x, torch.Tensor) else x) for k, x in vi.items()})
+    shs = views[0]["shs"]
+    for vi in views:  # one SH array for all views, as in DAS3R (the pose moves means and rotations only)
+        vi["shs"] = shs
+    g = torch.Generator().manual_seed(seed + 100)
+    dLs = [(torch.randn(3, H, W, generator=g) / (W * H)).to(dev) for _ in range(V)]
+    return views, dLs
+
+
+def _forward(C, vi, D):
+    e = torch.Tensor([])
+    return C.rasterize_gaussians(vi["bg"], vi["means3D"], e, vi["opacities"], vi["scales"], vi["rotations"], 1.0, e,
+                                 vi["viewmatrix"], vi["projmatrix"], vi["tanfovx"], vi["tanfovy"], vi["image_height"],
+                                 vi["image_width"], vi["shs"], D, vi["campos"], False, False)
+
+
+def _regular_sum(C, views, dLs, D):
+    """Sum over the views of the regular per-view backward (fresh buffers per view, summed in float64)."""
+    e = torch.Tensor([])
+    tot = None
+    states = []
+    for vi, dL in zip(views, dLs):
+        R, color, radii, geom, binning, img = _forward(C, vi, D)
+        states.append((R, radii, geom, binning, img))
+        out = C.rasterize_gaussians_backward(vi["bg"], vi["means3D"], radii, e, vi["scales"], vi["rotations"], 1.0, e,
+                                             vi["viewmatrix"], vi["projmatrix"], vi["tanfovx"], vi["tanfovy"], dL,
+                                             vi["shs"], D, vi["campos"], geom, R, binning, img, False)
+        g = [out[i].double() for i in IDX]
+        tot = g if tot is None else [a + b for a, b in zip(tot, g)]
+    return tot, states
+
+
+def _fused(C, views, dLs, states, D, outs, accumulate):
+    fv = []
+    for vi, dL, (R, radii, geom, binning, img) in zip(views, dLs, states):
+        acc = C.rasterize_gaussians_backward_blend(vi["bg"], dL, vi["means3D"].shape[0], geom, R, binning, img, False)
+        fv.append((vi["means3D"], radii, vi["scales"], vi["rotations"], vi["viewmatrix"], vi["projmatrix"],
+                   float(vi["tanfovx"]), float(vi["tanfovy"]), vi["campos"], geom, acc, int(vi["image_height"]),
+                   int(vi["image_width"])))
+    C.rasterize_gaussians_backward_finish(fv, views[0]["shs"], D, 1.0, outs, accumulate, False)
+    torch.cuda.synchronize()
+
+
+def _fresh(P, M, dev, fill=float("nan")):
+    shapes = ((P, 1), (P, 3), (P, M, 3), (P, 3), (P, 4))
+    return [torch.full(s, fill, device=dev) for s in shapes]
+
+
+def _check(outs, want, what):
+    for n, o, w in zip(NAMES, outs, want):
+        assert bool(torch.isfinite(o).all()), f"{what}: {n} has elements the call did not write"
+        err = Hn.rel_err(o.double().cpu().numpy(), w.cpu().numpy())
+        assert err <= Hn.GRAD_RTOL, f"{what}: {n} differs from the sum of per-view backwards by {err}"
+
+
+@pytest.mark.parametrize("D,V", [(3, 4), (1, 3), (3, 1), (3, 18)])
+def test_sum_over_views_matches_the_per_view_backward(D, V):
+    dev = torch.device("cuda:0")
+    C = load_native()
+    P, W, H = 20_000, 160, 96
+    views, dLs = _scene_views(P, V, W, H, D, seed=11 + D, dev=dev)
+    M = views[0]["shs"].shape[1]
+    want, states = _regular_sum(C, views, dLs, D)
+
+    outs = _fresh(P, M, dev)
+    _fused(C, views, dLs, states, D, outs, accumulate=False)
+    _check(outs, want, f"D={D} V={V} overwrite")
+
+    # accumulate: a second identical call on top of the first doubles everything, nothing else is touched
+    _fused(C, views, dLs, states, D, outs, accumulate=True)
+    _check(outs, [2 * w for w in want], f"D={D} V={V} accumulate")
+
+
+def test_gaussians_outside_every_view_get_zeros_or_stay_untouched():
+    dev = torch.device("cuda:0")
+    C = load_native()
+    D, V, P, W, H = 3, 3, 6_000, 128, 80
+    views, dLs = _scene_views(P, V, W, H, D, seed=5, dev=dev)
+    hidden = torch.arange(0, P, 7, device=dev)
+    for vi in views:  # behind the camera in all views
+        m = vi["means3D"].clone()
+        m[hidden, 2] = -1.0
+        vi["means3D"] = m
+    want, states = _regular_sum(C, views, dLs, D)
+    for r in states:
+        assert int((r[1][hidden] > 0).sum()) == 0
+    outs = _fresh(P, 16, dev)
+    _fused(C, views, dLs, states, D, outs, accumulate=False)
+    _check(outs, want, "overwrite")
+    for o in outs:
+        assert float(o[hidden].abs().max()) == 0.0
+    marked = _fresh(P, 16, dev, fill=3.0)
+    _fused(C, views, dLs, states, D, marked, accumulate=True)
+    for o in marked:
+        assert bool((o[hidden] == 3.0).all()), "accumulate mode wrote to a Gaussian no view rendered"
