@@ -243,7 +243,7 @@ def main():
         last_R[0] = R
         acc = C.rasterize_gaussians_backward_blend(S["bg"], dL, P, geom, R, binning, img, False)
         return (pv["means"], radii, S["scales"], pv["rots"], S["view"], S["proj"], float(S["tanx"]), float(S["tany"]),
-                S["campos"], geom, acc, H, W)
+                S["campos"], geom, acc, H, W, empty, empty)
 
     def finish(fviews, bk):
         """second half of the backward for all views of the step: one pass, gradients summed over the views."""

@@ -465,6 +465,7 @@ int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views
         const das3r_raster_inputs* in = views[v].in;
         fused = in->shs == views[0].in->shs && in->scales && in->rotations && !in->cov3D_precomp && !in->colors_precomp &&
                 ((reinterpret_cast<uintptr_t>(in->rotations) & 15) == 0) &&
+                ((reinterpret_cast<uintptr_t>(views[v].dL_drotations) & 15) == 0) &&
                 views[v].state->geom_bytes >= L.geom_bytes;
     }
     if (fused) {
@@ -485,6 +486,8 @@ int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views
                 m.radii = V.radii;
                 m.clamped = reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped);
                 m.acc = V.scratch;
+                m.dL_dmeans3D = V.dL_dmeans3D;
+                m.dL_drots = V.dL_drotations;
                 m.tan_fovx = V.params->tan_fovx; m.tan_fovy = V.params->tan_fovy;
                 m.focal_x = V.params->width / (2.0f * V.params->tan_fovx);
                 m.focal_y = V.params->height / (2.0f * V.params->tan_fovy);
@@ -501,6 +504,21 @@ int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views
         PreBwdArgs a;
         fill_prebwd_args(a, V.params, V.in, V.radii, reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped),
                          V.scratch, g, v == 0 ? g->accumulate : 1);
+        if (V.dL_dmeans3D || V.dL_drotations) {
+            // The one-view kernel has one accumulate switch for all outputs: a view with outputs of its own (which
+            // follow grads->accumulate) cannot share a launch with the summed ones (which accumulate from the second
+            // view on) unless both agree.
+            if (a.accumulate != g->accumulate)
+                return fail_msg(DAS3R_EINVAL, "backward_finish: per-view dL_dmeans3D / dL_drotations outside the fused "
+                                              "path need grads->accumulate = 1 (or a single view)");
+            // the summed output this view does not feed still has to be defined
+            if (!g->accumulate && V.dL_dmeans3D)
+                STAGE(cudaMemsetAsync(g->dL_dmeans3D, 0, (size_t)P * 3 * sizeof(float), stream), "memset(dL_dmeans3D)", ST_MEMSET, 0);
+            if (!g->accumulate && V.dL_drotations)
+                STAGE(cudaMemsetAsync(g->dL_drotations, 0, (size_t)P * 4 * sizeof(float), stream), "memset(dL_drotations)", ST_MEMSET, 0);
+            if (V.dL_dmeans3D) a.dL_dmeans3D = V.dL_dmeans3D;
+            if (V.dL_drotations) a.dL_drots = V.dL_drotations;
+        }
         STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd", ST_PREPROCESS_BWD, 1);
     }
     return DAS3R_OK;

@@ -596,7 +596,17 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
 #pragma unroll 1
     for (int v = 0; v < a.n_views; v++) {
         const MultiBwdView& V = a.v[v];
-        if (!in_range || V.radii[idx] <= 0) continue;
+        if (!in_range) continue;
+        if (V.radii[idx] <= 0) {
+            // not rendered in this view: a per-view output still has to be defined
+            if (!accum) {
+                if (V.dL_dmeans3D) {
+                    V.dL_dmeans3D[3 * idx] = 0.f; V.dL_dmeans3D[3 * idx + 1] = 0.f; V.dL_dmeans3D[3 * idx + 2] = 0.f;
+                }
+                if (V.dL_drots) reinterpret_cast<float4*>(V.dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            continue;
+        }
         any_vis = true;
         const float4* acc4 = reinterpret_cast<const float4*>(V.acc + (size_t)idx * ACC_STRIDE);
         const float4 q0 = acc4[0], q1 = acc4[1], q2 = acc4[2];
@@ -618,9 +628,27 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
                 out_acc[(3 * k + 1) * MV_OUT_PITCH + tid] += g.y;
                 out_acc[(3 * k + 2) * MV_OUT_PITCH + tid] += g.z;
             });
-        s_mean.x += gg.dmean.x + dm.x; s_mean.y += gg.dmean.y + dm.y; s_mean.z += gg.dmean.z + dm.z;
+        const float3 gm = {gg.dmean.x + dm.x, gg.dmean.y + dm.y, gg.dmean.z + dm.z};
+        if (V.dL_dmeans3D) {
+            float* o = V.dL_dmeans3D + 3 * (size_t)idx;
+            o[0] = accum ? o[0] + gm.x : gm.x;
+            o[1] = accum ? o[1] + gm.y : gm.y;
+            o[2] = accum ? o[2] + gm.z : gm.z;
+        } else {
+            s_mean.x += gm.x; s_mean.y += gm.y; s_mean.z += gm.z;
+        }
+        if (V.dL_drots) {
+            float4* o = reinterpret_cast<float4*>(V.dL_drots) + idx;
+            float4 r = gg.drot;
+            if (accum) {
+                const float4 p = *o;
+                r.x += p.x; r.y += p.y; r.z += p.z; r.w += p.w;
+            }
+            *o = r;
+        } else {
+            s_rot.x += gg.drot.x; s_rot.y += gg.drot.y; s_rot.z += gg.drot.z; s_rot.w += gg.drot.w;
+        }
         s_scale.x += gg.dscale.x; s_scale.y += gg.dscale.y; s_scale.z += gg.dscale.z;
-        s_rot.x += gg.drot.x; s_rot.y += gg.drot.y; s_rot.z += gg.drot.z; s_rot.w += gg.drot.w;
         s_opac += q1.y;
     }
 

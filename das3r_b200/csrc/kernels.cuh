@@ -60,6 +60,7 @@ struct MultiBwdView {
     const int* radii;
     const uint8_t* clamped;
     const float* acc;  // [P][ACC_STRIDE], filled by this view's backward blend
+    float *dL_dmeans3D, *dL_drots;  // optional per-view outputs (see das3r_raster_view); NULL: summed into the shared ones
     float tan_fovx, tan_fovy, focal_x, focal_y, scale_mod;
     int pad_;
 };

@@ -368,9 +368,11 @@ static torch::Tensor BackwardBlendCUDA(const torch::Tensor& background, const to
 }
 
 // (means3D, radii, scales, rotations, viewmatrix, projmatrix, tan_fovx, tan_fovy, campos, geomBuffer, accumulators,
-//  image_height, image_width) per view
+//  image_height, image_width, dL_dmeans3D_view, dL_drotations_view) per view; the last two are optional outputs (empty
+//  tensor: the view's gradient joins the summed dL_dmeans3D / dL_drotations)
 using FinishView = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
-                              float, float, torch::Tensor, torch::Tensor, torch::Tensor, int, int>;
+                              float, float, torch::Tensor, torch::Tensor, torch::Tensor, int, int, torch::Tensor,
+                              torch::Tensor>;
 
 // Second half for all views of a step: outs = {dL_dopacity [P,1], dL_dmeans3D [P,3], dL_dsh [P,M,3], dL_dscales [P,3],
 // dL_drotations [P,4]} receive (accumulate: are increased by) the sum over the views.
@@ -431,6 +433,18 @@ static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch
         memset(&vs[i], 0, sizeof(vs[i]));
         vs[i].params = &ps[i]; vs[i].in = &ins[i]; vs[i].radii = radii.data_ptr<int>(); vs[i].state = &sts[i];
         vs[i].scratch = acc.data_ptr<float>();
+        const auto& gm = std::get<13>(V);
+        const auto& gr = std::get<14>(V);
+        if (gm.defined() && gm.numel() > 0) {
+            TORCH_CHECK(gm.is_cuda() && gm.scalar_type() == torch::kFloat32 && gm.is_contiguous() && gm.numel() == 3LL * P,
+                        "per-view dL_dmeans3D must be a contiguous float32 CUDA tensor of 3*P elements");
+            vs[i].dL_dmeans3D = gm.data_ptr<float>();
+        }
+        if (gr.defined() && gr.numel() > 0) {
+            TORCH_CHECK(gr.is_cuda() && gr.scalar_type() == torch::kFloat32 && gr.is_contiguous() && gr.numel() == 4LL * P,
+                        "per-view dL_drotations must be a contiguous float32 CUDA tensor of 4*P elements");
+            vs[i].dL_drotations = gr.data_ptr<float>();
+        }
     }
     das3r_raster_grads g;
     memset(&g, 0, sizeof(g));

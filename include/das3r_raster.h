@@ -155,6 +155,11 @@ typedef struct das3r_raster_view {
     const das3r_raster_state* state;   /* the forward's state blobs */
     const float* dL_dpix;              /* [3,H,W] (blend half only) */
     float* scratch;                    /* per-view, written by the blend half, read by the finish half */
+    float* dL_dmeans3D;                /* optional [P,3]: this view's gradient w.r.t. ITS means3D goes here instead of
+                                          into grads->dL_dmeans3D (DAS3R hands every view its own pose-transformed means
+                                          and rotations, gaussian_renderer/__init__.py:83-92, so their gradients have to
+                                          go back through that view's pose); NULL: summed into grads->dL_dmeans3D */
+    float* dL_drotations;              /* optional [P,4], likewise for the rotations */
 } das3r_raster_view;
 int das3r_raster_backward_blend(const das3r_raster_view* view, void* stream);
 int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* grads,

@@ -57,13 +57,16 @@ def _regular_sum(C, views, dLs, D):
     return tot, states
 
 
-def _fused(C, views, dLs, states, D, outs, accumulate):
+def _fused(C, views, dLs, states, D, outs, accumulate, per_view=None):
+    """per_view: optional list (one entry per view) of (dL_dmeans3D, dL_drotations) tensors or None"""
     fv = []
-    for vi, dL, (R, radii, geom, binning, img) in zip(views, dLs, states):
+    e = torch.Tensor([])
+    for i, (vi, dL, (R, radii, geom, binning, img)) in enumerate(zip(views, dLs, states)):
         acc = C.rasterize_gaussians_backward_blend(vi["bg"], dL, vi["means3D"].shape[0], geom, R, binning, img, False)
+        pm, pr = (per_view[i] if per_view and per_view[i] is not None else (e, e))
         fv.append((vi["means3D"], radii, vi["scales"], vi["rotations"], vi["viewmatrix"], vi["projmatrix"],
                    float(vi["tanfovx"]), float(vi["tanfovy"]), vi["campos"], geom, acc, int(vi["image_height"]),
-                   int(vi["image_width"])))
+                   int(vi["image_width"]), pm, pr))
     C.rasterize_gaussians_backward_finish(fv, views[0]["shs"], D, 1.0, outs, accumulate, False)
     torch.cuda.synchronize()
 
@@ -96,6 +99,42 @@ def test_sum_over_views_matches_the_per_view_backward(D, V):
     # accumulate: a second identical call on top of the first doubles everything, nothing else is touched
     _fused(C, views, dLs, states, D, outs, accumulate=True)
     _check(outs, [2 * w for w in want], f"D={D} V={V} accumulate")
+
+
+@pytest.mark.parametrize("D", [3, 1])
+def test_per_view_mean_and_rotation_gradients(D):
+    """Views 0 and 2 ask for their own dL_dmeans3D / dL_drotations (what DAS3R needs to go back through each view's
+    pose); view 1 joins the summed outputs. D=1 exercises the per-view fallback, which supports this only when
+    accumulating."""
+    dev = torch.device("cuda:0")
+    C = load_native()
+    V, P, W, H = 3, 8_000, 128, 80
+    views, dLs = _scene_views(P, V, W, H, D, seed=21, dev=dev)
+    M = views[0]["shs"].shape[1]
+    e = torch.Tensor([])
+    singles, states = [], []
+    for vi, dL in zip(views, dLs):
+        R, color, radii, geom, binning, img = _forward(C, vi, D)
+        states.append((R, radii, geom, binning, img))
+        out = C.rasterize_gaussians_backward(vi["bg"], vi["means3D"], radii, e, vi["scales"], vi["rotations"], 1.0, e,
+                                             vi["viewmatrix"], vi["projmatrix"], vi["tanfovx"], vi["tanfovy"], dL,
+                                             vi["shs"], D, vi["campos"], geom, R, binning, img, False)
+        singles.append([out[i].double() for i in IDX])
+    accumulate = D != 3
+    fill = 0.0 if accumulate else float("nan")
+    outs = _fresh(P, M, dev, fill=fill)
+    per_view = [(torch.full((P, 3), fill, device=dev), torch.full((P, 4), fill, device=dev)), None,
+                (torch.full((P, 3), fill, device=dev), torch.full((P, 4), fill, device=dev))]
+    _fused(C, views, dLs, states, D, outs, accumulate=accumulate, per_view=per_view)
+    want = [sum(s[k] for s in singles) for k in range(5)]
+    want[1] = singles[1][1]  # summed dL_dmeans3D: view 1 only
+    want[4] = singles[1][4]  # summed dL_drotations: view 1 only
+    _check(outs, want, "summed outputs")
+    for v in (0, 2):
+        for got, w, n in ((per_view[v][0], singles[v][1], "dL_dmeans3D"), (per_view[v][1], singles[v][4], "dL_drotations")):
+            assert bool(torch.isfinite(got).all())
+            err = Hn.rel_err(got.double().cpu().numpy(), w.cpu().numpy())
+            assert err <= Hn.GRAD_RTOL, f"view {v} {n}: {err}"
 
 
 def test_gaussians_outside_every_view_get_zeros_or_stay_untouched():
