@@ -296,7 +296,7 @@ def main():
                 finish(fviews, buckets[b][0])
                 for fv in fviews:  # the per-view tensors were allocated on side streams and are last read on `main`
                     for t in fv:
-                        if isinstance(t, torch.Tensor):
+                        if isinstance(t, torch.Tensor) and t.is_cuda:
                             t.record_stream(main)
             else:
                 for si in range(1, S_):
