@@ -146,8 +146,26 @@ def view_bytes(P, R, N, T, s):
     return P * (318 + 3 * s) + 124 * R + 40 * N + 8 * T
 
 
+_JSON_FD = None
+
+
+def emit(obj):
+    """The one JSON line goes to the process's ORIGINAL stdout; everything else written to fd 1 (NCCL prints its version
+    banner there from native code, whatever NCCL_DEBUG_FILE says) has been pointed at stderr by main()."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
+
 def main():
+    global _JSON_FD
     args = parse_args()
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -177,7 +195,7 @@ def main():
         import oracle
         if not oracle.reference_available():
             if rank == 0:
-                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (run oracle/build_ref.sh "
+                emit(({"impl": "reference", "unavailable": "oracle/_ref not built (run oracle/build_ref.sh "
                                   "where /root/reference exists)"}))
             return
         C, _ = oracle.load_reference()
@@ -367,7 +385,7 @@ def main():
         out["e2e"] = {"value": out["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
         out["clocks"] = clocks
         if rank == 0:
-            print(json.dumps(out))
+            emit((out))
         if world > 1:
             dist.destroy_process_group()
         return
@@ -416,7 +434,7 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args, sc)
     if rank == 0:
-        print(json.dumps(out))
+        emit((out))
     if world > 1:
         dist.destroy_process_group()
 
@@ -518,7 +536,7 @@ def run_cpu_arm(args):
 
     sc = synth_scene(P=args.P, V=args.V, W=args.W, H=args.H, seed=args.seed, sh_degree=args.sh_degree)
     cb = cpu_baseline(args, sc)
-    print(json.dumps({"impl": "oracle-cpu", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 0,
+    emit(({"impl": "oracle-cpu", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 0,
                       "steps": args.cpu_views, "warmup": 1, "ms_per_step": round(1e3 / cb["value"], 2),
                       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                       "data": "synthetic", "config": {"workload": cb["sample"]}, "cpu_baseline": cb,
