@@ -411,9 +411,14 @@ def main():
     achieved = sb[dom] / (kern[dom] * 1e-3) / 1e9
     vb = view_bytes(P, R, N, T, s_bytes)
     per_view_ms = elapsed_ms / (vps * args.steps)
+    traffic = None
+    try:  # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (not measured by this run)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(dom)
+    except Exception:
+        pass
     out["roofline"] = {
         "bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-        "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+        "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": sb[dom], "avg_launch_ms": round(kern[dom], 5),
         "timing": f"CUDA events around every stage on the launching stream, {prof_steps} single-stream steps right "
                   "after the timed region",
