@@ -445,72 +445,119 @@ def main():
 
 
 def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
-    """views/s through the drop-in Python surface. Per view, inside the timed region: H2D (pinned) of the camera bundle
-    (viewmatrix 16 + projmatrix 16 + campos 3 + bg 3 floats) and of dL/d(colour) [3,H,W]; forward; loss; autograd
-    backward (gradients accumulate in the leaves' .grad); D2H of the rendered image and the loss. The Gaussian
-    parameters are the resident model state (like weights). For N > 1 the leaf gradients are all-reduced once per
-    step."""
+    """views/s through the public Python API with HOST inputs. Per view, inside the timed region: H2D (pinned) of the
+    camera bundle (viewmatrix 16 + projmatrix 16 + campos 3 + bg 3 floats) and of dL/d(colour) [3,H,W]; forward; loss;
+    autograd backward; D2H of the rendered image; D2H of the step's loss. The Gaussian parameters are the resident
+    model state (like weights). For N > 1 the leaf gradients are all-reduced once per step.
+
+    Two surfaces are timed: `MultiViewRasterizer` (das3r_b200/multiview.py: all views of the step in one autograd node -
+    the headline `value`) and the drop-in per-view `GaussianRasterizer` (`per_view_api`)."""
     from das3r_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    from das3r_b200.multiview import MultiViewRasterizer
     from das3r_b200 import sharding
 
     W, H, D, vps = args.W, args.H, args.sh_degree, args.views_per_step
     cam_host = torch.cat([S["view"].flatten().cpu(), S["proj"].flatten().cpu(), S["campos"].cpu(), S["bg"].cpu()]).pin_memory()
     dL_host = dL.cpu().pin_memory()
-    cam_dev = torch.empty_like(cam_host, device=dev)
-    dL_dev = torch.empty_like(dL_host, device=dev)
-    img_host = torch.empty(3, H, W).pin_memory()
+    cam_dev = [torch.empty_like(cam_host, device=dev) for _ in range(vps)]
+    dL_dev = [torch.empty_like(dL_host, device=dev) for _ in range(vps)]
+    img_host = [torch.empty(3, H, W).pin_memory() for _ in range(vps)]
     loss_host = torch.empty(1).pin_memory()
     leaves = dict(shs=S["shs"].clone().requires_grad_(True), opac=S["opac"].clone().requires_grad_(True),
                   scales=S["scales"].clone().requires_grad_(True))
     per_view = [dict(means=pv["means"].clone().requires_grad_(True), rots=pv["rots"].clone().requires_grad_(True))
                 for pv in pool]
     means2D = torch.zeros(args.P, 3, device=dev, requires_grad=True)
+    all_leaves = list(leaves.values()) + [means2D] + [x for pv in per_view for x in pv.values()]
+    mv = MultiViewRasterizer(streams=max(1, min(args.streams, vps)))
+    copy_stream = torch.cuda.Stream(device=dev)
 
-    def one_view(pv):
-        cam_dev.copy_(cam_host, non_blocking=True)
-        dL_dev.copy_(dL_host, non_blocking=True)
-        settings = GaussianRasterizationSettings(
-            image_height=H, image_width=W, tanfovx=S["tanx"], tanfovy=S["tany"], bg=cam_dev[35:38], scale_modifier=1.0,
-            viewmatrix=cam_dev[0:16].view(4, 4), projmatrix=cam_dev[16:32].view(4, 4), sh_degree=D,
-            campos=cam_dev[32:35], prefiltered=False, debug=False)
-        color, _radii = GaussianRasterizer(settings)(means3D=pv["means"], means2D=means2D, opacities=leaves["opac"],
-                                                     shs=leaves["shs"], scales=leaves["scales"], rotations=pv["rots"])
-        loss = (color * dL_dev).sum()
-        loss.backward()
-        img_host.copy_(color.detach(), non_blocking=True)
-        loss_host.copy_(loss.detach().view(1), non_blocking=True)
+    def settings_for(v):
+        c = cam_dev[v]
+        return GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=S["tanx"], tanfovy=S["tany"], bg=c[35:38], scale_modifier=1.0,
+            viewmatrix=c[0:16].view(4, 4), projmatrix=c[16:32].view(4, 4), sh_degree=D, campos=c[32:35],
+            prefiltered=False, debug=False)
 
-    def step():
-        for t in list(leaves.values()) + [means2D] + [x for pv in per_view for x in pv.values()]:
-            if t.grad is not None:
-                t.grad.zero_()
-        for pv in per_view:
-            one_view(pv)
+    def reduce_grads():
         if world > 1:
             for t in (leaves["shs"], leaves["opac"], leaves["scales"], per_view[0]["means"], per_view[0]["rots"]):
                 dist.all_reduce(t.grad)
-        torch.cuda.current_stream().synchronize()  # the step's image and loss are on the host now
+
+    def step_multi():
+        main = torch.cuda.current_stream()
+        for t in all_leaves:
+            t.grad = None  # optimizer.zero_grad(set_to_none=True)
+        for v in range(vps):
+            cam_dev[v].copy_(cam_host, non_blocking=True)
+        copy_stream.wait_stream(main)  # the previous step is done with dL_dev
+        with torch.cuda.stream(copy_stream):
+            for v in range(vps):
+                dL_dev[v].copy_(dL_host, non_blocking=True)  # only needed by the loss: overlaps the forwards
+        colors, _radii = mv([settings_for(v) for v in range(vps)], [pv["means"] for pv in per_view],
+                            [pv["rots"] for pv in per_view], leaves["opac"], leaves["shs"], leaves["scales"])
+        main.wait_stream(copy_stream)
+        loss = sum((c * dL_dev[v]).sum() for v, c in enumerate(colors))
+        copy_stream.wait_stream(main)
+        with torch.cuda.stream(copy_stream):  # images go home while the backward runs
+            for v, c in enumerate(colors):
+                img_host[v].copy_(c.detach(), non_blocking=True)
+                c.record_stream(copy_stream)
+        loss.backward()
+        loss_host.copy_(loss.detach().view(1), non_blocking=True)
+        reduce_grads()
+        main.wait_stream(copy_stream)
+        main.synchronize()  # the step's images and loss are on the host now
+
+    def step_per_view():
+        for t in all_leaves:
+            if t.grad is not None:
+                t.grad.zero_()
+        total = None
+        for v, pv in enumerate(per_view):
+            cam_dev[v].copy_(cam_host, non_blocking=True)
+            dL_dev[v].copy_(dL_host, non_blocking=True)
+            color, _radii = GaussianRasterizer(settings_for(v))(
+                means3D=pv["means"], means2D=means2D, opacities=leaves["opac"], shs=leaves["shs"],
+                scales=leaves["scales"], rotations=pv["rots"])
+            loss = (color * dL_dev[v]).sum()
+            loss.backward()
+            img_host[v].copy_(color.detach(), non_blocking=True)
+            total = loss.detach() if total is None else total + loss.detach()
+        loss_host.copy_(total.view(1), non_blocking=True)
+        reduce_grads()
+        torch.cuda.current_stream().synchronize()
+
+    def timed(step, steps):
+        for _ in range(2):
+            step()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = sharding.all_reduce_max(e0.elapsed_time(e1), dev)
+        if world > 1:
+            dist.barrier()
+        return round(world * vps * steps / (ms / 1e3), 2)
 
     steps = max(3, args.steps // 3)
-    for _ in range(2):
-        step()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        step()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = sharding.all_reduce_max(e0.elapsed_time(e1), dev)
-    if world > 1:
-        dist.barrier()
-    return {"value": round(world * vps * steps / (ms / 1e3), 2), "unit": "views/s",
-            "h2d_bytes_per_step": vps * (38 * 4 + 3 * H * W * 4), "d2h_bytes_per_step": vps * (3 * H * W * 4 + 4),
+    v_multi = timed(step_multi, steps)
+    v_single = timed(step_per_view, steps)
+    return {"value": v_multi, "unit": "views/s",
+            "h2d_bytes_per_step": vps * (38 * 4 + 3 * H * W * 4), "d2h_bytes_per_step": vps * (3 * H * W * 4) + 4,
             "steps": steps,
-            "what": "GaussianRasterizer.forward + autograd backward per view; per-view H2D (pinned) of camera bundle + "
-                    "dL/dcolour, D2H of rendered image + loss; Gaussian parameters resident (model state)"}
+            "what": "das3r_b200.multiview.MultiViewRasterizer (all views of the step in one autograd node: forwards and "
+                    "backward blends on CUDA streams, one fused gradient pass) + autograd; per view H2D (pinned) of the "
+                    "camera bundle and dL/dcolour and D2H of the rendered image, per step D2H of the loss; Gaussian "
+                    "parameters resident (model state)",
+            "per_view_api": {"value": v_single, "unit": "views/s",
+                             "what": "the drop-in GaussianRasterizer.forward + autograd backward called once per view, "
+                                     "single stream, same copies"}}
 
 
 def cpu_baseline(args, sc):

@@ -159,3 +159,48 @@ def test_gaussians_outside_every_view_get_zeros_or_stay_untouched():
     _fused(C, views, dLs, states, D, marked, accumulate=True)
     for o in marked:
         assert bool((o[hidden] == 3.0).all()), "accumulate mode wrote to a Gaussian no view rendered"
+
+
+@pytest.mark.parametrize("D", [3, 1])
+def test_multiview_rasterizer_matches_the_per_view_module(D):
+    """MultiViewRasterizer (one autograd node for all views, streams + fused gradient pass) against the drop-in
+    GaussianRasterizer called once per view: identical images and radii, gradients within tolerance."""
+    from das3r_b200.multiview import MultiViewRasterizer
+    from das3r_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+
+    dev = torch.device("cuda:0")
+    V, P, W, H = 4, 12_000, 144, 96
+    views, dLs = _scene_views(P, V, W, H, D, seed=31, dev=dev)
+
+    def leaves():
+        shared = [views[0][k].clone().requires_grad_(True) for k in ("opacities", "shs", "scales")]
+        per = [(vi["means3D"].clone().requires_grad_(True), vi["rotations"].clone().requires_grad_(True)) for vi in views]
+        return shared, per
+
+    settings = [GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=vi["tanfovx"], tanfovy=vi["tanfovy"], bg=vi["bg"], scale_modifier=1.0,
+        viewmatrix=vi["viewmatrix"], projmatrix=vi["projmatrix"], sh_degree=D, campos=vi["campos"], prefiltered=False,
+        debug=False) for vi in views]
+
+    (op_a, sh_a, sc_a), per_a = leaves()
+    want_colors = []
+    loss = 0
+    for rs, (m, r), dL in zip(settings, per_a, dLs):
+        m2d = torch.zeros(P, 3, device=dev, requires_grad=True)
+        color, radii = GaussianRasterizer(rs)(means3D=m, means2D=m2d, opacities=op_a, shs=sh_a, scales=sc_a, rotations=r)
+        want_colors.append(color.detach())
+        loss = loss + (color * dL).sum()
+    loss.backward()
+
+    (op_b, sh_b, sc_b), per_b = leaves()
+    colors, radii = MultiViewRasterizer(streams=3)(settings, [m for m, _ in per_b], [r for _, r in per_b], op_b, sh_b,
+                                                   sc_b)
+    sum((c * dL).sum() for c, dL in zip(colors, dLs)).backward()
+    torch.cuda.synchronize()
+    for c, w in zip(colors, want_colors):
+        assert float((c.detach() - w).abs().max()) == 0.0
+    for name, a, b in (("opacities", op_a, op_b), ("shs", sh_a, sh_b), ("scales", sc_a, sc_b)):
+        assert Hn.rel_err(b.grad, a.grad) <= Hn.GRAD_RTOL, name
+    for v, ((ma, ra), (mb, rb)) in enumerate(zip(per_a, per_b)):
+        assert Hn.rel_err(mb.grad, ma.grad) <= Hn.GRAD_RTOL, f"means3D of view {v}"
+        assert Hn.rel_err(rb.grad, ra.grad) <= Hn.GRAD_RTOL, f"rotations of view {v}"
