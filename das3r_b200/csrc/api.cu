@@ -313,13 +313,10 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
 
     if (R > 0) {
         STAGE(launch_scatter(P, gx, gy, rec, out->radii, tiles_touched, cursors, unsorted, stream), "scatter", ST_SCATTER, 1);
-        if (!fallback)
-            STAGE(launch_tile_sort(R, T, max_count, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, stream),
-                  "tile_sort", ST_TILE_SORT, 2 + (max_count > 4096 ? 1 : 0) + (max_count > 8192 ? 1 : 0));
-        else
-            STAGE(launch_tile_sort_fallback(R, T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted,
-                                            bin + X.b_fallback, X.fallback_bytes, stream),
-                  "tile_sort_fallback", ST_TILE_SORT, 3);
+        STAGE(launch_tile_sort(R, T, max_count, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted,
+                               fallback ? bin + X.b_fallback : nullptr, X.fallback_bytes, stream),
+              "tile_sort", ST_TILE_SORT,
+              2 + (max_count > 4096 ? 1 : 0) + (max_count > 8192 ? 1 : 0) + (fallback ? 3 : 0));
     }
     if (R > 0)
         STAGE(launch_rect_lists(T, gx, W, H, ranges, sA, sBC, rect_off, rect_cnt, rect_list, stream), "rect_lists",

@@ -472,20 +472,23 @@ __device__ __forceinline__ void bitonic_sort_tile(uint64_t* sm, const uint64_t* 
 // at exactly the same depth), the block falls back to the bitonic network over the whole tile.
 // MAXE bounds the per-thread key count of the instantiation (registers / shared memory); MIN_N..512*MAXE is the size
 // class this launch handles, blocks of other classes exit at once.
-constexpr int LOG_NB = 10;
-constexpr int NB = 1 << LOG_NB;
 constexpr int LEAF_MAX = 128;
+constexpr int MED_CAP = 2048;  // buckets with more than 8 keys: at most 16384 / 9 of them
 
-template <int MAXE, int MIN_N>
+template <int MAXE, int MIN_N, int LOG_NB>
 __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
     tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ unsorted,
                      const GaussRec* __restrict__ rec, uint32_t* __restrict__ point_list, float4* __restrict__ sA,
                      float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
+    constexpr int NB = 1 << LOG_NB;
+    constexpr int PER = NB / SORT_THREADS;  // bucket counters per thread in the scan
+    static_assert(NB % SORT_THREADS == 0 && PER >= 1, "bucket count must be a multiple of the block size");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* sm = reinterpret_cast<uint64_t*>(smem_raw);                                   // [512*MAXE] keys
     uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw + (size_t)SORT_THREADS * MAXE * 8);  // [NB] bucket sizes
     uint32_t* s_off = s_cnt + NB;                                                           // [NB] bucket starts
     uint32_t* s_cur = s_off + NB;                                                           // [NB] scatter cursors
+    uint16_t* s_med = reinterpret_cast<uint16_t*>(s_cur + NB);                              // [MED_CAP] buckets > 8 keys
     __shared__ uint32_t s_red[2][SORT_THREADS / 32];
     __shared__ uint32_t s_warp_tot[SORT_THREADS / 32];
     __shared__ uint32_t s_flags[2];
@@ -516,7 +519,10 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
         s_red[0][warp] = v_and;
         s_red[1][warp] = v_or;
     }
-    if (t == 0) s_flags[0] = 0;
+    if (t == 0) {
+        s_flags[0] = 0;
+        s_flags[1] = 0;
+    }
     __syncthreads();
     v_and = 0xffffffffu;
     v_or = 0u;
@@ -536,11 +542,22 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
         if (i < n) atomicAdd(&s_cnt[((uint32_t)(k[e] >> 32) >> shift) & (NB - 1)], 1u);
     }
     __syncthreads();
-    // exclusive scan of the NB counts (2 per thread) + largest bucket
+    // exclusive scan of the NB counts (PER consecutive ones per thread) + largest bucket + list of medium buckets
     {
-        const uint32_t c0 = s_cnt[2 * t], c1 = s_cnt[2 * t + 1];
-        if (max(c0, c1) > (uint32_t)LEAF_MAX) atomicOr(&s_flags[0], 1u);
-        uint32_t incl = c0 + c1;
+        uint32_t c[PER];
+        uint32_t sum = 0, cmax = 0;
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            c[j] = s_cnt[PER * t + j];
+            sum += c[j];
+            cmax = max(cmax, c[j]);
+            if (c[j] > 8u) {
+                const uint32_t slot = atomicAdd(&s_flags[1], 1u);
+                if (slot < (uint32_t)MED_CAP) s_med[slot] = (uint16_t)(PER * t + j);
+            }
+        }
+        if (cmax > (uint32_t)LEAF_MAX) atomicOr(&s_flags[0], 1u);
+        uint32_t incl = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
@@ -551,11 +568,13 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
         uint32_t wbase = 0;
 #pragma unroll
         for (int w = 0; w < SORT_THREADS / 32; w++) wbase += (w < warp) ? s_warp_tot[w] : 0u;
-        const uint32_t ex = wbase + incl - (c0 + c1);
-        s_off[2 * t] = ex;
-        s_off[2 * t + 1] = ex + c0;
-        s_cur[2 * t] = ex;
-        s_cur[2 * t + 1] = ex + c0;
+        uint32_t ex = wbase + incl - sum;
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            s_off[PER * t + j] = ex;
+            s_cur[PER * t + j] = ex;
+            ex += c[j];
+        }
     }
     __syncthreads();
 
@@ -579,10 +598,26 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
         }
         __syncthreads();
         // ---- 3. leaf: every bucket is put in order on the FULL key ----
-        // (a) small buckets (<= 8 keys): one thread each, keys in registers, fixed odd-even transposition network
+        // (a) small buckets (<= 8 keys): one thread each, keys in registers, fixed compare-exchange networks sized to
+        //     the bucket (2: one exchange, 3..4: the 5-exchange network, 5..8: odd-even transposition)
         for (int b = t; b < NB; b += SORT_THREADS) {
             const uint32_t s0 = s_off[b], m = s_cnt[b];
-            if (m > 1 && m <= 8) {
+            if (m == 2) {
+                const uint64_t x = sm[s0], y = sm[s0 + 1];
+                sm[s0] = min(x, y);
+                sm[s0 + 1] = max(x, y);
+            } else if (m > 2 && m <= 4) {
+                uint64_t v0 = sm[s0], v1 = sm[s0 + 1], v2 = sm[s0 + 2], v3 = (m == 4) ? sm[s0 + 3] : ~0ull;
+                cmpx(v0, v1, true);
+                cmpx(v2, v3, true);
+                cmpx(v0, v2, true);
+                cmpx(v1, v3, true);
+                cmpx(v1, v2, true);
+                sm[s0] = v0;
+                sm[s0 + 1] = v1;
+                sm[s0 + 2] = v2;
+                if (m == 4) sm[s0 + 3] = v3;
+            } else if (m > 4 && m <= 8) {
                 uint64_t v[8];
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = (j < (int)m) ? sm[s0 + j] : ~0ull;
@@ -601,7 +636,9 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
             }
         }
         // (b) medium buckets (9..128 keys): one warp each, rank sort (a key's final slot = number of smaller keys)
-        for (int b = warp; b < NB; b += SORT_THREADS / 32) {
+        const int n_med = (int)min(s_flags[1], (uint32_t)MED_CAP);
+        for (int q = warp; q < n_med; q += SORT_THREADS / 32) {
+            const int b = s_med[q];
             const uint32_t s0 = s_off[b], m = s_cnt[b];
             if (m > 8) {  // m <= LEAF_MAX is guaranteed by the flag test above
                 uint64_t mine[LEAF_MAX / 32];
@@ -650,17 +687,19 @@ __global__ void __launch_bounds__(256) gather_records_kernel(int R, const uint32
 
 int tile_sort_capacity() { return SORT_THREADS * SORT_MAX_E; }
 
-template <int MAXE, int MIN_N>
+template <int MAXE, int MIN_N, int LOG_NB>
 static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const uint64_t* unsorted, const GaussRec* rec,
                                             uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
                                             cudaStream_t s) {
-    const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t) + 3 * NB * sizeof(uint32_t);
-    if (smem > 48 * 1024) {
-        cudaError_t err =
-            cudaFuncSetAttribute(tile_sort_kernel<MAXE, MIN_N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t) + 3 * ((size_t)1 << LOG_NB) * sizeof(uint32_t) +
+                        MED_CAP * sizeof(uint16_t);
+    if (smem + 2048 > 48 * 1024) {  // + the kernel's static shared memory
+        cudaError_t err = cudaFuncSetAttribute(tile_sort_kernel<MAXE, MIN_N, LOG_NB>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
     }
-    tile_sort_kernel<MAXE, MIN_N><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sA, sBC, keys_sorted);
+    tile_sort_kernel<MAXE, MIN_N, LOG_NB><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sA, sBC,
+                                                                        keys_sorted);
     return cudaGetLastError();
 }
 
@@ -694,14 +733,19 @@ cudaError_t side_streams(cudaStream_t out[2]) {
 }
 }  // namespace
 
-cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
+static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint64_t* unsorted, uint32_t* point_list,
+                                        uint64_t* keys_sorted, void* temp, size_t temp_bytes, cudaStream_t s);
+
+cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, uint64_t* unsorted,
                              const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
-                             cudaStream_t s) {
-    if (max_count > (uint32_t)tile_sort_capacity()) return cudaErrorInvalidValue;
-    // Tiles are sorted by the cheapest variant that fits them (<= 4096, <= 8192, <= 16384 entries): every launch covers
-    // all tiles and a block whose tile belongs to another size class exits at once. The crowded classes (one block
-    // per SM, a few dozen tiles) run on auxiliary streams next to the common one instead of in front of it.
+                             void* temp, size_t temp_bytes, cudaStream_t s) {
+    // Tiles are sorted by the cheapest variant that fits them (<= 4096, <= 8192, <= 16384 entries in shared memory;
+    // beyond that a library segmented radix sort restricted to those tiles): every launch covers all tiles and a block
+    // whose tile belongs to another size class exits at once. The crowded classes (one block per SM, a few dozen
+    // tiles) run on auxiliary streams next to the common one instead of in front of it.
     const bool need16 = max_count > SORT_THREADS * 8, need32 = max_count > SORT_THREADS * 16;
+    const bool need_lib = max_count > (uint32_t)tile_sort_capacity();
+    if (need_lib && (temp == nullptr || temp_bytes < tile_sort_fallback_bytes(R, T))) return cudaErrorInvalidValue;
     cudaError_t e = cudaSuccess;
     cudaStream_t side[2] = {nullptr, nullptr};
     cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
@@ -713,17 +757,21 @@ cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* rang
             if (c == 1 && !need32) break;
             e = cudaStreamWaitEvent(side[c], fork, 0);
             if (e != cudaSuccess) break;
-            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8>(T, ranges, unsorted, rec, point_list, sA, sBC,
-                                                                         keys_sorted, side[c])
-                         : launch_tile_sort_variant<32, SORT_THREADS * 16>(T, ranges, unsorted, rec, point_list, sA, sBC,
-                                                                          keys_sorted, side[c]);
+            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8, 12>(T, ranges, unsorted, rec, point_list, sA, sBC,
+                                                                             keys_sorted, side[c])
+                         : launch_tile_sort_variant<32, SORT_THREADS * 16, 12>(T, ranges, unsorted, rec, point_list, sA,
+                                                                              sBC, keys_sorted, side[c]);
             if (e != cudaSuccess) break;
+            if (c == 1 && need_lib) {
+                e = sort_oversized_tiles(R, T, ranges, unsorted, point_list, keys_sorted, temp, temp_bytes, side[c]);
+                if (e != cudaSuccess) break;
+            }
             if ((e = cudaEventCreateWithFlags(&join[c], cudaEventDisableTiming)) != cudaSuccess) break;
             e = cudaEventRecord(join[c], side[c]);
         }
     }
     if (e == cudaSuccess)
-        e = launch_tile_sort_variant<8, 0>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+        e = launch_tile_sort_variant<8, 0, 10>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
     for (int c = 0; c < 2; c++)
         if (join[c]) {
             if (e == cudaSuccess) e = cudaStreamWaitEvent(s, join[c], 0);
@@ -735,33 +783,30 @@ cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* rang
     return cudaGetLastError();
 }
 
-// Fallback for tiles larger than the in-shared-memory capacity: library segmented radix sort of the
-// (depth|index) entries, segment = tile, then the same gather.
-__global__ void gather_sorted_kernel(int R, int T, const uint2* __restrict__ ranges,
-                                     const uint64_t* __restrict__ sorted_entries, const GaussRec* __restrict__ rec,
-                                     uint32_t* __restrict__ point_list, float4* __restrict__ sA,
-                                     float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
-    // one block per tile so the tile id is known without a search
-    const uint32_t tile = blockIdx.x;
+// Tiles beyond the shared-memory capacity: library segmented radix sort of their (depth|index) entries (segment =
+// tile; the other tiles are passed as empty segments), then the sorted entries become point_list / debug keys. The
+// record streams are written by the common gather afterwards.
+__global__ void oversized_to_list_kernel(int T, uint32_t capacity, const uint2* __restrict__ ranges,
+                                         const uint64_t* __restrict__ sorted_entries,
+                                         uint32_t* __restrict__ point_list, uint64_t* __restrict__ keys_sorted) {
+    const uint32_t tile = blockIdx.x;  // one block per tile so the tile id is known without a search
     const uint2 range = ranges[tile];
+    if (range.y - range.x <= capacity) return;
     for (uint32_t i = range.x + threadIdx.x; i < range.y; i += blockDim.x) {
-        uint64_t key = sorted_entries[i];
-        uint32_t g = (uint32_t)key;
-        point_list[i] = g;
-        const GaussRec r = rec[g];
-        sA[i] = r.A;
-        sBC[2 * (size_t)i] = r.B;
-        sBC[2 * (size_t)i + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
+        const uint64_t key = sorted_entries[i];
+        point_list[i] = (uint32_t)key;
         if (keys_sorted) keys_sorted[i] = ((uint64_t)tile << 32) | (key >> 32);
     }
 }
 
-__global__ void ranges_to_offsets_kernel(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ beg,
-                                         uint32_t* __restrict__ end) {
+__global__ void oversized_offsets_kernel(int T, uint32_t capacity, const uint2* __restrict__ ranges,
+                                         uint32_t* __restrict__ beg, uint32_t* __restrict__ end) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < T) {
-        beg[i] = ranges[i].x;
-        end[i] = ranges[i].y;
+        const uint2 r = ranges[i];
+        const bool big = r.y - r.x > capacity;
+        beg[i] = big ? r.x : 0u;
+        end[i] = big ? r.y : 0u;
     }
 }
 
@@ -826,9 +871,8 @@ size_t tile_sort_fallback_bytes(int R, int T) {
     return align_up((size_t)R * 8, 256) + 2 * align_up((size_t)T * 4, 256) + align_up(cub_bytes, 256);
 }
 
-cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
-                                      uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted, void* temp,
-                                      size_t temp_bytes, cudaStream_t s) {
+static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint64_t* unsorted, uint32_t* point_list,
+                                        uint64_t* keys_sorted, void* temp, size_t temp_bytes, cudaStream_t s) {
     char* p = static_cast<char*>(temp);
     uint64_t* sorted_entries = reinterpret_cast<uint64_t*>(p);
     p += align_up((size_t)R * 8, 256);
@@ -837,11 +881,12 @@ cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_
     uint32_t* end = reinterpret_cast<uint32_t*>(p);
     p += align_up((size_t)T * 4, 256);
     size_t cub_bytes = temp_bytes - (size_t)(p - static_cast<char*>(temp));
-    ranges_to_offsets_kernel<<<(T + 255) / 256, 256, 0, s>>>(T, ranges, beg, end);
+    const uint32_t cap = (uint32_t)tile_sort_capacity();
+    oversized_offsets_kernel<<<(T + 255) / 256, 256, 0, s>>>(T, cap, ranges, beg, end);
     cudaError_t e = cub::DeviceSegmentedRadixSort::SortKeys(p, cub_bytes, unsorted, sorted_entries, R, T, beg, end, 0,
                                                             64, s);
     if (e != cudaSuccess) return e;
-    gather_sorted_kernel<<<T, 256, 0, s>>>(R, T, ranges, sorted_entries, rec, point_list, sA, sBC, keys_sorted);
+    oversized_to_list_kernel<<<T, 256, 0, s>>>(T, cap, ranges, sorted_entries, point_list, keys_sorted);
     return cudaGetLastError();
 }
 

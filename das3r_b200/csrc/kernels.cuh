@@ -77,17 +77,13 @@ cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint3
                              cudaStream_t s);
 cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,
                            const uint32_t* tiles_touched, uint32_t* cursors, uint64_t* unsorted, cudaStream_t s);
-// Sorts every tile whose entry count is <= tile_sort_capacity(); returns cudaErrorInvalidValue if max_count is larger
-// (the caller then uses the segmented fallback).
+// Per-tile sort + tile-ordered record streams. Tiles with more than tile_sort_capacity() entries need `temp`
+// (tile_sort_fallback_bytes(R, T) bytes) for the library segmented sort that handles just them.
 int tile_sort_capacity();
-cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, const uint64_t* unsorted,
-                             const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
-                             cudaStream_t s);
-// Fallback for tiles beyond the shared-memory capacity: library segmented radix sort + gather.
 size_t tile_sort_fallback_bytes(int R, int T);
-cudaError_t launch_tile_sort_fallback(int R, int T, const uint2* ranges, uint64_t* unsorted, const GaussRec* rec,
-                                      uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted, void* temp,
-                                      size_t temp_bytes, cudaStream_t s);
+cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, uint64_t* unsorted,
+                             const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
+                             void* temp, size_t temp_bytes, cudaStream_t s);
 cudaError_t launch_rect_lists(int T, unsigned gx, int W, int H, const uint2* ranges, const float4* sA,
                               const float4* sBC, uint32_t* rect_off, uint32_t* rect_cnt, uint2* rect_list,
                               cudaStream_t s);
