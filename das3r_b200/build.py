@@ -25,7 +25,7 @@ LIB = os.path.join(HERE, "libdas3r_raster.so")
 EXT = os.path.join(HERE, "_C" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
 
 CU_SOURCES = ["forward.cu", "backward.cu", "knn.cu", "api.cu"]
-HEADERS = ["common.cuh", "kernels.cuh", os.path.join(ROOT, "include", "das3r_raster.h")]
+HEADERS = ["common.cuh", "kernels.cuh", os.path.join(ROOT, "include", "das3r_raster.h"), "blend_common.cuh"]
 
 
 def _mtime(p: str) -> float:

@@ -19,12 +19,13 @@ namespace das3r {
 // to the Gaussian's 48-byte accumulator with two 128-bit and one 32-bit no-return atomics (REDG.E.ADD.F32x4) instead of
 // the reference's nine scalar ones.
 struct BwdPair {
+    float4 col;  // {r, g, b, gaussian index}: fetched in prep so that apply starts without a shared-memory wait
     float2 d;
     float G, alpha, inv_1ma;
     bool skip;
 };
 
-__global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
+__global__ void __launch_bounds__(32 * BLEND_WARPS, DAS3R_BWD_MIN_BLOCKS) blend_bwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
     const uint2* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
     unsigned gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
@@ -62,7 +63,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
     if (wmax == 0) return;
 
-    walk_rect_list<true, BWD_K>(
+    walk_rect_list<true, BWD_K, BWD_NPAIR>(
         sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, wmax,
         [&]() { return last_contributor != 0u; },
         [&](const RingRec& r) {
@@ -78,6 +79,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
             // compared at 1e-3; the forward's T and alpha decisions are not touched by this)
             x.inv_1ma = __frcp_rn(1.f - x.alpha);
             x.skip = __float_as_uint(A.z) >= last_contributor || x.alpha < 1.0f / 255.0f;
+            x.col = r.C;
             return x;
         },
         [&](const RingRec& r, const BwdPair& x) {
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, 16) blend_bwd_kernel(
             const float4 con_o = r.B;
             const float2 d = x.d;
             const float G = x.G, alpha = x.alpha, inv_1ma = x.inv_1ma;
-            const float4 col4 = r.C;
+            const float4 col4 = x.col;
             const float col[3] = {col4.x, col4.y, col4.z};
             T = T * inv_1ma;
             const float dchannel_dcolor = alpha * T;

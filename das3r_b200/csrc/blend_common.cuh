@@ -34,14 +34,29 @@ constexpr int CHUNK = 32;        // list entries gathered per round (one per lan
 #ifndef DAS3R_BWD_K
 #define DAS3R_BWD_K 4
 #endif
+#ifndef DAS3R_FWD_NPAIR
+#define DAS3R_FWD_NPAIR 3
+#endif
+#ifndef DAS3R_BWD_NPAIR
+#define DAS3R_BWD_NPAIR 2
+#endif
+#ifndef DAS3R_LIST_AHEAD
+#define DAS3R_LIST_AHEAD 0
+#endif
 #ifndef DAS3R_BLEND_INFLIGHT
-#define DAS3R_BLEND_INFLIGHT 2
+#define DAS3R_BLEND_INFLIGHT 1
+#endif
+#ifndef DAS3R_BWD_MIN_BLOCKS
+#define DAS3R_BWD_MIN_BLOCKS 16
 #endif
 #ifndef DAS3R_BLEND_BURST
-#define DAS3R_BLEND_BURST 8
+#define DAS3R_BLEND_BURST 3
 #endif
 constexpr int FWD_K = DAS3R_FWD_K;  // ring depth (chunks) of the forward / backward blend
 constexpr int BWD_K = DAS3R_BWD_K;
+constexpr int FWD_NPAIR = DAS3R_FWD_NPAIR;  // records prepared side by side per blend round
+constexpr int BWD_NPAIR = DAS3R_BWD_NPAIR;
+constexpr int LIST_AHEAD = DAS3R_LIST_AHEAD;  // chunks of list entries fetched ahead of the record gather
 constexpr int BLEND_INFLIGHT = DAS3R_BLEND_INFLIGHT;  // chunks whose record copies may be in flight (1..3)
 static_assert(BLEND_INFLIGHT >= 1 && BLEND_INFLIGHT <= 3, "wait_group immediates below cover 1..3");
 constexpr int BLEND_BURST = DAS3R_BLEND_BURST;  // blend rounds between two checks of the gather side
@@ -116,7 +131,24 @@ __device__ __forceinline__ uint32_t transpose_bits(uint32_t x, int lane) {
 // Chunks are numbered in walk order; `iss` chunks have been started, `vis` of them have landed (records readable, masks
 // stored), up to BLEND_INFLIGHT are in flight. A lane holds the unblended rest `m` of its mask of chunk nx-1. Chunk c lives in
 // ring slot c % K, so chunk `iss` may be started as soon as no lane needs chunk iss-K any more.
-template <bool REVERSE, int K, typename Keep, typename Prep, typename Apply>
+#ifdef DAS3R_BLEND_TIMING  // developer instrumentation: cycles per phase of the walk, per warp
+__device__ unsigned long long g_walk_prof[8 * 65536];
+#define WALK_PROF_DECL long long wp_t = clock64(); unsigned long long wp[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long wq_t = 0; unsigned long long wq[6] = {0, 0, 0, 0, 0, 0};
+#define WALK_Q0 wq_t = clock64();
+#define WALK_Q(i) { const long long wq_n = clock64(); wq[i] += (unsigned long long)(wq_n - wq_t); wq_t = wq_n; }
+#define WALK_PROF(i) { const long long wp_n = clock64(); wp[i] += (unsigned long long)(wp_n - wp_t); if ((i) >= 2) wp[(i) + 4]++; wp_t = wp_n; }
+#define WALK_COUNT_ROUND { wp[4]++; wp[5] += __popc(__ballot_sync(0xffffffffu, m != 0)); }
+#define WALK_PROF_STORE if (lane == 0) { unsigned long long* o = g_walk_prof + 8 * (size_t)(blockIdx.x * BLEND_WARPS + (threadIdx.x >> 5)); for (int q = 0; q < 8; q++) o[q] = wp[q]; unsigned long long* o2 = g_walk_prof + 8 * (size_t)32768 + 8 * (size_t)(blockIdx.x * BLEND_WARPS + (threadIdx.x >> 5)); for (int q = 0; q < 6; q++) o2[q] = wq[q]; }
+#else
+#define WALK_PROF_DECL
+#define WALK_PROF(i)
+#define WALK_Q0
+#define WALK_Q(i)
+#define WALK_COUNT_ROUND
+#define WALK_PROF_STORE
+#endif
+
+template <bool REVERSE, int K, int NPAIR, typename Keep, typename Prep, typename Apply>
 __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint32_t* __restrict__ qmask,
                                                const uint2* __restrict__ list, int cnt,
                                                const float4* __restrict__ gA, const float4* __restrict__ gBC,
@@ -134,8 +166,10 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
     };
     int lc = REVERSE ? nchunks - 1 : 0;  // list chunk to start next
     int left = nchunks;                  // list chunks not started yet
-    uint2 e_cur = load_entry(lc);
-    uint2 e_nxt = load_entry(lc + step);
+    // list entries are fetched LIST_AHEAD chunks before they are needed: a chunk start must never wait for them
+    uint2 e_q[LIST_AHEAD + 1];
+#pragma unroll
+    for (int j = 0; j <= LIST_AHEAD; j++) e_q[j] = load_entry(lc + j * step);
 
     uint32_t m = 0;
     int nx = 0, vis = 0, iss = 0;
@@ -147,6 +181,7 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
         pend_pos[f] = 0xffffffffu;
     }
 
+    WALK_PROF_DECL
     for (;;) {
         if (!keep()) {
             m = 0;
@@ -159,9 +194,12 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
         const bool idle = (m == 0);  // nothing landed is left for this lane
         if (__all_sync(0xffffffffu, !keep())) break;
         const int oldest = __reduce_min_sync(0xffffffffu, idle ? vis : nx - 1);  // lowest chunk still needed
-        const int nfly = iss - vis;
-        if (left > 0 && nfly < BLEND_INFLIGHT && iss - oldest < K) {
-            // start the next list chunk that somebody needs
+        int nfly = iss - vis;
+        bool acted = false;
+        WALK_PROF(0)
+        // start list chunks while the window and the pipeline have room (chunks nobody needs are skipped)
+        while (left > 0 && nfly < BLEND_INFLIGHT && iss - oldest < K) {
+            const uint2 e_cur = e_q[0];
             const bool valid = e_cur.x < pos_limit;
             if (__any_sync(0xffffffffu, valid)) {
                 RingRec& r = ring[(iss & (K - 1)) * 32 + lane];
@@ -179,13 +217,16 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
                         pend_pos[f] = valid ? e_cur.x : 0xffffffffu;
                     }
                 iss++;
+                nfly++;
             }
             lc += step;
             left--;
-            e_cur = e_nxt;
-            e_nxt = load_entry(lc + step);
-            continue;
+#pragma unroll
+            for (int j = 0; j < LIST_AHEAD; j++) e_q[j] = e_q[j + 1];
+            e_q[LIST_AHEAD] = load_entry(lc + LIST_AHEAD * step);
+            acted = true;
         }
+        WALK_PROF(1)
         if (nfly > 0 && (oldest == vis || nfly == BLEND_INFLIGHT || left == 0)) {
             // land the oldest chunk in flight: the pipeline is full, or everybody is out of work, or nothing is left
             // to start
@@ -202,9 +243,10 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
             }
             __syncwarp();
             vis++;
-            continue;
+            acted = true;
+            WALK_PROF(2)
         }
-        if (oldest == vis) break;  // nothing landed, nothing in flight, nothing left to start
+        if (!acted && oldest == vis) break;  // nothing landed, nothing in flight, nothing left to start
         // blend: a few rounds between two looks at the gather side; lanes step to their next landed chunk on their own
 #pragma unroll 1
         for (int round = 0; round < BLEND_BURST; round++) {
@@ -212,27 +254,44 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
                 m = qmask[(nx & (K - 1)) * 32 + lane];
                 nx++;
             }
+            WALK_COUNT_ROUND
+            WALK_Q0
             if (m) {
+                // up to NPAIR records per round: their order-independent parts are evaluated side by side (a missing
+                // one repeats the first record and is not applied)
                 const RingRec* base = ring + ((nx - 1) & (K - 1)) * 32;
-                const int bit0 = __ffs(m) - 1;
-                m &= m - 1;
-                const bool two = (m != 0);
-                const int bit1 = two ? __ffs(m) - 1 : bit0;
-                m &= m - 1;
-                const RingRec& r0 = base[bit0];
-                const RingRec& r1 = base[bit1];
-                const auto x0 = prep(r0);
-                const auto x1 = prep(r1);
-                apply(r0, x0);
-                if (two && keep()) apply(r1, x1);
+                const RingRec* r[NPAIR];
+                bool have[NPAIR];
+#pragma unroll
+                for (int j = 0; j < NPAIR; j++) {
+                    have[j] = (m != 0);
+                    const int bit = have[j] ? __ffs(m) - 1 : 0;
+                    r[j] = have[j] ? base + bit : r[0];
+                    m &= m - 1;
+                }
+                WALK_Q(0)
+                decltype(prep(*r[0])) x[NPAIR];
+#pragma unroll
+                for (int j = 0; j < NPAIR; j++) x[j] = prep(*r[j]);
+                WALK_Q(1)
+                apply(*r[0], x[0]);
+                WALK_Q(2)
+#pragma unroll
+                for (int j = 1; j < NPAIR; j++)
+                    if (have[j] && keep()) apply(*r[j], x[j]);
+                WALK_Q(3)
                 if (!keep()) {
                     m = 0;
                     nx = vis;
                 }
             }
+            WALK_Q(4)
             if (!__any_sync(0xffffffffu, m != 0 || nx < vis)) break;  // nothing landed is left for anybody
+            WALK_Q(5)
         }
+        WALK_PROF(3)
     }
+    WALK_PROF_STORE
     cp_async_wait_all();  // never leave with a copy into this block's shared memory in flight
 }
 

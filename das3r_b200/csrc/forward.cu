@@ -997,12 +997,21 @@ __device__ unsigned long long g_blend_dbg[4 * 65536];
 extern "C" int das3r_debug_blend_timing(unsigned long long* host_out, int n_words) {
     return (int)cudaMemcpyFromSymbol(host_out, g_blend_dbg, sizeof(unsigned long long) * n_words);
 }
+extern "C" int das3r_debug_walk_prof(unsigned long long* host_out, int n_words) {
+    return (int)cudaMemcpyFromSymbol(host_out, g_walk_prof, sizeof(unsigned long long) * n_words);
+}
 __device__ __forceinline__ unsigned long long dbg_globaltimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
 #endif
+
+struct FwdPair {
+    float4 col;  // {r, g, b, depth (EXTRAS only)}
+    float alpha;
+    uint32_t pos1;  // tile-list position + 1
+};
 
 template <bool EXTRAS>
 __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
@@ -1029,34 +1038,42 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     float C[3] = {0.f, 0.f, 0.f};
     float Dz = 0.f;
 
-    walk_rect_list<false, FWD_K>(
+    walk_rect_list<false, FWD_K, FWD_NPAIR>(
         sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, 0xffffffffu,
         [&]() { return !done; },
         [&](const RingRec& r) {
+            FwdPair x;
             const float4 A = r.A;
             const float4 con_o = r.B;
+            x.col = r.C;  // fetched with the rest: apply() then has no shared-memory latency in the pixel's chain
+            if (EXTRAS) x.col.w = rec_by_id[__float_as_uint(x.col.w)].C.w;  // the record carries the index, not the depth
+            x.pos1 = __float_as_uint(A.z) + 1u;
             const float power = splat_power(con_o, make_float2(A.x - pixf.x, A.y - pixf.y));
             // forward.cu:339-340 (power <= 0 is guaranteed by the pixel mask)
-            return min(0.99f, __fmul_rn(con_o.w, expf(power)));
+            x.alpha = min(0.99f, __fmul_rn(con_o.w, expf(power)));
+            return x;
         },
-        [&](const RingRec& r, const float alpha) {
-            // forward.cu:341-361
-            if (alpha < 1.0f / 255.0f) return;
+        [&](const RingRec&, const FwdPair& x) {
+            // forward.cu:341-361, written with selects instead of early returns (no divergent branches in the chain)
+            const float alpha = x.alpha;
             const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-            if (test_T < 0.0001f) {
-                done = true;
-                return;
-            }
-            const float4 col = r.C;
-            C[0] = __fmaf_rn(T, __fmul_rn(col.x, alpha), C[0]);
-            C[1] = __fmaf_rn(T, __fmul_rn(col.y, alpha), C[1]);
-            C[2] = __fmaf_rn(T, __fmul_rn(col.z, alpha), C[2]);
+            const bool counts = !done && !(alpha < 1.0f / 255.0f);
+            const bool stop = counts && (test_T < 0.0001f);
+            const bool blend = counts && !stop;
+            const float w = blend ? T : 0.f;  // C += T * (c * alpha) only where the pair contributes
+            const float c0 = __fmaf_rn(w, __fmul_rn(x.col.x, alpha), C[0]);
+            const float c1 = __fmaf_rn(w, __fmul_rn(x.col.y, alpha), C[1]);
+            const float c2 = __fmaf_rn(w, __fmul_rn(x.col.z, alpha), C[2]);
+            C[0] = blend ? c0 : C[0];
+            C[1] = blend ? c1 : C[1];
+            C[2] = blend ? c2 : C[2];
             if (EXTRAS) {
-                const float z = rec_by_id[__float_as_uint(col.w)].C.w;
-                Dz = __fmaf_rn(T, __fmul_rn(z, alpha), Dz);
+                const float dz = __fmaf_rn(w, __fmul_rn(x.col.w, alpha), Dz);
+                Dz = blend ? dz : Dz;
             }
-            T = test_T;
-            last_contributor = __float_as_uint(r.A.z) + 1u;
+            T = blend ? test_T : T;
+            last_contributor = blend ? x.pos1 : last_contributor;
+            done = done || stop;
         });
 
 #ifdef DAS3R_BLEND_TIMING
@@ -1099,8 +1116,14 @@ cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, cons
                                                                      rec_by_id, W, H, gx, bg, final_T, n_contrib,
                                                                      out_color, out_depth, out_alpha);
     } else {
-        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS,
-                                           sizeof(BlendSmem<FWD_K>));
+        size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS,
+                                     sizeof(BlendSmem<FWD_K>));
+#ifdef DAS3R_BLEND_TIMING  // occupancy experiments
+        if (const char* ex = getenv("DAS3R_BLEND_EXTRA_SMEM")) {
+            pad = (size_t)atoi(ex);
+            cudaFuncSetAttribute(blend_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
+        }
+#endif
         blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
                                                                       rec_by_id, W, H, gx, bg, final_T, n_contrib,
                                                                       out_color, out_depth, out_alpha);

@@ -41,3 +41,19 @@ print("fit cycles = %.0f + %.1f * cnt" % (coef[0], coef[1]))
 # per-SM finish times
 fin = np.array([t1[smid == s].max() - base for s in np.unique(smid)])
 print("per-SM finish ns: min", fin.min(), "mean", fin.mean(), "max", fin.max())
+
+wpall = np.zeros(8 * 65536, np.uint64)
+if hasattr(lib, "das3r_debug_walk_prof") and lib.das3r_debug_walk_prof(wpall.ctypes.data_as(ctypes.c_void_p), 8 * 65536) == 0:
+    wp = wpall[:8 * nw].reshape(nw, 8).astype(np.int64)
+    wq = wpall[8 * 32768:8 * 32768 + 8 * nw].reshape(nw, 8).astype(np.int64)
+    names = ["bookkeeping", "start", "land", "blend burst"]
+    for label, sel in (("all warps", slice(None)), ("12 slowest", order[:12])):
+        tot = wp[sel, :4].sum(0)
+        rounds, lanes, lands, bursts = wp[sel, 4].sum(), wp[sel, 5].sum(), wp[sel, 6].sum(), wp[sel, 7].sum()
+        ent = cnt[sel].sum()
+        print(label, "cycle share by phase:", dict(zip(names, np.round(tot / tot.sum(), 3))))
+        print(label, "rounds per chunk %.2f, active lanes per round %.1f, cycles per round %.0f, bursts per chunk %.2f, lands per chunk %.2f"
+              % (rounds / (ent / 32), lanes / max(rounds, 1), tot[3] / max(rounds, 1), bursts / (ent / 32), lands / (ent / 32)))
+        q = wq[sel, :6].sum(0)
+        print(label, "cycles per round inside the burst: pop+addr %.0f, prep %.0f, apply0 %.0f, apply1 %.0f, keep %.0f, vote %.0f"
+              % tuple(q / max(rounds, 1)))
