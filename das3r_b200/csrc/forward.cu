@@ -896,7 +896,10 @@ static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint6
 // by ballot compaction in a single pass (four chunks of 32 entries in flight per round); rectangle w of a tile with n
 // entries owns the n slots starting at 8*range.x + w*n of the output array, so no counting pass or atomics are needed.
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) rect_lists_kernel(const uint2* __restrict__ ranges,
+#ifndef DAS3R_RECT_MIN_BLOCKS
+#define DAS3R_RECT_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(const uint2* __restrict__ ranges,
                                                          const float4* __restrict__ sA, const float4* __restrict__ sBC,
                                                          unsigned gx, int W, int H, uint32_t* __restrict__ rect_off,
                                                          uint32_t* __restrict__ rect_cnt,
