@@ -2,6 +2,7 @@
 // state blobs, stage sequencing, error reporting. Replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
 // (reference cuda_rasterizer/rasterizer_impl.cu:141-434) and SimpleKNN::knn (simple-knn/simple_knn.cu:186-222).
 #include "../../include/das3r_raster.h"
+#include "../../include/das3r_frontend.h"
 #include "kernels.cuh"
 #include <stdio.h>
 #include <stdlib.h>
@@ -589,6 +590,83 @@ int das3r_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scr
     g_launches += 7;  // init, bbox, morton, (library sort), gather, boxes, search
     cudaError_t e = knn_dist2(P, points, mean_dist2, scratch, scratch_bytes, static_cast<cudaStream_t>(stream_v));
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "knn", e);
+    return DAS3R_OK;
+}
+
+
+// ---- fused DAS3R render front-end (include/das3r_frontend.h) ------------------------------------------------------
+static bool frontend_model_ok(const das3r_frontend_model* m) {
+    return m && m->P >= 0 &&
+           (m->P == 0 || (m->xyz && m->rotation && m->opacity && m->scaling && m->features_dc && m->features_rest &&
+                          m->conf_static && ((reinterpret_cast<uintptr_t>(m->rotation) & 15) == 0)));
+}
+
+int das3r_frontend_forward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                           const das3r_frontend_outputs* out, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!frontend_model_ok(model) || !out || n_views < 1 || n_views > DAS3R_FRONTEND_MAX_VIEWS || !poses)
+        return fail_msg(DAS3R_EINVAL, "frontend_forward: null or invalid argument (1..16 views, rotation 16-byte aligned)");
+    if (model->P == 0) return DAS3R_OK;
+    if (!out->opacity || !out->scales || !out->shs) return fail_msg(DAS3R_EINVAL, "frontend_forward: null output");
+    FrontendFwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.P = model->P; a.n_views = n_views;
+    a.xyz = model->xyz; a.rotation = model->rotation; a.opacity_raw = model->opacity; a.scaling_raw = model->scaling;
+    a.features_dc = model->features_dc; a.features_rest = model->features_rest; a.conf_static = model->conf_static;
+    a.conf_index = model->conf_index; a.poses = poses;
+    a.opacity = out->opacity; a.scales = out->scales; a.shs = out->shs;
+    for (int v = 0; v < n_views; v++) {
+        if (!out->means3D[v] || !out->rotations[v] || (reinterpret_cast<uintptr_t>(out->rotations[v]) & 15))
+            return fail_msg(DAS3R_EINVAL, "frontend_forward: null or misaligned per-view output");
+        a.means3D[v] = out->means3D[v];
+        a.rotations[v] = out->rotations[v];
+    }
+    cudaError_t e = launch_frontend_fwd(a, stream);
+    g_launches += 1;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_fwd", e);
+    return DAS3R_OK;
+}
+
+size_t das3r_frontend_backward_scratch_bytes(int32_t P, int32_t n_views) {
+    return frontend_backward_scratch_bytes(P > 0 ? P : 0, n_views > 0 ? n_views : 0);
+}
+
+int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                            const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!frontend_model_ok(model) || !gin || !gout || n_views < 1 || n_views > DAS3R_FRONTEND_MAX_VIEWS || !poses)
+        return fail_msg(DAS3R_EINVAL, "frontend_backward: null or invalid argument (1..16 views)");
+    if (!gout->dL_dposes) return fail_msg(DAS3R_EINVAL, "frontend_backward: dL_dposes is null");
+    if (model->P == 0) {
+        cudaError_t e = cudaMemsetAsync(gout->dL_dposes, 0, sizeof(float) * 7 * n_views, stream);
+        if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_backward memset", e);
+        return DAS3R_OK;
+    }
+    if (!gin->dL_dopacity || !gin->dL_dscales || !gin->dL_dshs || !gout->dL_dxyz || !gout->dL_drotation ||
+        !gout->dL_dopacity || !gout->dL_dscaling || !gout->dL_dfeatures_dc || !gout->dL_dfeatures_rest ||
+        !gout->dL_dconf || !gout->scratch || (reinterpret_cast<uintptr_t>(gout->dL_drotation) & 15))
+        return fail_msg(DAS3R_EINVAL, "frontend_backward: null or misaligned buffer");
+    FrontendBwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.P = model->P; a.n_views = n_views;
+    a.xyz = model->xyz; a.rotation = model->rotation; a.opacity_raw = model->opacity; a.scaling_raw = model->scaling;
+    a.conf_static = model->conf_static; a.conf_index = model->conf_index; a.poses = poses;
+    a.dL_dopacity = gin->dL_dopacity; a.dL_dscales = gin->dL_dscales; a.dL_dshs = gin->dL_dshs;
+    for (int v = 0; v < n_views; v++) {
+        if (!gin->dL_dmeans3D[v] || !gin->dL_drotations[v] || (reinterpret_cast<uintptr_t>(gin->dL_drotations[v]) & 15))
+            return fail_msg(DAS3R_EINVAL, "frontend_backward: null or misaligned per-view gradient");
+        a.dL_dmeans3D[v] = gin->dL_dmeans3D[v];
+        a.dL_drotations[v] = gin->dL_drotations[v];
+    }
+    a.dL_dxyz = gout->dL_dxyz; a.dL_drotation = gout->dL_drotation; a.dL_dopacity_raw = gout->dL_dopacity;
+    a.dL_dscaling_raw = gout->dL_dscaling; a.dL_dfeatures_dc = gout->dL_dfeatures_dc;
+    a.dL_dfeatures_rest = gout->dL_dfeatures_rest; a.dL_dconf = gout->dL_dconf;
+    a.partials = gout->scratch;
+    cudaError_t e = launch_frontend_bwd(a, gout->dL_dposes, stream);
+    g_launches += 2;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_bwd", e);
     return DAS3R_OK;
 }
 

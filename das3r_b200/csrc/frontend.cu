@@ -1,0 +1,250 @@
+// Fused DAS3R render front-end for sm_100a (see include/das3r_frontend.h): pose transform of means and rotations for
+// all views of a step, opacity / scale activations, SH concatenation - and the backward, which reduces the per-view
+// mean / rotation gradients to parameter gradients and pose gradients in one pass over the Gaussians.
+// Reference: gaussian_renderer/__init__.py:83-108,:126; utils/pose_utils.py:10-104; scene/gaussian_model.py:103-113,
+// :186-194. HBM-bound: every array is read or written once, the per-view arrays once per view.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace das3r {
+
+constexpr int FE_THREADS = 256;
+constexpr int FE_POSE_F = 16;  // per view in shared memory: R (9, row-major), raw quaternion (4), translation (3)
+constexpr int FE_PART_F = 16;  // per view and block: sum g (3), sum g x^T (9, row-major), quaternion-product part (4)
+
+// Pose (r,x,y,z,tx,ty,tz) -> rotation matrix of the NORMALISED quaternion (utils/pose_utils.py:36-55), raw quaternion,
+// translation.
+__device__ __forceinline__ void pose_to_smem(const float* __restrict__ pose, float* __restrict__ o) {
+    const float q0 = pose[0], q1 = pose[1], q2 = pose[2], q3 = pose[3];
+    const float norm = sqrtf(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);
+    const float r = q0 / norm, x = q1 / norm, y = q2 / norm, z = q3 / norm;
+    o[0] = 1 - 2 * (y * y + z * z);
+    o[1] = 2 * (x * y - r * z);
+    o[2] = 2 * (x * z + r * y);
+    o[3] = 2 * (x * y + r * z);
+    o[4] = 1 - 2 * (x * x + z * z);
+    o[5] = 2 * (y * z - r * x);
+    o[6] = 2 * (x * z - r * y);
+    o[7] = 2 * (y * z + r * x);
+    o[8] = 1 - 2 * (x * x + y * y);
+    o[9] = q0; o[10] = q1; o[11] = q2; o[12] = q3;
+    o[13] = pose[4]; o[14] = pose[5]; o[15] = pose[6];
+}
+
+// Block-cooperative copy between the split SH layout (dc [P,1,3], rest [P,15,3]) and the joint one ([P,16,3]): flat,
+// coalesced on the split side. TO_JOINT: dc/rest -> shs; else shs -> dc/rest.
+template <bool TO_JOINT, typename TD, typename TR, typename TS>
+__device__ __forceinline__ void sh_rows_copy(TD* dc, TR* rest, TS* shs, int base, int nvalid) {
+    const int tid = threadIdx.x;
+    for (int e = tid; e < nvalid * 3; e += FE_THREADS) {
+        const int g = e / 3, j = e - 3 * g;
+        if constexpr (TO_JOINT) shs[(size_t)(base + g) * 48 + j] = dc[(size_t)base * 3 + e];
+        else dc[(size_t)base * 3 + e] = shs[(size_t)(base + g) * 48 + j];
+    }
+    for (int e = tid; e < nvalid * 45; e += FE_THREADS) {
+        const int g = e / 45, j = e - 45 * g;
+        if constexpr (TO_JOINT) shs[(size_t)(base + g) * 48 + 3 + j] = rest[(size_t)base * 45 + e];
+        else rest[(size_t)base * 45 + e] = shs[(size_t)(base + g) * 48 + 3 + j];
+    }
+}
+
+__global__ void __launch_bounds__(FE_THREADS) frontend_fwd_kernel(const __grid_constant__ FrontendFwdArgs a) {
+    __shared__ float s_pose[FE_MAX_VIEWS * FE_POSE_F];
+    const int tid = threadIdx.x;
+    const int base = blockIdx.x * FE_THREADS;
+    const int idx = base + tid;
+    const int nvalid = min(FE_THREADS, a.P - base);
+    if (tid < a.n_views) pose_to_smem(a.poses + 7 * tid, s_pose + FE_POSE_F * tid);
+    sh_rows_copy<true>(a.features_dc, a.features_rest, a.shs, base, nvalid);
+    __syncthreads();
+    if (idx >= a.P) return;
+
+    // activations (scene/gaussian_model.py:103-105,:193-194; gaussian_renderer/__init__.py:95-97)
+    const float o = a.opacity_raw[idx];
+    const float conf = a.conf_static[a.conf_index ? a.conf_index[idx] : (int64_t)idx];
+    a.opacity[idx] = (1.0f / (1.0f + expf(-o))) * conf;
+#pragma unroll
+    for (int k = 0; k < 3; k++) a.scales[3 * idx + k] = expf(a.scaling_raw[3 * idx + k]);
+
+    const float X = a.xyz[3 * idx], Y = a.xyz[3 * idx + 1], Z = a.xyz[3 * idx + 2];
+    const float4 rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + idx);  // (w2, x2, y2, z2)
+#pragma unroll 1
+    for (int v = 0; v < a.n_views; v++) {
+        const float* p = s_pose + FE_POSE_F * v;
+        // gaussian_renderer/__init__.py:87-89: rows of [R | t] times (X, Y, Z, 1)
+        float* m = a.means3D[v] + 3 * (size_t)idx;
+        m[0] = p[0] * X + p[1] * Y + p[2] * Z + p[13];
+        m[1] = p[3] * X + p[4] * Y + p[5] * Z + p[14];
+        m[2] = p[6] * X + p[7] * Y + p[8] * Z + p[15];
+        // utils/pose_utils.py:94-101 with q1 = raw pose quaternion, q2 = Gaussian rotation
+        const float w1 = p[9], x1 = p[10], y1 = p[11], z1 = p[12];
+        float4 r;
+        r.x = w1 * rq.x - x1 * rq.y - y1 * rq.z - z1 * rq.w;
+        r.y = w1 * rq.y + x1 * rq.x + y1 * rq.w - z1 * rq.z;
+        r.z = w1 * rq.z - x1 * rq.w + y1 * rq.x + z1 * rq.y;
+        r.w = w1 * rq.w + x1 * rq.z - y1 * rq.y + z1 * rq.x;
+        reinterpret_cast<float4*>(a.rotations[v])[idx] = r;
+    }
+}
+
+cudaError_t launch_frontend_fwd(const FrontendFwdArgs& a, cudaStream_t s) {
+    const int blocks = (a.P + FE_THREADS - 1) / FE_THREADS;
+    frontend_fwd_kernel<<<blocks, FE_THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+// Sum of `v` over the block, result valid in thread 0. `red` holds one float per warp.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float t = 0.f;
+    if (threadIdx.x == 0)
+#pragma unroll
+        for (int w = 0; w < FE_THREADS / 32; w++) t += red[w];
+    __syncthreads();
+    return t;
+}
+
+__global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_constant__ FrontendBwdArgs a) {
+    __shared__ float s_pose[FE_MAX_VIEWS * FE_POSE_F];
+    __shared__ float s_part[FE_MAX_VIEWS * FE_PART_F];           // this block's partial sums
+    __shared__ float s_warp[FE_THREADS / 32][FE_PART_F];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int base = blockIdx.x * FE_THREADS;
+    const int idx = base + tid;
+    const int nvalid = min(FE_THREADS, a.P - base);
+    const bool in_range = idx < a.P;
+    if (tid < a.n_views) pose_to_smem(a.poses + 7 * tid, s_pose + FE_POSE_F * tid);
+    sh_rows_copy<false>(a.dL_dfeatures_dc, a.dL_dfeatures_rest, a.dL_dshs, base, nvalid);
+    __syncthreads();
+
+    float X = 0.f, Y = 0.f, Z = 0.f;
+    float4 rq = {0.f, 0.f, 0.f, 0.f};
+    if (in_range) {
+        // activation derivatives
+        const float o = a.opacity_raw[idx];
+        const float sg = 1.0f / (1.0f + expf(-o));
+        const float conf = a.conf_static[a.conf_index ? a.conf_index[idx] : (int64_t)idx];
+        const float go = a.dL_dopacity[idx];
+        a.dL_dopacity_raw[idx] = go * conf * sg * (1.0f - sg);
+        a.dL_dconf[idx] = go * sg;
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+            a.dL_dscaling_raw[3 * idx + k] = a.dL_dscales[3 * idx + k] * expf(a.scaling_raw[3 * idx + k]);
+        X = a.xyz[3 * idx]; Y = a.xyz[3 * idx + 1]; Z = a.xyz[3 * idx + 2];
+        rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + idx);
+    }
+
+    float dX = 0.f, dY = 0.f, dZ = 0.f;
+    float4 dr = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+    for (int v = 0; v < a.n_views; v++) {
+        const float* p = s_pose + FE_POSE_F * v;
+        float part[FE_PART_F];
+#pragma unroll
+        for (int k = 0; k < FE_PART_F; k++) part[k] = 0.f;
+        if (in_range) {
+            const float* gm = a.dL_dmeans3D[v] + 3 * (size_t)idx;
+            const float g0 = gm[0], g1 = gm[1], g2 = gm[2];
+            const float4 d = __ldg(reinterpret_cast<const float4*>(a.dL_drotations[v]) + idx);
+            // means = R X + t
+            dX += p[0] * g0 + p[3] * g1 + p[6] * g2;
+            dY += p[1] * g0 + p[4] * g1 + p[7] * g2;
+            dZ += p[2] * g0 + p[5] * g1 + p[8] * g2;
+            part[0] = g0; part[1] = g1; part[2] = g2;
+            part[3] = g0 * X; part[4] = g0 * Y; part[5] = g0 * Z;
+            part[6] = g1 * X; part[7] = g1 * Y; part[8] = g1 * Z;
+            part[9] = g2 * X; part[10] = g2 * Y; part[11] = g2 * Z;
+            // rotations = q1 (x) q2: gradient w.r.t. q2 (the Gaussian) ...
+            const float w1 = p[9], x1 = p[10], y1 = p[11], z1 = p[12];
+            dr.x += d.x * w1 + d.y * x1 + d.z * y1 + d.w * z1;
+            dr.y += -d.x * x1 + d.y * w1 + d.z * z1 - d.w * y1;
+            dr.z += -d.x * y1 - d.y * z1 + d.z * w1 + d.w * x1;
+            dr.w += -d.x * z1 + d.y * y1 - d.z * x1 + d.w * w1;
+            // ... and w.r.t. q1 (the raw pose quaternion)
+            part[12] = d.x * rq.x + d.y * rq.y + d.z * rq.z + d.w * rq.w;
+            part[13] = -d.x * rq.y + d.y * rq.x - d.z * rq.w + d.w * rq.z;
+            part[14] = -d.x * rq.z + d.y * rq.w + d.z * rq.x - d.w * rq.y;
+            part[15] = -d.x * rq.w - d.y * rq.z + d.z * rq.y + d.w * rq.x;
+        }
+        // block sum of the 16 partials of this view: warp butterflies, then one warp adds the 8 warp results
+#pragma unroll
+        for (int k = 0; k < FE_PART_F; k++) {
+            float s = part[k];
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0) s_warp[warp][k] = s;
+        }
+        __syncthreads();
+        if (tid < FE_PART_F) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < FE_THREADS / 32; w++) s += s_warp[w][tid];
+            s_part[v * FE_PART_F + tid] = s;
+        }
+        __syncthreads();
+    }
+    if (in_range) {
+        a.dL_dxyz[3 * idx] = dX; a.dL_dxyz[3 * idx + 1] = dY; a.dL_dxyz[3 * idx + 2] = dZ;
+        reinterpret_cast<float4*>(a.dL_drotation)[idx] = dr;
+    }
+    // this block's partial sums -> scratch[block][view][16] (summed by frontend_pose_kernel)
+    for (int e = tid; e < a.n_views * FE_PART_F; e += FE_THREADS)
+        a.partials[(size_t)blockIdx.x * a.n_views * FE_PART_F + e] = s_part[e];
+}
+
+// One block per view: sums the per-block partials in a fixed order and turns them into dL/d(pose) (7 values).
+__global__ void __launch_bounds__(FE_THREADS) frontend_pose_kernel(const float* __restrict__ partials, int n_blocks,
+                                                                  int n_views, const float* __restrict__ poses,
+                                                                  float* __restrict__ dL_dposes) {
+    __shared__ float red[FE_THREADS / 32];
+    __shared__ float s_sum[FE_PART_F];
+    const int v = blockIdx.x;
+    for (int k = 0; k < FE_PART_F; k++) {
+        float s = 0.f;
+        for (int b = threadIdx.x; b < n_blocks; b += FE_THREADS) s += partials[((size_t)b * n_views + v) * FE_PART_F + k];
+        const float t = block_sum(s, red);
+        if (threadIdx.x == 0) s_sum[k] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    const float* pose = poses + 7 * v;
+    const float q0 = pose[0], q1 = pose[1], q2 = pose[2], q3 = pose[3];
+    const float norm = sqrtf(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);
+    const float r = q0 / norm, x = q1 / norm, y = q2 / norm, z = q3 / norm;
+    const float* M = s_sum + 3;  // M[3*a+b] = sum_i g_a X_b = dL/dR[a][b]
+    // dL/d(normalised quaternion) = sum_ab M_ab dR_ab/dq (R as in utils/pose_utils.py:47-55)
+    const float dr_ = 2 * (-z * M[1] + y * M[2] + z * M[3] - x * M[5] - y * M[6] + x * M[7]);
+    const float dx_ = 2 * (y * M[1] + z * M[2] + y * M[3] - 2 * x * M[4] - r * M[5] + z * M[6] + r * M[7] - 2 * x * M[8]);
+    const float dy_ = 2 * (-2 * y * M[0] + x * M[1] + r * M[2] + x * M[3] + z * M[5] - r * M[6] + z * M[7] - 2 * y * M[8]);
+    const float dz_ = 2 * (-2 * z * M[0] - r * M[1] + x * M[2] + r * M[3] - 2 * z * M[4] + y * M[5] + x * M[6] + y * M[7]);
+    // through q / |q|
+    const float dot = r * dr_ + x * dx_ + y * dy_ + z * dz_;
+    float* o = dL_dposes + 7 * v;
+    o[0] = (dr_ - r * dot) / norm + s_sum[12];
+    o[1] = (dx_ - x * dot) / norm + s_sum[13];
+    o[2] = (dy_ - y * dot) / norm + s_sum[14];
+    o[3] = (dz_ - z * dot) / norm + s_sum[15];
+    o[4] = s_sum[0];
+    o[5] = s_sum[1];
+    o[6] = s_sum[2];
+}
+
+size_t frontend_backward_scratch_bytes(int P, int n_views) {
+    const size_t blocks = (size_t)(P + FE_THREADS - 1) / FE_THREADS;
+    return (blocks * (size_t)n_views * FE_PART_F * sizeof(float) + 255) / 256 * 256;
+}
+
+cudaError_t launch_frontend_bwd(const FrontendBwdArgs& a, float* dL_dposes, cudaStream_t s) {
+    const int blocks = (a.P + FE_THREADS - 1) / FE_THREADS;
+    frontend_bwd_kernel<<<blocks, FE_THREADS, 0, s>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    frontend_pose_kernel<<<a.n_views, FE_THREADS, 0, s>>>(a.partials, blocks, a.n_views, a.poses, dL_dposes);
+    return cudaGetLastError();
+}
+
+}  // namespace das3r

@@ -71,6 +71,30 @@ struct MultiBwdArgs {
     MultiBwdView v[MV_MAX_VIEWS];
 };
 
+// Fused DAS3R render front-end (frontend.cu, include/das3r_frontend.h)
+constexpr int FE_MAX_VIEWS = 16;
+struct FrontendFwdArgs {
+    int P, n_views;
+    const float *xyz, *rotation, *opacity_raw, *scaling_raw, *features_dc, *features_rest, *conf_static, *poses;
+    const int64_t* conf_index;
+    float *opacity, *scales, *shs;
+    float* means3D[FE_MAX_VIEWS];
+    float* rotations[FE_MAX_VIEWS];
+};
+struct FrontendBwdArgs {
+    int P, n_views;
+    const float *xyz, *rotation, *opacity_raw, *scaling_raw, *conf_static, *poses;
+    const int64_t* conf_index;
+    const float *dL_dopacity, *dL_dscales, *dL_dshs;
+    const float* dL_dmeans3D[FE_MAX_VIEWS];
+    const float* dL_drotations[FE_MAX_VIEWS];
+    float *dL_dxyz, *dL_drotation, *dL_dopacity_raw, *dL_dscaling_raw, *dL_dfeatures_dc, *dL_dfeatures_rest, *dL_dconf;
+    float* partials;  // [blocks][n_views][16]
+};
+cudaError_t launch_frontend_fwd(const FrontendFwdArgs& a, cudaStream_t s);
+size_t frontend_backward_scratch_bytes(int P, int n_views);
+cudaError_t launch_frontend_bwd(const FrontendBwdArgs& a, float* dL_dposes, cudaStream_t s);
+
 // forward.cu
 cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
 cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,

@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 #include "../../include/das3r_raster.h"
+#include "../../include/das3r_frontend.h"
 
 namespace {
 
@@ -458,6 +459,135 @@ static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch
     check(das3r_raster_backward_finish((int32_t)n, vs.data(), &g, stream), "rasterize_gaussians_backward_finish");
 }
 
+// ---- fused DAS3R render front-end (include/das3r_frontend.h) ------------------------------------------------------
+static void fill_model(das3r_frontend_model& m, const torch::Tensor& xyz, const torch::Tensor& rotation,
+                       const torch::Tensor& opacity, const torch::Tensor& scaling, const torch::Tensor& f_dc,
+                       const torch::Tensor& f_rest, const torch::Tensor& conf_static, const torch::Tensor& conf_index) {
+    memset(&m, 0, sizeof(m));
+    m.P = (int32_t)xyz.size(0);
+    m.xyz = xyz.data_ptr<float>();
+    m.rotation = rotation.data_ptr<float>();
+    m.opacity = opacity.data_ptr<float>();
+    m.scaling = scaling.data_ptr<float>();
+    m.features_dc = f_dc.defined() && f_dc.numel() ? f_dc.data_ptr<float>() : nullptr;
+    m.features_rest = f_rest.defined() && f_rest.numel() ? f_rest.data_ptr<float>() : nullptr;
+    m.conf_static = conf_static.data_ptr<float>();
+    m.conf_index = conf_index.defined() && conf_index.numel() ? conf_index.data_ptr<int64_t>() : nullptr;
+}
+
+static void check_model(const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity,
+                        const torch::Tensor& scaling, const torch::Tensor& conf_static, const torch::Tensor& conf_index,
+                        const torch::Tensor& poses) {
+    TORCH_CHECK(xyz.is_cuda(), "xyz must be a CUDA tensor: the front-end has no CPU path");
+    const int64_t P = xyz.size(0);
+    auto ok = [&](const torch::Tensor& t, int64_t n) {
+        return t.is_cuda() && t.device() == xyz.device() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() &&
+               t.numel() == n;
+    };
+    TORCH_CHECK(ok(xyz, 3 * P) && ok(rotation, 4 * P) && ok(opacity, P) && ok(scaling, 3 * P),
+                "xyz [P,3], rotation [P,4], opacity [P,1], scaling [P,3] must be contiguous float32 CUDA tensors");
+    TORCH_CHECK(conf_static.is_cuda() && conf_static.scalar_type() == torch::kFloat32 && conf_static.is_contiguous(),
+                "conf_static must be a contiguous float32 CUDA tensor");
+    if (conf_index.defined() && conf_index.numel()) {
+        TORCH_CHECK(conf_index.is_cuda() && conf_index.scalar_type() == torch::kInt64 && conf_index.is_contiguous() &&
+                        conf_index.numel() == P,
+                    "conf_index must be a contiguous int64 CUDA tensor with one entry per Gaussian");
+    } else {
+        TORCH_CHECK(conf_static.numel() >= P, "conf_static has fewer entries than there are Gaussians");
+    }
+    TORCH_CHECK(poses.is_cuda() && poses.scalar_type() == torch::kFloat32 && poses.is_contiguous() && poses.dim() == 2 &&
+                    poses.size(1) == 7 && poses.size(0) >= 1 && poses.size(0) <= DAS3R_FRONTEND_MAX_VIEWS,
+                "poses must be a contiguous float32 CUDA tensor [V,7] with 1 <= V <= 16");
+}
+
+static std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, std::vector<torch::Tensor>, std::vector<torch::Tensor>>
+FrontendForwardCUDA(const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity,
+                    const torch::Tensor& scaling, const torch::Tensor& f_dc, const torch::Tensor& f_rest,
+                    const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses) {
+    check_model(xyz, rotation, opacity, scaling, conf_static, conf_index, poses);
+    const int64_t P = xyz.size(0);
+    TORCH_CHECK(f_dc.is_cuda() && f_dc.is_contiguous() && f_dc.numel() == 3 * P && f_rest.is_cuda() &&
+                    f_rest.is_contiguous() && f_rest.numel() == 45 * P && f_dc.scalar_type() == torch::kFloat32 &&
+                    f_rest.scalar_type() == torch::kFloat32,
+                "features_dc [P,1,3] and features_rest [P,15,3] must be contiguous float32 CUDA tensors");
+    c10::cuda::CUDAGuard guard(xyz.device());
+    const int V = (int)poses.size(0);
+    auto o = xyz.options();
+    auto opac = torch::empty({P, 1}, o), scales = torch::empty({P, 3}, o), shs = torch::empty({P, 16, 3}, o);
+    std::vector<torch::Tensor> means, rots;
+    das3r_frontend_outputs out;
+    memset(&out, 0, sizeof(out));
+    out.opacity = opac.data_ptr<float>();
+    out.scales = scales.data_ptr<float>();
+    out.shs = shs.data_ptr<float>();
+    for (int v = 0; v < V; v++) {
+        means.push_back(torch::empty({P, 3}, o));
+        rots.push_back(torch::empty({P, 4}, o));
+        out.means3D[v] = means.back().data_ptr<float>();
+        out.rotations[v] = rots.back().data_ptr<float>();
+    }
+    das3r_frontend_model m;
+    fill_model(m, xyz, rotation, opacity, scaling, f_dc, f_rest, conf_static, conf_index);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(xyz.device().index()).stream();
+    check(das3r_frontend_forward(&m, V, poses.data_ptr<float>(), &out, stream), "frontend_forward");
+    return std::make_tuple(opac, scales, shs, means, rots);
+}
+
+static std::vector<torch::Tensor> FrontendBackwardCUDA(
+    const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity, const torch::Tensor& scaling,
+    const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses,
+    const torch::Tensor& dL_dopacity, const torch::Tensor& dL_dscales, const torch::Tensor& dL_dshs,
+    const std::vector<torch::Tensor>& dL_dmeans, const std::vector<torch::Tensor>& dL_drots) {
+    check_model(xyz, rotation, opacity, scaling, conf_static, conf_index, poses);
+    const int64_t P = xyz.size(0);
+    const int V = (int)poses.size(0);
+    TORCH_CHECK((int)dL_dmeans.size() == V && (int)dL_drots.size() == V, "one dL_dmeans3D / dL_drotations per view");
+    c10::cuda::CUDAGuard guard(xyz.device());
+    const auto dev = xyz.device();
+    auto o = xyz.options();
+    std::vector<torch::Tensor> keep;
+    auto cg = [&](const torch::Tensor& t, int64_t n, const char* name) {
+        TORCH_CHECK(t.is_cuda() && t.device() == dev && t.scalar_type() == torch::kFloat32 && t.numel() == n, name,
+                    " must be a float32 CUDA tensor of ", n, " elements");
+        keep.push_back(t.contiguous());
+        return keep.back().data_ptr<float>();
+    };
+    das3r_frontend_grads_in gin;
+    memset(&gin, 0, sizeof(gin));
+    gin.dL_dopacity = cg(dL_dopacity, P, "dL_dopacity");
+    gin.dL_dscales = cg(dL_dscales, 3 * P, "dL_dscales");
+    gin.dL_dshs = cg(dL_dshs, 48 * P, "dL_dshs");
+    for (int v = 0; v < V; v++) {
+        gin.dL_dmeans3D[v] = cg(dL_dmeans[v], 3 * P, "dL_dmeans3D");
+        gin.dL_drotations[v] = cg(dL_drots[v], 4 * P, "dL_drotations");
+    }
+    auto dxyz = torch::empty({P, 3}, o), drot = torch::empty({P, 4}, o), dop = torch::empty({P, 1}, o);
+    auto dsc = torch::empty({P, 3}, o), ddc = torch::empty({P, 1, 3}, o), drest = torch::empty({P, 15, 3}, o);
+    auto dconf = torch::empty({P}, o), dposes = torch::empty({V, 7}, o);
+    auto scratch = torch::empty({(long long)das3r_frontend_backward_scratch_bytes((int32_t)P, V)},
+                                torch::TensorOptions().dtype(torch::kByte).device(dev));
+    das3r_frontend_grads_out gout;
+    memset(&gout, 0, sizeof(gout));
+    gout.dL_dxyz = dxyz.data_ptr<float>();
+    gout.dL_drotation = drot.data_ptr<float>();
+    gout.dL_dopacity = dop.data_ptr<float>();
+    gout.dL_dscaling = dsc.data_ptr<float>();
+    gout.dL_dfeatures_dc = ddc.data_ptr<float>();
+    gout.dL_dfeatures_rest = drest.data_ptr<float>();
+    gout.dL_dconf = dconf.data_ptr<float>();
+    gout.dL_dposes = dposes.data_ptr<float>();
+    gout.scratch = reinterpret_cast<float*>(scratch.data_ptr());
+    das3r_frontend_model m;
+    torch::Tensor none;
+    fill_model(m, xyz, rotation, opacity, scaling, none, none, conf_static, conf_index);
+    // the backward does not read the features, only their shapes matter; the C ABI wants non-null pointers
+    m.features_dc = m.xyz;
+    m.features_rest = m.xyz;
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    check(das3r_frontend_backward(&m, V, poses.data_ptr<float>(), &gin, &gout, stream), "frontend_backward");
+    return {dxyz, drot, dop, dsc, ddc, drest, dconf, dposes};
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     // The GIL is released around every call into the library: a host that drives several CUDA streams from several
     // threads (bench.py) must not serialise on the forward's read-back of num_rendered.
@@ -467,6 +597,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardIntoCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_blend", &BackwardBlendCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_finish", &BackwardFinishCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("frontend_forward", &FrontendForwardCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("frontend_backward", &FrontendBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
     m.def("prof_collect", [](bool reset) {
         int n = das3r_prof_num_stages();

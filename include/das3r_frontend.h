@@ -1,0 +1,88 @@
+/* C ABI of the fused DAS3R render front-end: everything DAS3R's render() does to the
+ * Gaussian parameters between the model and the rasterizer call, for all views of a step at once, and its backward.
+ *
+ * The reference does this with about ten separate torch kernels per view (clone, index, cat, matmul, unbind/stack,
+ * sigmoid, exp, mul): reference gaussian_renderer/__init__.py:83-108 and :126,
+ *   means3D   = (get_camera_from_tensor(pose) @ [xyz | 1]^T)^T[:, :3]        (:83-90, utils/pose_utils.py:57-85, :10-55)
+ *   rotations = quadmultiply(pose[:4], _rotation)                            (:91, utils/pose_utils.py:86-104)
+ *   opacity   = sigmoid(_opacity) * _conf_static.reshape(-1,1)[aggregated_mask]   (:95-97, scene/gaussian_model.py:194)
+ *   scales    = exp(_scaling)                                                (:106, scene/gaussian_model.py:103-105)
+ *   shs       = cat(_features_dc, _features_rest, dim=1)                     (:126, scene/gaussian_model.py:186-190)
+ * Note the reference's asymmetry, kept here: the rotation matrix that moves the means is built from the NORMALISED
+ * pose quaternion (quad2rotation divides by the norm), the quaternion product uses the RAW one.
+ *
+ * Same conventions as das3r_raster.h: extern "C", plain device pointers, caller owns all memory, work is enqueued on
+ * `stream`, return 0 or a negative DAS3R_E* code with das3r_last_error(). No CPU path.
+ */
+#ifndef DAS3R_FRONTEND_H
+#define DAS3R_FRONTEND_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DAS3R_FRONTEND_MAX_VIEWS 16 /* views per call */
+
+typedef struct das3r_frontend_model {
+    int32_t P;                   /* Gaussians */
+    const float* xyz;            /* [P,3]   _xyz */
+    const float* rotation;       /* [P,4]   _rotation (raw, un-normalised; r,x,y,z) */
+    const float* opacity;        /* [P,1]   _opacity (pre-sigmoid) */
+    const float* scaling;        /* [P,3]   _scaling (log) */
+    const float* features_dc;    /* [P,1,3] _features_dc */
+    const float* features_rest;  /* [P,15,3] _features_rest */
+    const float* conf_static;    /* flat _conf_static (one value per pointmap pixel) */
+    const int64_t* conf_index;   /* [P] position of Gaussian i in conf_static = nonzero(aggregated_mask); NULL: i */
+} das3r_frontend_model;
+
+typedef struct das3r_frontend_outputs {
+    float* opacity;    /* [P,1]    sigmoid(_opacity) * conf */
+    float* scales;     /* [P,3]    exp(_scaling) */
+    float* shs;        /* [P,16,3] {dc, rest} */
+    float* means3D[DAS3R_FRONTEND_MAX_VIEWS];   /* per view [P,3] */
+    float* rotations[DAS3R_FRONTEND_MAX_VIEWS]; /* per view [P,4] */
+} das3r_frontend_outputs;
+
+/* Gradients arriving from the rasterizer (das3r_raster_backward_finish: the three shared ones summed over the views,
+ * means / rotations per view). */
+typedef struct das3r_frontend_grads_in {
+    const float* dL_dopacity;  /* [P,1] */
+    const float* dL_dscales;   /* [P,3] */
+    const float* dL_dshs;      /* [P,16,3] */
+    const float* dL_dmeans3D[DAS3R_FRONTEND_MAX_VIEWS];   /* per view [P,3] */
+    const float* dL_drotations[DAS3R_FRONTEND_MAX_VIEWS]; /* per view [P,4] */
+} das3r_frontend_grads_in;
+
+/* Gradients w.r.t. the model parameters and the poses; every element is written. */
+typedef struct das3r_frontend_grads_out {
+    float* dL_dxyz;            /* [P,3] */
+    float* dL_drotation;       /* [P,4] */
+    float* dL_dopacity;        /* [P,1] */
+    float* dL_dscaling;        /* [P,3] */
+    float* dL_dfeatures_dc;    /* [P,1,3] */
+    float* dL_dfeatures_rest;  /* [P,15,3] */
+    float* dL_dconf;           /* [P]: gradient w.r.t. conf_static[conf_index[i]] (the caller scatters it; indices are
+                                  unique) */
+    float* dL_dposes;          /* [n_views,7] */
+    float* scratch;            /* das3r_frontend_backward_scratch_bytes(P, n_views) bytes */
+} das3r_frontend_grads_out;
+
+/* poses: [n_views,7] device array, {quaternion r,x,y,z ; translation} per view (camera_pose in render()). */
+int das3r_frontend_forward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                           const das3r_frontend_outputs* out, void* stream);
+
+size_t das3r_frontend_backward_scratch_bytes(int32_t P, int32_t n_views);
+
+/* Backward of das3r_frontend_forward: one pass over the Gaussians turns the per-view dL_dmeans3D / dL_drotations into
+ * dL_dxyz / dL_drotation and per-block partial sums for the pose gradients, and applies the activation derivatives; a
+ * second, tiny kernel reduces the partial sums (deterministically, no atomics) to dL_dposes. */
+int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                            const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
