@@ -545,9 +545,52 @@ def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
             dist.barrier()
         return round(world * vps * steps / (ms / 1e3), 2)
 
+    # The same step started one stage earlier: raw model parameters + camera poses -> fused front-end
+    # (das3r_b200/frontend.py: what gaussian_renderer/__init__.py:83-126 does with ~10 torch kernels per view) ->
+    # MultiViewRasterizer; the backward reaches the raw parameters and the poses.
+    from das3r_b200.frontend import render_inputs
+    raw = dict(xyz=per_view[0]["means"].detach().clone(), rotation=per_view[0]["rots"].detach().clone(),
+               opacity=torch.logit(S["opac"].clamp(1e-6, 1 - 1e-6)), scaling=torch.log(S["scales"]),
+               features_dc=S["shs"][:, :1].contiguous(), features_rest=S["shs"][:, 1:].contiguous(),
+               conf_static=torch.ones(args.P, device=dev))
+    raw = {k: v.requires_grad_(True) for k, v in raw.items()}
+    poses_host = torch.tensor([[1.0, 0, 0, 0, 0, 0, 0]] * vps).pin_memory()  # identity: the scene stays in view
+    poses_dev = torch.empty(vps, 7, device=dev, requires_grad=True)
+
+    def step_frontend():
+        main = torch.cuda.current_stream()
+        for t in list(raw.values()) + [poses_dev]:
+            t.grad = None
+        with torch.no_grad():
+            poses_dev.copy_(poses_host, non_blocking=True)
+        for v in range(vps):
+            cam_dev[v].copy_(cam_host, non_blocking=True)
+        copy_stream.wait_stream(main)
+        with torch.cuda.stream(copy_stream):
+            for v in range(vps):
+                dL_dev[v].copy_(dL_host, non_blocking=True)
+        fe = render_inputs(raw["xyz"], raw["rotation"], raw["opacity"], raw["scaling"], raw["features_dc"],
+                           raw["features_rest"], raw["conf_static"], None, poses_dev)
+        colors, _radii = mv([settings_for(v) for v in range(vps)], fe.means3D, fe.rotations, fe.opacity, fe.shs, fe.scales)
+        main.wait_stream(copy_stream)
+        loss = sum((c * dL_dev[v]).sum() for v, c in enumerate(colors))
+        copy_stream.wait_stream(main)
+        with torch.cuda.stream(copy_stream):
+            for v, c in enumerate(colors):
+                img_host[v].copy_(c.detach(), non_blocking=True)
+                c.record_stream(copy_stream)
+        loss.backward()
+        loss_host.copy_(loss.detach().view(1), non_blocking=True)
+        if world > 1:
+            for t in raw.values():
+                dist.all_reduce(t.grad)
+        main.wait_stream(copy_stream)
+        main.synchronize()
+
     steps = max(3, args.steps // 3)
     v_multi = timed(step_multi, steps)
     v_single = timed(step_per_view, steps)
+    v_front = timed(step_frontend, steps)
     return {"value": v_multi, "unit": "views/s",
             "h2d_bytes_per_step": vps * (38 * 4 + 3 * H * W * 4), "d2h_bytes_per_step": vps * (3 * H * W * 4) + 4,
             "steps": steps,
@@ -555,6 +598,10 @@ def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
                     "backward blends on CUDA streams, one fused gradient pass) + autograd; per view H2D (pinned) of the "
                     "camera bundle and dL/dcolour and D2H of the rendered image, per step D2H of the loss; Gaussian "
                     "parameters resident (model state)",
+            "from_raw_parameters": {"value": v_front, "unit": "views/s",
+                                    "what": "same step started from the raw model parameters and camera poses: fused "
+                                            "front-end (das3r_b200.frontend.render_inputs) + MultiViewRasterizer; "
+                                            "gradients reach the raw parameters and the poses"},
             "per_view_api": {"value": v_single, "unit": "views/s",
                              "what": "the drop-in GaussianRasterizer.forward + autograd backward called once per view, "
                                      "single stream, same copies"}}
