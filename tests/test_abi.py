@@ -10,9 +10,14 @@ ROOT = Hn.ROOT
 
 
 def declared_symbols():
-    text = open(os.path.join(ROOT, "include", "das3r_raster.h")).read()
-    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(das3r_[a-z0-9_]+)\s*\(", text)))
+    names = set()
+    for h in sorted(os.listdir(os.path.join(ROOT, "include"))):
+        if not h.endswith(".h"):
+            continue
+        text = open(os.path.join(ROOT, "include", h)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names |= set(re.findall(r"\b(das3r_[a-z0-9_]+)\s*\(", text))
+    return sorted(names)
 
 
 def test_header_symbols_are_exported():
@@ -20,6 +25,8 @@ def test_header_symbols_are_exported():
     names = declared_symbols()
     assert "das3r_raster_forward" in names and "das3r_raster_backward" in names and "das3r_knn_dist2" in names
     assert "das3r_mark_visible" in names
+    assert "das3r_frontend_forward" in names and "das3r_frontend_backward" in names
+    assert "das3r_raster_backward_blend" in names and "das3r_raster_backward_finish" in names
     for n in names:
         assert hasattr(lib, n), f"{n} is declared in include/das3r_raster.h but not exported by libdas3r_raster.so"
 
