@@ -32,19 +32,50 @@ __device__ __forceinline__ void pose_to_smem(const float* __restrict__ pose, flo
 }
 
 // Block-cooperative copy between the split SH layout (dc [P,1,3], rest [P,15,3]) and the joint one ([P,16,3]): flat,
-// coalesced on the split side. TO_JOINT: dc/rest -> shs; else shs -> dc/rest.
+// coalesced on the split side, 15 independent loads in flight per thread before the first store (a load -> store loop
+// keeps one 4-byte access per thread in flight and ran at a third of the bandwidth). TO_JOINT: dc/rest -> shs; else
+// shs -> dc/rest.
 template <bool TO_JOINT, typename TD, typename TR, typename TS>
 __device__ __forceinline__ void sh_rows_copy(TD* dc, TR* rest, TS* shs, int base, int nvalid) {
     const int tid = threadIdx.x;
-    for (int e = tid; e < nvalid * 3; e += FE_THREADS) {
-        const int g = e / 3, j = e - 3 * g;
-        if constexpr (TO_JOINT) shs[(size_t)(base + g) * 48 + j] = dc[(size_t)base * 3 + e];
-        else dc[(size_t)base * 3 + e] = shs[(size_t)(base + g) * 48 + j];
+    {
+        float v[3];
+        const int total = nvalid * 3;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const int e = tid + k * FE_THREADS;
+            const int g = e / 3, j = e - 3 * g;
+            if (e < total) v[k] = TO_JOINT ? dc[(size_t)base * 3 + e] : shs[(size_t)(base + g) * 48 + j];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const int e = tid + k * FE_THREADS;
+            const int g = e / 3, j = e - 3 * g;
+            if (e < total) {
+                if constexpr (TO_JOINT) shs[(size_t)(base + g) * 48 + j] = v[k];
+                else dc[(size_t)base * 3 + e] = v[k];
+            }
+        }
     }
-    for (int e = tid; e < nvalid * 45; e += FE_THREADS) {
-        const int g = e / 45, j = e - 45 * g;
-        if constexpr (TO_JOINT) shs[(size_t)(base + g) * 48 + 3 + j] = rest[(size_t)base * 45 + e];
-        else rest[(size_t)base * 45 + e] = shs[(size_t)(base + g) * 48 + 3 + j];
+    const int total = nvalid * 45;
+#pragma unroll 1
+    for (int c = 0; c < 3; c++) {
+        float v[15];
+#pragma unroll
+        for (int k = 0; k < 15; k++) {
+            const int e = tid + (c * 15 + k) * FE_THREADS;
+            const int g = e / 45, j = e - 45 * g;
+            if (e < total) v[k] = TO_JOINT ? rest[(size_t)base * 45 + e] : shs[(size_t)(base + g) * 48 + 3 + j];
+        }
+#pragma unroll
+        for (int k = 0; k < 15; k++) {
+            const int e = tid + (c * 15 + k) * FE_THREADS;
+            const int g = e / 45, j = e - 45 * g;
+            if (e < total) {
+                if constexpr (TO_JOINT) shs[(size_t)(base + g) * 48 + 3 + j] = v[k];
+                else rest[(size_t)base * 45 + e] = v[k];
+            }
+        }
     }
 }
 
@@ -108,10 +139,27 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
     return t;
 }
 
+// Sums 16 per-lane values over the warp with 16 shuffles instead of 80: at every butterfly step a lane hands half of
+// its values to its partner and keeps the other half. Returns the complete sum of value `idx` (a function of the
+// lane's bits 4..1; both lanes of a pair hold the same result).
+__device__ __forceinline__ float warp_reduce16(const float (&v)[16], int lane, int& idx) {
+    const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4, h1 = lane & 2;
+    float a[8], b[4], c[2];
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = (h4 ? v[k + 8] : v[k]) + __shfl_xor_sync(0xffffffffu, h4 ? v[k] : v[k + 8], 16);
+#pragma unroll
+    for (int k = 0; k < 4; k++) b[k] = (h3 ? a[k + 4] : a[k]) + __shfl_xor_sync(0xffffffffu, h3 ? a[k] : a[k + 4], 8);
+#pragma unroll
+    for (int k = 0; k < 2; k++) c[k] = (h2 ? b[k + 2] : b[k]) + __shfl_xor_sync(0xffffffffu, h2 ? b[k] : b[k + 2], 4);
+    float d = (h1 ? c[1] : c[0]) + __shfl_xor_sync(0xffffffffu, h1 ? c[0] : c[1], 2);
+    d += __shfl_xor_sync(0xffffffffu, d, 1);
+    idx = (h4 ? 8 : 0) + (h3 ? 4 : 0) + (h2 ? 2 : 0) + (h1 ? 1 : 0);
+    return d;
+}
+
 __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_constant__ FrontendBwdArgs a) {
     __shared__ float s_pose[FE_MAX_VIEWS * FE_POSE_F];
-    __shared__ float s_part[FE_MAX_VIEWS * FE_PART_F];           // this block's partial sums
-    __shared__ float s_warp[FE_THREADS / 32][FE_PART_F];
+    __shared__ float s_warp[FE_MAX_VIEWS][FE_THREADS / 32][FE_PART_F];  // per view: every warp's 16 sums
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int base = blockIdx.x * FE_THREADS;
     const int idx = base + tid;
@@ -140,7 +188,7 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
 
     float dX = 0.f, dY = 0.f, dZ = 0.f;
     float4 dr = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
+#pragma unroll 2
     for (int v = 0; v < a.n_views; v++) {
         const float* p = s_pose + FE_POSE_F * v;
         float part[FE_PART_F];
@@ -170,30 +218,24 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
             part[14] = -d.x * rq.z + d.y * rq.w + d.z * rq.x - d.w * rq.y;
             part[15] = -d.x * rq.w - d.y * rq.z + d.z * rq.y + d.w * rq.x;
         }
-        // block sum of the 16 partials of this view: warp butterflies, then one warp adds the 8 warp results
-#pragma unroll
-        for (int k = 0; k < FE_PART_F; k++) {
-            float s = part[k];
-#pragma unroll
-            for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) s_warp[warp][k] = s;
-        }
-        __syncthreads();
-        if (tid < FE_PART_F) {
-            float s = 0.f;
-#pragma unroll
-            for (int w = 0; w < FE_THREADS / 32; w++) s += s_warp[w][tid];
-            s_part[v * FE_PART_F + tid] = s;
-        }
-        __syncthreads();
+        // the warp's sums of the 16 partials of this view (the block sum follows after the loop: no barrier in here)
+        int pi;
+        const float ps = warp_reduce16(part, lane, pi);
+        if ((lane & 1) == 0) s_warp[v][warp][pi] = ps;
     }
     if (in_range) {
         a.dL_dxyz[3 * idx] = dX; a.dL_dxyz[3 * idx + 1] = dY; a.dL_dxyz[3 * idx + 2] = dZ;
         reinterpret_cast<float4*>(a.dL_drotation)[idx] = dr;
     }
     // this block's partial sums -> scratch[block][view][16] (summed by frontend_pose_kernel)
-    for (int e = tid; e < a.n_views * FE_PART_F; e += FE_THREADS)
-        a.partials[(size_t)blockIdx.x * a.n_views * FE_PART_F + e] = s_part[e];
+    __syncthreads();
+    for (int e = tid; e < a.n_views * FE_PART_F; e += FE_THREADS) {
+        const int v = e / FE_PART_F, k = e - v * FE_PART_F;
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < FE_THREADS / 32; w++) t += s_warp[v][w][k];
+        a.partials[(size_t)blockIdx.x * a.n_views * FE_PART_F + e] = t;
+    }
 }
 
 // One block per view: sums the per-block partials in a fixed order and turns them into dL/d(pose) (7 values).
