@@ -5,9 +5,15 @@
 //                      rasterizer_impl.cu:277, and identifyTileRanges, :116-138)
 //   scatter         -> one (depth|index) entry per (Gaussian, tile) pair into its tile bucket (replaces
 //                      duplicateWithKeys, rasterizer_impl.cu:70-111)
-//   tile_sort       -> per-tile bitonic sort in registers/shuffles/shared memory (replaces the global 64-bit
-//                      cub::DeviceRadixSort, rasterizer_impl.cu:303-308) + gather of tile-ordered records
-//   blend_fwd       -> front-to-back alpha blend per 16x16 tile (replaces renderCUDA, forward.cu:261-374)
+//   tile_sort       -> per-tile most-significant-digit bucket sort in shared memory, three size classes, bitonic
+//                      network for skewed depths, library segmented sort only for tiles above 16384 entries (replaces
+//                      the global 64-bit cub::DeviceRadixSort, rasterizer_impl.cu:303-308) + gather_records: the
+//                      tile-ordered record streams
+//   rect_lists      -> per 8x4-pixel rectangle the list of {tile-list position, pixel mask} of the Gaussians that can
+//                      reach alpha >= 1/255 there (no reference counterpart: there every thread of the tile looks at
+//                      every Gaussian of the tile)
+//   blend_fwd       -> front-to-back alpha blend, one warp per rectangle walking its list (replaces renderCUDA,
+//                      forward.cu:261-374; see blend_common.cuh)
 //
 // The result of scatter+tile_sort is bit-identical to the reference's stable LSD radix sort of (tile<<32|depth)
 // keys: equal keys keep emission order there, i.e. ascending Gaussian index, so the total order is
