@@ -42,7 +42,7 @@ METRIC = "raster fwd+bwd views/s @1M Gaussians 512x288"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=300)  # ~1 s timed region: enough clock samples
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "oracle-cpu"])
     ap.add_argument("--views-per-step", type=int, default=8)
@@ -64,7 +64,7 @@ def parse_args():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -78,7 +78,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
                  str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
@@ -424,6 +424,7 @@ def main():
                   "after the timed region",
         "stage_ms": {k: round(v, 5) for k, v in stages.items()},
         "stage_share_of_step": {k: round(v / sum(stage_total.values()), 4) for k, v in stage_total.items()},
+        "sort_gkeys_per_s": round(R / (stages["tile_sort"] * 1e-3) / 1e9, 2) if "tile_sort" in stages else None,
         "stage_frac_of_hbm_peak": {k: round(sb[k] / (v * 1e-3) / 1e9 / peak, 4) for k, v in kern.items()},
         "view": {"algorithmic_bytes": vb, "achieved_gbs": round(vb / (per_view_ms * 1e-3) / 1e9, 1),
                  "frac": round(vb / (per_view_ms * 1e-3) / 1e9 / peak, 4),
@@ -587,7 +588,7 @@ def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
         main.wait_stream(copy_stream)
         main.synchronize()
 
-    steps = max(3, args.steps // 3)
+    steps = max(3, min(args.steps // 3, 40))
     v_multi = timed(step_multi, steps)
     v_single = timed(step_per_view, steps)
     v_front = timed(step_frontend, steps)
