@@ -3,6 +3,7 @@
 // (reference cuda_rasterizer/rasterizer_impl.cu:141-434) and SimpleKNN::knn (simple-knn/simple_knn.cu:186-222).
 #include "../../include/das3r_raster.h"
 #include "../../include/das3r_frontend.h"
+#include "../../include/das3r_loss.h"
 #include "kernels.cuh"
 #include <stdio.h>
 #include <stdlib.h>
@@ -667,6 +668,59 @@ int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, 
     cudaError_t e = launch_frontend_bwd(a, gout->dL_dposes, stream);
     g_launches += 2;
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_bwd", e);
+    return DAS3R_OK;
+}
+
+
+// ---- fused photometric loss (include/das3r_loss.h) ----------------------------------------------------------------
+static int loss_prepare(const das3r_loss_inputs* in, const char* who, LossArgs* a) {
+    if (!in || in->width <= 0 || in->height <= 0 || !in->image || !in->gt || !(in->lambda_dssim >= 0.f && in->lambda_dssim <= 1.f))
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": null or invalid argument");
+    // the window weights live in constant memory: uploaded once per device
+    static std::mutex mu;
+    static bool uploaded[64] = {false};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) return fail(DAS3R_ECUDA, who, e);
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!uploaded[dev]) {
+            e = loss_upload_window();
+            if (e != cudaSuccess) return fail(DAS3R_ECUDA, "loss window upload", e);
+            uploaded[dev] = true;
+        }
+    }
+    a->W = in->width; a->H = in->height; a->lambda_dssim = in->lambda_dssim;
+    a->image = in->image; a->gt = in->gt; a->static_mask = in->static_mask;
+    return DAS3R_OK;
+}
+
+size_t das3r_loss_state_bytes(int32_t width, int32_t height) {
+    return (width > 0 && height > 0) ? loss_state_bytes(width, height) : 0;
+}
+
+int das3r_loss_forward(const das3r_loss_inputs* in, float* out, void* state, void* stream_v) {
+    g_err.clear();
+    LossArgs a;
+    int rc = loss_prepare(in, "loss_forward", &a);
+    if (rc != DAS3R_OK) return rc;
+    if (!out || !state) return fail_msg(DAS3R_EINVAL, "loss_forward: null output or state");
+    cudaError_t e = launch_loss_fwd(a, out, state, static_cast<cudaStream_t>(stream_v));
+    g_launches += 2;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "loss_fwd", e);
+    return DAS3R_OK;
+}
+
+int das3r_loss_backward(const das3r_loss_inputs* in, const void* state, const float* grad_loss, float* dL_dimage,
+                        float* dL_dstatic, float* dL_dgt, void* stream_v) {
+    g_err.clear();
+    LossArgs a;
+    int rc = loss_prepare(in, "loss_backward", &a);
+    if (rc != DAS3R_OK) return rc;
+    if (!state || !dL_dimage) return fail_msg(DAS3R_EINVAL, "loss_backward: null state or dL_dimage");
+    cudaError_t e = launch_loss_bwd(a, state, grad_loss, dL_dimage, dL_dstatic, dL_dgt, static_cast<cudaStream_t>(stream_v));
+    g_launches += 1;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "loss_bwd", e);
     return DAS3R_OK;
 }
 

@@ -95,6 +95,18 @@ cudaError_t launch_frontend_fwd(const FrontendFwdArgs& a, cudaStream_t s);
 size_t frontend_backward_scratch_bytes(int P, int n_views);
 cudaError_t launch_frontend_bwd(const FrontendBwdArgs& a, float* dL_dposes, cudaStream_t s);
 
+// Fused photometric loss (loss.cu, include/das3r_loss.h)
+struct LossArgs {
+    int W, H;
+    float lambda_dssim;
+    const float *image, *gt, *static_mask;
+};
+cudaError_t loss_upload_window();  // once per device: the 11 window weights into constant memory
+size_t loss_state_bytes(int W, int H);
+cudaError_t launch_loss_fwd(const LossArgs& a, float* out, void* state, cudaStream_t s);
+cudaError_t launch_loss_bwd(const LossArgs& a, const void* state, const float* grad_loss, float* dL_dimage,
+                            float* dL_dstatic, float* dL_dgt, cudaStream_t s);
+
 // forward.cu
 cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
 cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,

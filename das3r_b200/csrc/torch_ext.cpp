@@ -10,6 +10,7 @@
 #include <vector>
 #include "../../include/das3r_raster.h"
 #include "../../include/das3r_frontend.h"
+#include "../../include/das3r_loss.h"
 
 namespace {
 
@@ -588,6 +589,75 @@ static std::vector<torch::Tensor> FrontendBackwardCUDA(
     return {dxyz, drot, dop, dsc, ddc, drest, dconf, dposes};
 }
 
+// ---- fused photometric loss (include/das3r_loss.h) ----------------------------------------------------------------
+static void loss_inputs(das3r_loss_inputs& in, const torch::Tensor& image, const torch::Tensor& gt,
+                        const torch::Tensor& static_mask, float lambda_dssim) {
+    TORCH_CHECK(image.is_cuda(), "image must be a CUDA tensor: the loss has no CPU path");
+    TORCH_CHECK(image.dim() == 3 && image.size(0) == 3 && image.scalar_type() == torch::kFloat32 && image.is_contiguous(),
+                "image must be a contiguous float32 [3,H,W] tensor");
+    TORCH_CHECK(gt.is_cuda() && gt.device() == image.device() && gt.sizes() == image.sizes() &&
+                    gt.scalar_type() == torch::kFloat32 && gt.is_contiguous(),
+                "gt must be a contiguous float32 CUDA tensor of the image's shape");
+    const bool has_static = static_mask.defined() && static_mask.numel() > 0;
+    if (has_static)
+        TORCH_CHECK(static_mask.is_cuda() && static_mask.device() == image.device() &&
+                        static_mask.scalar_type() == torch::kFloat32 && static_mask.is_contiguous() &&
+                        static_mask.numel() == image.size(1) * image.size(2),
+                    "static mask must be a contiguous float32 CUDA tensor with H*W elements");
+    memset(&in, 0, sizeof(in));
+    in.height = (int32_t)image.size(1);
+    in.width = (int32_t)image.size(2);
+    in.lambda_dssim = lambda_dssim;
+    in.image = image.data_ptr<float>();
+    in.gt = gt.data_ptr<float>();
+    in.static_mask = has_static ? static_mask.data_ptr<float>() : nullptr;
+}
+
+// -> (out [2] = {loss, psnr}, state)
+static std::tuple<torch::Tensor, torch::Tensor> LossForwardCUDA(const torch::Tensor& image, const torch::Tensor& gt,
+                                                                const torch::Tensor& static_mask, float lambda_dssim) {
+    das3r_loss_inputs in;
+    loss_inputs(in, image, gt, static_mask, lambda_dssim);
+    c10::cuda::CUDAGuard guard(image.device());
+    auto out = torch::empty({2}, image.options());
+    auto state = torch::empty({(long long)das3r_loss_state_bytes(in.width, in.height)},
+                              torch::TensorOptions().dtype(torch::kByte).device(image.device()));
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(image.device().index()).stream();
+    check(das3r_loss_forward(&in, out.data_ptr<float>(), state.data_ptr(), stream), "loss_forward");
+    return std::make_tuple(out, state);
+}
+
+// -> (dL_dimage, dL_dstatic or empty, dL_dgt or empty); grad_loss: 1-element float32 CUDA tensor or empty (= 1)
+static std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> LossBackwardCUDA(
+    const torch::Tensor& image, const torch::Tensor& gt, const torch::Tensor& static_mask, float lambda_dssim,
+    const torch::Tensor& state, const torch::Tensor& grad_loss, bool want_static, bool want_gt) {
+    das3r_loss_inputs in;
+    loss_inputs(in, image, gt, static_mask, lambda_dssim);
+    TORCH_CHECK(state.is_cuda() && (size_t)state.numel() >= das3r_loss_state_bytes(in.width, in.height),
+                "state must be the tensor loss_forward returned");
+    const float* gl = nullptr;
+    torch::Tensor glc;
+    if (grad_loss.defined() && grad_loss.numel() > 0) {
+        TORCH_CHECK(grad_loss.is_cuda() && grad_loss.scalar_type() == torch::kFloat32 && grad_loss.numel() == 1,
+                    "grad_loss must be a 1-element float32 CUDA tensor");
+        glc = grad_loss.contiguous();
+        gl = glc.data_ptr<float>();
+    }
+    c10::cuda::CUDAGuard guard(image.device());
+    auto dimg = torch::empty_like(image);
+    torch::Tensor dstatic, dgt;
+    if (want_static) dstatic = torch::empty({image.size(1), image.size(2)}, image.options());
+    if (want_gt) dgt = torch::empty_like(image);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(image.device().index()).stream();
+    check(das3r_loss_backward(&in, state.data_ptr(), gl, dimg.data_ptr<float>(),
+                              want_static ? dstatic.data_ptr<float>() : nullptr, want_gt ? dgt.data_ptr<float>() : nullptr,
+                              stream),
+          "loss_backward");
+    if (!want_static) dstatic = torch::empty({0}, image.options());
+    if (!want_gt) dgt = torch::empty({0}, image.options());
+    return std::make_tuple(dimg, dstatic, dgt);
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     // The GIL is released around every call into the library: a host that drives several CUDA streams from several
     // threads (bench.py) must not serialise on the forward's read-back of num_rendered.
@@ -599,6 +669,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians_backward_finish", &BackwardFinishCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("frontend_forward", &FrontendForwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("frontend_backward", &FrontendBackwardCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("loss_forward", &LossForwardCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("loss_backward", &LossBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
     m.def("prof_collect", [](bool reset) {
         int n = das3r_prof_num_stages();
