@@ -2,12 +2,13 @@
 (submodules/diff-gaussian-rasterization) and 3-NN initialiser (submodules/simple-knn).
 
 Layout:
-  csrc/            hand-written CUDA kernels + the C ABI (include/das3r_raster.h, include/das3r_frontend.h, include/das3r_loss.h) + the thin
+  csrc/            hand-written CUDA kernels + the C ABI (include/das3r_raster.h, include/das3r_frontend.h, include/das3r_loss.h, include/das3r_adam.h) + the thin
                    torch binding
   rasterizer.py    the Python surface DAS3R imports (GaussianRasterizationSettings, GaussianRasterizer, ...)
   multiview.py     MultiViewRasterizer: all views of a step in one autograd node (streams + fused gradient pass)
   frontend.py      render_inputs: DAS3R's render() front-end (pose transform, activations, SH concat) as one fused op
   loss.py          photometric_loss: the masked L1 + SSIM training loss (and PSNR) as one fused op
+  optim.py         FusedAdam: the Adam step of all parameter groups in one launch
   knn.py           distCUDA2
   synth.py         synthetic DAS3R-shaped scenes for tests and bench (no datasets on the box)
   sharding.py      view/frame sharding + the one gradient all-reduce of the multi-GPU plan

@@ -4,6 +4,8 @@
 #include "../../include/das3r_raster.h"
 #include "../../include/das3r_frontend.h"
 #include "../../include/das3r_loss.h"
+#include "../../include/das3r_adam.h"
+#include <math.h>
 #include "kernels.cuh"
 #include <stdio.h>
 #include <stdlib.h>
@@ -721,6 +723,50 @@ int das3r_loss_backward(const das3r_loss_inputs* in, const void* state, const fl
     cudaError_t e = launch_loss_bwd(a, state, grad_loss, dL_dimage, dL_dstatic, dL_dgt, static_cast<cudaStream_t>(stream_v));
     g_launches += 1;
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "loss_bwd", e);
+    return DAS3R_OK;
+}
+
+
+// ---- fused Adam step (include/das3r_adam.h) -----------------------------------------------------------------------
+int das3r_adam_step(int32_t n_tensors, const das3r_adam_tensor* tensors, double beta1, double beta2, double eps,
+                    int64_t step, void* stream_v) {
+    g_err.clear();
+    if (n_tensors < 0 || n_tensors > DAS3R_ADAM_MAX_TENSORS || (n_tensors > 0 && !tensors) || step < 1 ||
+        !(beta1 >= 0.0 && beta1 < 1.0) || !(beta2 >= 0.0 && beta2 < 1.0))
+        return fail_msg(DAS3R_EINVAL, "adam_step: invalid argument (at most 16 tensors, step >= 1, betas in [0,1))");
+    AdamArgs a;
+    memset(&a, 0, sizeof(a));
+    // bias corrections in double, like the Python floats of torch/optim/adam.py
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
+    a.b1w = (float)(1.0 - beta1);
+    a.beta2 = (float)beta2;
+    a.b2w = (float)(1.0 - beta2);
+    a.bc2_sqrt = (float)sqrt(bc2);
+    a.eps = (float)eps;
+    const int chunk = adam_chunk_elems();
+    int blocks = 0, k = 0;
+    for (int i = 0; i < n_tensors; i++) {
+        const das3r_adam_tensor& t = tensors[i];
+        if (t.n < 0) return fail_msg(DAS3R_EINVAL, "adam_step: negative element count");
+        if (t.n == 0) continue;
+        if (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq) return fail_msg(DAS3R_EINVAL, "adam_step: null buffer");
+        AdamTensor& o = a.t[k];
+        o.param = t.param; o.grad = t.grad; o.exp_avg = t.exp_avg; o.exp_avg_sq = t.exp_avg_sq; o.n = t.n;
+        o.step_size = (float)(t.lr / bc1);
+        o.vec4 = (((reinterpret_cast<uintptr_t>(t.param) | reinterpret_cast<uintptr_t>(t.grad) |
+                    reinterpret_cast<uintptr_t>(t.exp_avg) | reinterpret_cast<uintptr_t>(t.exp_avg_sq)) & 15) == 0) ? 1 : 0;
+        a.block_start[k] = blocks;
+        const int64_t nb = (t.n + chunk - 1) / chunk;
+        if (nb > (int64_t)0x7fffffff - blocks) return fail_msg(DAS3R_ELIMIT, "adam_step: too many elements for one launch");
+        blocks += (int)nb;
+        k++;
+    }
+    a.block_start[k] = blocks;
+    a.n_tensors = k;
+    cudaError_t e = launch_adam(a, blocks, static_cast<cudaStream_t>(stream_v));
+    if (blocks > 0) g_launches += 1;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "adam", e);
     return DAS3R_OK;
 }
 

@@ -107,6 +107,25 @@ cudaError_t launch_loss_fwd(const LossArgs& a, float* out, void* state, cudaStre
 cudaError_t launch_loss_bwd(const LossArgs& a, const void* state, const float* grad_loss, float* dL_dimage,
                             float* dL_dstatic, float* dL_dgt, cudaStream_t s);
 
+// Fused multi-tensor Adam (adam.cu, include/das3r_adam.h)
+constexpr int ADAM_MAX_TENSORS = 16;
+struct AdamTensor {
+    float* param;
+    const float* grad;
+    float *exp_avg, *exp_avg_sq;
+    int64_t n;
+    float step_size;  // lr / (1 - beta1^t)
+    int vec4;         // all four arrays 16-byte aligned
+};
+struct AdamArgs {
+    int n_tensors;
+    float b1w, beta2, b2w, bc2_sqrt, eps;  // 1-beta1, beta2, 1-beta2, sqrt(1-beta2^t), eps
+    int block_start[ADAM_MAX_TENSORS + 1];
+    AdamTensor t[ADAM_MAX_TENSORS];
+};
+int adam_chunk_elems();
+cudaError_t launch_adam(const AdamArgs& a, int total_blocks, cudaStream_t s);
+
 // forward.cu
 cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
 cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,

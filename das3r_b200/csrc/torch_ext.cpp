@@ -11,6 +11,7 @@
 #include "../../include/das3r_raster.h"
 #include "../../include/das3r_frontend.h"
 #include "../../include/das3r_loss.h"
+#include "../../include/das3r_adam.h"
 
 namespace {
 
@@ -658,6 +659,40 @@ static std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> LossBackwardCUDA(
     return std::make_tuple(dimg, dstatic, dgt);
 }
 
+// ---- fused Adam step (include/das3r_adam.h) -----------------------------------------------------------------------
+// params / grads / exp_avgs / exp_avg_sqs: parallel lists of contiguous float32 CUDA tensors; lrs: one per tensor.
+static void AdamStepCUDA(const std::vector<torch::Tensor>& params, const std::vector<torch::Tensor>& grads,
+                         const std::vector<torch::Tensor>& exp_avgs, const std::vector<torch::Tensor>& exp_avg_sqs,
+                         const std::vector<double>& lrs, double beta1, double beta2, double eps, int64_t step) {
+    const size_t n = params.size();
+    TORCH_CHECK(grads.size() == n && exp_avgs.size() == n && exp_avg_sqs.size() == n && lrs.size() == n,
+                "params, grads, exp_avgs, exp_avg_sqs and lrs must have the same length");
+    if (n == 0) return;
+    TORCH_CHECK(params[0].is_cuda(), "parameters must be CUDA tensors: the fused Adam has no CPU path");
+    const auto dev = params[0].device();
+    c10::cuda::CUDAGuard guard(dev);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    for (size_t i0 = 0; i0 < n; i0 += DAS3R_ADAM_MAX_TENSORS) {
+        das3r_adam_tensor t[DAS3R_ADAM_MAX_TENSORS];
+        const size_t m = std::min(n - i0, (size_t)DAS3R_ADAM_MAX_TENSORS);
+        for (size_t j = 0; j < m; j++) {
+            const size_t i = i0 + j;
+            for (const torch::Tensor* x : {&params[i], &grads[i], &exp_avgs[i], &exp_avg_sqs[i]})
+                TORCH_CHECK(x->is_cuda() && x->device() == dev && x->scalar_type() == torch::kFloat32 &&
+                                x->is_contiguous() && x->numel() == params[i].numel(),
+                            "tensor ", i, ": parameter, gradient and moments must be contiguous float32 CUDA tensors of "
+                            "one size on one device");
+            t[j].param = params[i].data_ptr<float>();
+            t[j].grad = grads[i].data_ptr<float>();
+            t[j].exp_avg = exp_avgs[i].data_ptr<float>();
+            t[j].exp_avg_sq = exp_avg_sqs[i].data_ptr<float>();
+            t[j].n = params[i].numel();
+            t[j].lr = lrs[i];
+        }
+        check(das3r_adam_step((int32_t)m, t, beta1, beta2, eps, step, stream), "adam_step");
+    }
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     // The GIL is released around every call into the library: a host that drives several CUDA streams from several
     // threads (bench.py) must not serialise on the forward's read-back of num_rendered.
@@ -671,6 +706,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("frontend_backward", &FrontendBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("loss_forward", &LossForwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("loss_backward", &LossBackwardCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("adam_step", &AdamStepCUDA);
     m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
     m.def("prof_collect", [](bool reset) {
         int n = das3r_prof_num_stages();

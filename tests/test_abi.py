@@ -27,6 +27,7 @@ def test_header_symbols_are_exported():
     assert "das3r_mark_visible" in names
     assert "das3r_frontend_forward" in names and "das3r_frontend_backward" in names
     assert "das3r_loss_forward" in names and "das3r_loss_backward" in names
+    assert "das3r_adam_step" in names
     assert "das3r_raster_backward_blend" in names and "das3r_raster_backward_finish" in names
     for n in names:
         assert hasattr(lib, n), f"{n} is declared in include/das3r_raster.h but not exported by libdas3r_raster.so"
