@@ -478,6 +478,9 @@ __device__ __forceinline__ void bitonic_sort_tile(uint64_t* sm, const uint64_t* 
 // at exactly the same depth), the block falls back to the bitonic network over the whole tile.
 // MAXE bounds the per-thread key count of the instantiation (registers / shared memory); MIN_N..512*MAXE is the size
 // class this launch handles, blocks of other classes exit at once.
+#ifndef DAS3R_SORT16_LOGNB
+#define DAS3R_SORT16_LOGNB 12
+#endif
 constexpr int LEAF_MAX = 128;
 constexpr int MED_CAP = 2048;  // buckets with more than 8 keys: at most 16384 / 9 of them
 
@@ -646,7 +649,15 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
         for (int q = warp; q < n_med; q += SORT_THREADS / 32) {
             const int b = s_med[q];
             const uint32_t s0 = s_off[b], m = s_cnt[b];
-            if (m > 8) {  // m <= LEAF_MAX is guaranteed by the flag test above
+            if (m > 8 && m <= 32) {
+                // the common medium bucket: one key per lane, one compare per key (ncu: with the four-slot loop below
+                // for every bucket, half of the kernel's instructions were these compares)
+                const uint64_t mine = ((uint32_t)lane < m) ? sm[s0 + lane] : ~0ull;
+                uint32_t rank = 0;
+                for (uint32_t j = 0; j < m; j++) rank += (sm[s0 + j] < mine) ? 1u : 0u;  // broadcast read
+                __syncwarp();
+                if ((uint32_t)lane < m) sm[s0 + rank] = mine;
+            } else if (m > 32) {  // m <= LEAF_MAX is guaranteed by the flag test above
                 uint64_t mine[LEAF_MAX / 32];
                 uint32_t rank[LEAF_MAX / 32];
 #pragma unroll
@@ -763,7 +774,7 @@ cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* rang
             if (c == 1 && !need32) break;
             e = cudaStreamWaitEvent(side[c], fork, 0);
             if (e != cudaSuccess) break;
-            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8, 12>(T, ranges, unsorted, rec, point_list, sA, sBC,
+            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8, DAS3R_SORT16_LOGNB>(T, ranges, unsorted, rec, point_list, sA, sBC,
                                                                              keys_sorted, side[c])
                          : launch_tile_sort_variant<32, SORT_THREADS * 16, 12>(T, ranges, unsorted, rec, point_list, sA,
                                                                               sBC, keys_sorted, side[c]);

@@ -15,6 +15,6 @@ while [ $# -ge 2 ]; do
   done
   wait
   /usr/local/cuda/bin/nvcc $ARCH -shared -o var/$name.so /tmp/var_build/${name}_forward.o /tmp/var_build/${name}_backward.o \
-      das3r_b200/build/api.o das3r_b200/build/knn.o -cudart static
+      $(ls das3r_b200/build/*.o | grep -v -e /forward.o -e /backward.o) -cudart static
   echo built var/$name.so
 done
