@@ -46,4 +46,4 @@ if __name__ == "__main__":
     make("small", H=40, W=56, seed=0, lam=0.2)
     make("odd_nostatic", H=37, W=51, seed=1, lam=0.2, with_static=False)
     make("tiny", H=7, W=9, seed=2, lam=0.5, grad_scale=3.0)     # smaller than the window: padding everywhere
-    make("frame", H=144, W=256, seed=3, lam=0.2)
+    make("frame", H=96, W=160, seed=3, lam=0.2)
