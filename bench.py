@@ -255,9 +255,20 @@ def main():
             g["scales"].add_(d_sc)
             g["rotations"].add_(d_rot)
 
-    def view_blend(pv):
-        """fwd + first half of the backward (backward blend) of one view; returns what the fused second half needs."""
-        R, color, radii, geom, binning, img = fwd(pv)
+    def preprocess_all():
+        """first half of the forward for all views of the step in one call (one kernel reads the shared SH rows once)"""
+        return C.rasterize_gaussians_forward_preprocess(
+            [(S["bg"], pv["means"], pv["rots"], S["view"], S["proj"], float(S["tanx"]), float(S["tany"]), H, W,
+              S["campos"]) for pv in pool], S["opac"], S["scales"], S["shs"], D, 1.0, False, False)
+
+    def view_blend(pv, pre_v, lane_stream=None):
+        """second half of the forward + first half of the backward (backward blend) of one view; returns what the fused
+        second half of the backward needs."""
+        color, radii, geom, img = pre_v
+        if lane_stream is not None:
+            for t in (color, radii, geom, img):
+                t.record_stream(lane_stream)
+        R, binning = C.rasterize_gaussians_forward_render(S["bg"], color, radii, geom, img, False)
         last_R[0] = R
         acc = C.rasterize_gaussians_backward_blend(S["bg"], dL, P, geom, R, binning, img, False)
         return (pv["means"], radii, S["scales"], pv["rots"], S["view"], S["proj"], float(S["tanx"]), float(S["tany"]),
@@ -280,7 +291,8 @@ def main():
             handles[b] = None
         if S_ == 1 or single_stream[0]:
             if fused_bwd:
-                finish([view_blend(pv) for pv in pool], buckets[b][0])
+                pre = preprocess_all()
+                finish([view_blend(pv, pre[j]) for j, pv in enumerate(pool)], buckets[b][0])
             else:
                 buckets[b][0].zero_()
                 for pv in pool:
@@ -289,6 +301,7 @@ def main():
             # one host thread per stream: the forward blocks its thread on the 16-byte read-back of num_rendered, the
             # other threads keep their streams fed meanwhile
             main = torch.cuda.current_stream()
+            pre = preprocess_all() if fused_bwd else None
             ev = torch.cuda.Event()
             ev.record(main)
             fviews = [None] * len(pool)
@@ -302,7 +315,7 @@ def main():
                         buckets[b][si].zero_()
                     for j in range(si, len(pool), S_):
                         if fused_bwd:
-                            fviews[j] = view_blend(pool[j])
+                            fviews[j] = view_blend(pool[j], pre[j], st)
                         else:
                             one_view(pool[j], buckets[b][si])
 

@@ -214,43 +214,48 @@ int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, in
     return DAS3R_OK;
 }
 
-int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_inputs* in,
-                         const das3r_raster_outputs* out, das3r_alloc_fn geom_alloc, void* geom_ctx,
-                         das3r_alloc_fn binning_alloc, void* binning_ctx, das3r_alloc_fn image_alloc, void* image_ctx,
-                         das3r_raster_state* state, void* stream_v) {
-    g_err.clear();
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
-    if (!check_params(params) || !in || !out || !state || !geom_alloc || !binning_alloc || !image_alloc)
-        return fail_msg(DAS3R_EINVAL, "forward: null or invalid argument");
-    if (!out->out_color || (params->P > 0 && !out->radii)) return fail_msg(DAS3R_EINVAL, "forward: null output");
+// ---- forward in two halves ----------------------------------------------------------------------------------------
+// Validation shared by every forward entry point. Returns DAS3R_OK, or 1 for the P == 0 early-out (image zeroed).
+static int forward_check(const char* who, const das3r_raster_params* params, const das3r_raster_inputs* in,
+                         const das3r_raster_outputs* out, das3r_raster_state* state, cudaStream_t stream) {
+    if (!check_params(params) || !in || !out || !state)
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": null or invalid argument");
+    if (!out->out_color || (params->P > 0 && !out->radii)) return fail_msg(DAS3R_EINVAL, std::string(who) + ": null output");
     const int P = params->P, W = params->width, H = params->height;
-    memset(state, 0, sizeof(*state));
     if (P == 0) {
-        // rasterize_points.cu:68,:81 — the image stays all-zero (no background) when there are no Gaussians
+        // rasterize_points.cu:68,:81 - the image stays all-zero (no background) when there are no Gaussians
+        memset(state, 0, sizeof(*state));
         cudaError_t e = cudaMemsetAsync(out->out_color, 0, (size_t)3 * W * H * 4, stream);
         if (e == cudaSuccess && out->out_depth) e = cudaMemsetAsync(out->out_depth, 0, (size_t)W * H * 4, stream);
         if (e == cudaSuccess && out->out_alpha) e = cudaMemsetAsync(out->out_alpha, 0, (size_t)W * H * 4, stream);
         if (e != cudaSuccess) return fail(DAS3R_ECUDA, "memset(out_color)", e);
-        return 0;
+        return 1;
     }
     if (!in->means3D || !in->opacities || !params->background || !params->viewmatrix || !params->projmatrix ||
         !params->campos)
-        return fail_msg(DAS3R_EINVAL, "forward: means3D/opacities/background/matrices/campos must be non-null");
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": means3D/opacities/background/matrices/campos must be non-null");
     if ((in->shs == nullptr) == (in->colors_precomp == nullptr))
-        return fail_msg(DAS3R_EINVAL, "forward: provide exactly one of shs / colors_precomp");
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": provide exactly one of shs / colors_precomp");
     const bool has_sr = in->scales != nullptr && in->rotations != nullptr;
     if (has_sr == (in->cov3D_precomp != nullptr) || ((in->scales != nullptr) != (in->rotations != nullptr)))
-        return fail_msg(DAS3R_EINVAL, "forward: provide exactly one of (scales, rotations) / cov3D_precomp");
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": provide exactly one of (scales, rotations) / cov3D_precomp");
     if (in->shs && (params->M < (params->D + 1) * (params->D + 1) || params->M > 16))
-        return fail_msg(DAS3R_EINVAL, "forward: M must satisfy (D+1)^2 <= M <= 16");
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": M must satisfy (D+1)^2 <= M <= 16");
+    return DAS3R_OK;
+}
 
+// Allocates the geom and image blobs of one view, clears its tile counters and fills the preprocess arguments.
+static int forward_begin(const das3r_raster_params* params, const das3r_raster_inputs* in, const das3r_raster_outputs* out,
+                         das3r_alloc_fn geom_alloc, void* geom_ctx, das3r_alloc_fn image_alloc, void* image_ctx,
+                         das3r_raster_state* state, cudaStream_t stream, PreFwdArgs* a_out) {
+    const int P = params->P, W = params->width, H = params->height;
+    memset(state, 0, sizeof(*state));
     const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     const int T = (int)(gx * gy);
     das3r_raster_state_layout L;
     memset(&L, 0, sizeof(L));
     geom_layout(P, &L);
     image_layout(W, H, &L);
-
     char* geom = geom_alloc(L.geom_bytes, geom_ctx);
     char* img = image_alloc(L.image_bytes, image_ctx);
     if (!geom || !img) return fail_msg(DAS3R_ENOMEM, "forward: allocator returned NULL");
@@ -258,19 +263,8 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     state->geom_bytes = L.geom_bytes;
     state->image = img;
     state->image_bytes = L.image_bytes;
-
-    GaussRec* rec = reinterpret_cast<GaussRec*>(geom + L.g_recA);
-    uint32_t* tiles_touched = reinterpret_cast<uint32_t*>(geom + L.g_tiles_touched);
-    uint8_t* clamped = reinterpret_cast<uint8_t*>(geom + L.g_clamped);
-    float* final_T = reinterpret_cast<float*>(img + L.i_final_T);
-    uint32_t* n_contrib = reinterpret_cast<uint32_t*>(img + L.i_n_contrib);
-    uint2* ranges = reinterpret_cast<uint2*>(img + L.i_ranges);
     uint32_t* tile_counts = reinterpret_cast<uint32_t*>(img + L.i_tile_counts);
-    uint32_t* cursors = reinterpret_cast<uint32_t*>(img + L.i_cursors);
-    uint32_t* totals = reinterpret_cast<uint32_t*>(img + L.i_totals);
-
     STAGE(cudaMemsetAsync(tile_counts, 0, (size_t)T * 4, stream), "memset(tile_counts)", ST_MEMSET, 0);
-
     PreFwdArgs a;
     memset(&a, 0, sizeof(a));
     a.P = P; a.D = params->D; a.M = params->M; a.W = W; a.H = H;
@@ -283,11 +277,48 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     a.means = in->means3D; a.shs = in->shs; a.colors_precomp = in->colors_precomp; a.opac = in->opacities;
     a.scales = in->scales; a.rots = in->rotations; a.cov3D_precomp = in->cov3D_precomp;
     a.view = params->viewmatrix; a.proj = params->projmatrix; a.campos = params->campos;
-    a.radii = out->radii; a.rec = rec; a.tiles_touched = tiles_touched; a.clamped = clamped;
+    a.radii = out->radii;
+    a.rec = reinterpret_cast<GaussRec*>(geom + L.g_recA);
+    a.tiles_touched = reinterpret_cast<uint32_t*>(geom + L.g_tiles_touched);
+    a.clamped = reinterpret_cast<uint8_t*>(geom + L.g_clamped);
     a.tile_counts = tile_counts;
-    static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
-    STAGE(launch_preprocess_fwd(a, stage_sh, stream), "preprocess_fwd", ST_PREPROCESS_FWD, 1);
-    STAGE(launch_tile_scan(tile_counts, T, ranges, cursors, totals, stream), "tile_scan", ST_TILE_SCAN, 1);
+    *a_out = a;
+    return DAS3R_OK;
+}
+
+static int forward_scan(const das3r_raster_params* params, const das3r_raster_state* state, cudaStream_t stream) {
+    const int W = params->width, H = params->height;
+    const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    das3r_raster_state_layout L;
+    memset(&L, 0, sizeof(L));
+    image_layout(W, H, &L);
+    char* img = state->image;
+    STAGE(launch_tile_scan(reinterpret_cast<uint32_t*>(img + L.i_tile_counts), T,
+                           reinterpret_cast<uint2*>(img + L.i_ranges), reinterpret_cast<uint32_t*>(img + L.i_cursors),
+                           reinterpret_cast<uint32_t*>(img + L.i_totals), stream),
+          "tile_scan", ST_TILE_SCAN, 1);
+    return DAS3R_OK;
+}
+
+// Second half: read back num_rendered, size the binning blob, scatter, per-tile sort, rect lists, blend.
+static int forward_finish(const das3r_raster_params* params, const das3r_raster_outputs* out, das3r_alloc_fn binning_alloc,
+                          void* binning_ctx, das3r_raster_state* state, cudaStream_t stream) {
+    const int P = params->P, W = params->width, H = params->height;
+    const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const int T = (int)(gx * gy);
+    das3r_raster_state_layout L;
+    memset(&L, 0, sizeof(L));
+    geom_layout(P, &L);
+    image_layout(W, H, &L);
+    char* geom = state->geom;
+    char* img = state->image;
+    GaussRec* rec = reinterpret_cast<GaussRec*>(geom + L.g_recA);
+    uint32_t* tiles_touched = reinterpret_cast<uint32_t*>(geom + L.g_tiles_touched);
+    float* final_T = reinterpret_cast<float*>(img + L.i_final_T);
+    uint32_t* n_contrib = reinterpret_cast<uint32_t*>(img + L.i_n_contrib);
+    uint2* ranges = reinterpret_cast<uint2*>(img + L.i_ranges);
+    uint32_t* cursors = reinterpret_cast<uint32_t*>(img + L.i_cursors);
+    uint32_t* totals = reinterpret_cast<uint32_t*>(img + L.i_totals);
 
     // The one host round trip of the forward (the reference has the same one, rasterizer_impl.cu:281).
     uint32_t host_totals[4] = {0, 0, 0, 0};
@@ -329,6 +360,96 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
                            out->out_depth, out->out_alpha, stream),
           "blend_fwd", ST_BLEND_FWD, 1);
     return R;
+}
+
+int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_inputs* in,
+                         const das3r_raster_outputs* out, das3r_alloc_fn geom_alloc, void* geom_ctx,
+                         das3r_alloc_fn binning_alloc, void* binning_ctx, das3r_alloc_fn image_alloc, void* image_ctx,
+                         das3r_raster_state* state, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!geom_alloc || !binning_alloc || !image_alloc) return fail_msg(DAS3R_EINVAL, "forward: null allocator");
+    int rc = forward_check("forward", params, in, out, state, stream);
+    if (rc != DAS3R_OK) return rc < 0 ? rc : 0;
+    PreFwdArgs a;
+    rc = forward_begin(params, in, out, geom_alloc, geom_ctx, image_alloc, image_ctx, state, stream, &a);
+    if (rc != DAS3R_OK) return rc;
+    static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
+    STAGE(launch_preprocess_fwd(a, stage_sh, stream), "preprocess_fwd", ST_PREPROCESS_FWD, 1);
+    rc = forward_scan(params, state, stream);
+    if (rc != DAS3R_OK) return rc;
+    return forward_finish(params, out, binning_alloc, binning_ctx, state, stream);
+}
+
+int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view* views, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (n_views < 1 || !views) return fail_msg(DAS3R_EINVAL, "forward_preprocess: null or invalid argument");
+    std::vector<PreFwdArgs> args((size_t)n_views);
+    std::vector<char> live((size_t)n_views, 0);
+    const das3r_raster_params* params = nullptr;  // for the STAGE macro
+    for (int v = 0; v < n_views; v++) {
+        const das3r_raster_fwd_view& V = views[v];
+        if (!V.geom_alloc || !V.image_alloc) return fail_msg(DAS3R_EINVAL, "forward_preprocess: null allocator");
+        int rc = forward_check("forward_preprocess", V.params, V.in, V.out, V.state, stream);
+        if (rc < 0) return rc;
+        if (rc == 1) continue;  // P == 0: nothing to preprocess
+        rc = forward_begin(V.params, V.in, V.out, V.geom_alloc, V.geom_ctx, V.image_alloc, V.image_ctx, V.state, stream,
+                           &args[v]);
+        if (rc != DAS3R_OK) return rc;
+        live[v] = 1;
+        params = V.params;
+    }
+    if (!params) return DAS3R_OK;
+    static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
+    // Views that can share one pass: same SH rows (degree 3, 16 coefficients, aligned), same P and image size.
+    auto fusable = [&](int v) {
+        const PreFwdArgs& a = args[v];
+        return live[v] && stage_sh && a.shs && !a.colors_precomp && a.D == 3 && a.M == 16 &&
+               ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+    };
+    std::vector<char> done((size_t)n_views, 0);
+    for (int v0 = 0; v0 < n_views; v0++) {
+        if (!live[v0] || done[v0]) continue;
+        if (!fusable(v0)) {
+            params = views[v0].params;
+            STAGE(launch_preprocess_fwd(args[v0], stage_sh, stream), "preprocess_fwd", ST_PREPROCESS_FWD, 1);
+            done[v0] = 1;
+            continue;
+        }
+        MultiFwdArgs m;
+        memset(&m, 0, sizeof(m));
+        m.T = (int)(args[v0].gx * args[v0].gy);
+        for (int v = v0; v < n_views && m.n_views < MF_MAX_VIEWS; v++) {
+            if (done[v] || !fusable(v)) continue;
+            const PreFwdArgs& a = args[v];
+            if (a.shs != args[v0].shs || a.P != args[v0].P || a.W != args[v0].W || a.H != args[v0].H) continue;
+            m.v[m.n_views++] = a;
+            done[v] = 1;
+        }
+        params = views[v0].params;
+        if (m.n_views == 1)
+            STAGE(launch_preprocess_fwd(m.v[0], stage_sh, stream), "preprocess_fwd", ST_PREPROCESS_FWD, 1);
+        else
+            STAGE(launch_preprocess_fwd_multi(m, stream), "preprocess_fwd_multi", ST_PREPROCESS_FWD, 1);
+    }
+    for (int v = 0; v < n_views; v++)
+        if (live[v]) {
+            int rc = forward_scan(views[v].params, views[v].state, stream);
+            if (rc != DAS3R_OK) return rc;
+        }
+    return DAS3R_OK;
+}
+
+int das3r_raster_forward_render(const das3r_raster_fwd_view* view, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!view || !check_params(view->params) || !view->out || !view->state || !view->binning_alloc)
+        return fail_msg(DAS3R_EINVAL, "forward_render: null or invalid argument");
+    if (view->params->P == 0) return 0;  // the preprocess half has zeroed the image
+    if (!view->state->geom || !view->state->image || !view->out->out_color || !view->out->radii)
+        return fail_msg(DAS3R_EINVAL, "forward_render: the view has not been through das3r_raster_forward_preprocess");
+    return forward_finish(view->params, view->out, view->binning_alloc, view->binning_ctx, view->state, stream);
 }
 
 size_t das3r_raster_backward_scratch_bytes(int32_t P) {

@@ -39,7 +39,11 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* f, float3 pos,
     dir.z = dir.z / len;
     float res[3];
 #pragma unroll
-    for (int c = 0; c < 3; c++) res[c] = kSH0 * f[c];
+    for (int c = 0; c < 3; c++) res[c] = __fmul_rn(kSH0, f[c]);  // rounded product, as in the reference's build: left to
+                                                                  // the compiler, this multiply or the next one gets
+                                                                  // fused into the subtraction below depending on the
+                                                                  // surrounding kernel (seen in SASS: one-view vs
+                                                                  // multi-view), a 1-ulp difference in the colour
     if (deg > 0) {
         float x = dir.x, y = dir.y, z = dir.z;
 #pragma unroll
@@ -78,35 +82,20 @@ constexpr int SH_ROW_PAD_F4 = 13;  // padded row pitch in shared memory: 13 floa
 // preprocess_fwd. STAGE_SH: the block's 256 degree-3 SH rows (48 KB contiguous) are brought into shared memory with
 // coalesced 16-byte cp.async while the geometry is computed, then read back row-wise without bank conflicts.
 // ---------------------------------------------------------------------------------------------------------------
-template <bool STAGE_SH>
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFwdArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4* sh_stage = reinterpret_cast<float4*>(smem_raw);
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + (STAGE_SH ? PRE_THREADS * SH_ROW_PAD_F4 * 16 : 0));
+// What the geometry half of the preprocess leaves for the colour / record half.
+struct PreGeom {
+    bool vis;
+    float my_radius;
+    uint2 rmin, rmax;
+    float2 point_image;
+    float3 p_orig, conic;
+    float depth, opacity, hrad, negtau;
+};
 
-    const int tid = threadIdx.x;
-    const int base = blockIdx.x * PRE_THREADS;
-    const int idx = base + tid;
-    const int T = (int)(a.gx * a.gy);
-
-    if (a.smem_hist)
-        for (int i = tid; i < T; i += PRE_THREADS) hist[i] = 0;
-
-    if (STAGE_SH) {
-        const int nvalid = min(PRE_THREADS, a.P - base);
-        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)base * SH_ROW_F4;
-        const int total = nvalid * SH_ROW_F4;
-#pragma unroll
-        for (int k = 0; k < SH_ROW_F4; k++) {
-            int e = tid + k * PRE_THREADS;
-            if (e < total) {
-                int g = e / SH_ROW_F4, j = e - g * SH_ROW_F4;
-                cp_async_16(&sh_stage[g * SH_ROW_PAD_F4 + j], src + e);
-            }
-        }
-        cp_async_commit();
-    }
-
+// Geometry half of preprocessCUDA (forward.cu:182-237) for Gaussian idx of one view: near cull, projection, EWA
+// covariance, conic, radius, tile rectangle, and the culling radius / threshold of the blend. Shared by the one-view and
+// the multi-view kernel (same code, same rounding).
+__device__ __forceinline__ PreGeom pre_geometry(const PreFwdArgs& a, const int idx) {
     bool vis = false;
     float my_radius = 0.f;
     uint2 rmin = {0, 0}, rmax = {0, 0};
@@ -179,14 +168,22 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
         }
     }
 
-    if (STAGE_SH) cp_async_wait_all();
-    __syncthreads();
+    PreGeom g;
+    g.vis = vis; g.my_radius = my_radius; g.rmin = rmin; g.rmax = rmax; g.point_image = point_image;
+    g.p_orig = p_orig; g.conic = conic; g.depth = depth; g.opacity = opacity; g.hrad = hrad; g.negtau = negtau;
+    return g;
+}
 
+// Colour / record half: radii and tile count, SH -> RGB (the row comes from shared memory when STAGE_SH), the 48-byte
+// record, clamp bits, tile histogram (forward.cu:239-255).
+template <bool STAGE_SH>
+__device__ __forceinline__ void pre_finish(const PreFwdArgs& a, const int idx, const PreGeom& g,
+                                           const float4* __restrict__ sh_row, uint32_t* __restrict__ hist) {
     if (idx < a.P) {
-        a.radii[idx] = vis ? (int)my_radius : 0;
-        a.tiles_touched[idx] = vis ? (rmax.y - rmin.y) * (rmax.x - rmin.x) : 0u;
+        a.radii[idx] = g.vis ? (int)g.my_radius : 0;
+        a.tiles_touched[idx] = g.vis ? (g.rmax.y - g.rmin.y) * (g.rmax.x - g.rmin.x) : 0u;
     }
-    if (vis) {
+    if (g.vis) {
         float3 rgb;
         uint8_t cl = 0;
         if (a.colors_precomp == nullptr) {
@@ -194,7 +191,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
             if (STAGE_SH) {
 #pragma unroll
                 for (int j = 0; j < SH_ROW_F4; j++) {
-                    float4 v = sh_stage[tid * SH_ROW_PAD_F4 + j];
+                    float4 v = sh_row[j];
                     f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
                 }
             } else {
@@ -203,25 +200,62 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
                 load_sh_row(row, a.D, aligned, f);
             }
             float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
-            rgb = sh_to_rgb(a.D, f, p_orig, cam, cl);
+            rgb = sh_to_rgb(a.D, f, g.p_orig, cam, cl);
         } else {
             rgb = {a.colors_precomp[3 * idx], a.colors_precomp[3 * idx + 1], a.colors_precomp[3 * idx + 2]};
         }
         GaussRec r;
-        r.A = make_float4(point_image.x, point_image.y, hrad, negtau);
-        r.B = make_float4(conic.x, conic.y, conic.z, opacity);
-        r.C = make_float4(rgb.x, rgb.y, rgb.z, depth);
+        r.A = make_float4(g.point_image.x, g.point_image.y, g.hrad, g.negtau);
+        r.B = make_float4(g.conic.x, g.conic.y, g.conic.z, g.opacity);
+        r.C = make_float4(rgb.x, rgb.y, rgb.z, g.depth);
         a.rec[idx] = r;
         a.clamped[idx] = cl;
         // Tile histogram (this replaces the prefix sum over all P Gaussians of the reference).
-        for (unsigned y = rmin.y; y < rmax.y; y++)
-            for (unsigned x = rmin.x; x < rmax.x; x++) {
+        for (unsigned y = g.rmin.y; y < g.rmax.y; y++)
+            for (unsigned x = g.rmin.x; x < g.rmax.x; x++) {
                 if (a.smem_hist)
                     atomicAdd(&hist[y * a.gx + x], 1u);
                 else
                     atomicAdd(&a.tile_counts[y * a.gx + x], 1u);
             }
     }
+}
+
+template <bool STAGE_SH>
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFwdArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* sh_stage = reinterpret_cast<float4*>(smem_raw);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + (STAGE_SH ? PRE_THREADS * SH_ROW_PAD_F4 * 16 : 0));
+
+    const int tid = threadIdx.x;
+    const int base = blockIdx.x * PRE_THREADS;
+    const int idx = base + tid;
+    const int T = (int)(a.gx * a.gy);
+
+    if (a.smem_hist)
+        for (int i = tid; i < T; i += PRE_THREADS) hist[i] = 0;
+
+    if (STAGE_SH) {
+        const int nvalid = min(PRE_THREADS, a.P - base);
+        const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)base * SH_ROW_F4;
+        const int total = nvalid * SH_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < SH_ROW_F4; k++) {
+            int e = tid + k * PRE_THREADS;
+            if (e < total) {
+                int g = e / SH_ROW_F4, j = e - g * SH_ROW_F4;
+                cp_async_16(&sh_stage[g * SH_ROW_PAD_F4 + j], src + e);
+            }
+        }
+        cp_async_commit();
+    }
+
+    PreGeom g = pre_geometry(a, idx);
+
+    if (STAGE_SH) cp_async_wait_all();
+    __syncthreads();
+
+    pre_finish<STAGE_SH>(a, idx, g, sh_stage + tid * SH_ROW_PAD_F4, hist);
     if (a.smem_hist) {
         __syncthreads();
         for (int i = tid; i < T; i += PRE_THREADS) {
@@ -229,6 +263,64 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
             if (v) atomicAdd(&a.tile_counts[i], v);
         }
     }
+}
+
+// preprocess_fwd for SEVERAL views that share their SH rows (degree 3): the block's 256 rows are staged once, every
+// thread then runs the geometry and colour halves for each view with the row in registers - the 192 bytes of SH per
+// Gaussian, two thirds of the kernel's traffic, are read once per step instead of once per view. Same device functions
+// as the one-view kernel, so every output is bit-identical to it (tests/test_gpu_multiview.py).
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_multi_kernel(const __grid_constant__ MultiFwdArgs m) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* sh_stage = reinterpret_cast<float4*>(smem_raw);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + PRE_THREADS * SH_ROW_PAD_F4 * 16);
+    const int tid = threadIdx.x;
+    const int base = blockIdx.x * PRE_THREADS;
+    const int idx = base + tid;
+    const int P = m.v[0].P, T = m.T;
+    if (m.smem_hist)
+        for (int i = tid; i < T * m.n_views; i += PRE_THREADS) hist[i] = 0;
+    {
+        const int nvalid = min(PRE_THREADS, P - base);
+        const float4* src = reinterpret_cast<const float4*>(m.v[0].shs) + (size_t)base * SH_ROW_F4;
+        const int total = nvalid * SH_ROW_F4;
+#pragma unroll
+        for (int k = 0; k < SH_ROW_F4; k++) {
+            int e = tid + k * PRE_THREADS;
+            if (e < total) {
+                int g = e / SH_ROW_F4, j = e - g * SH_ROW_F4;
+                cp_async_16(&sh_stage[g * SH_ROW_PAD_F4 + j], src + e);
+            }
+        }
+        cp_async_commit();
+    }
+    cp_async_wait_all();
+    __syncthreads();
+#pragma unroll 1
+    for (int v = 0; v < m.n_views; v++) {
+        const PreFwdArgs& a = m.v[v];
+        const PreGeom g = pre_geometry(a, idx);
+        pre_finish<true>(a, idx, g, sh_stage + tid * SH_ROW_PAD_F4, hist + (size_t)v * T);
+    }
+    if (m.smem_hist) {
+        __syncthreads();
+        for (int i = tid; i < T * m.n_views; i += PRE_THREADS) {
+            const uint32_t c = hist[i];
+            if (c) atomicAdd(&m.v[i / T].tile_counts[i % T], c);
+        }
+    }
+}
+
+cudaError_t launch_preprocess_fwd_multi(const MultiFwdArgs& m_in, cudaStream_t s) {
+    MultiFwdArgs m = m_in;
+    const size_t hist_bytes = (size_t)m.T * m.n_views * 4;
+    m.smem_hist = hist_bytes <= 96 * 1024 ? 1 : 0;
+    for (int v = 0; v < m.n_views; v++) m.v[v].smem_hist = m.smem_hist;
+    const size_t smem = (size_t)PRE_THREADS * SH_ROW_PAD_F4 * 16 + (m.smem_hist ? hist_bytes : 0);
+    cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int blocks = (m.v[0].P + PRE_THREADS - 1) / PRE_THREADS;
+    preprocess_fwd_multi_kernel<<<blocks, PRE_THREADS, smem, s>>>(m);
+    return cudaGetLastError();
 }
 
 constexpr int SMEM_HIST_MAX_TILES = 8192;

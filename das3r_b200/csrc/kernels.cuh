@@ -42,6 +42,12 @@ struct PreFwdArgs {
     int smem_hist;  // 1: per-block shared-memory histogram of tile counts, 0: direct global atomics
 };
 
+constexpr int MF_MAX_VIEWS = 16;
+struct MultiFwdArgs {  // views that share shs (degree 3, M == 16) and the image size
+    int n_views, T, smem_hist, pad_;
+    PreFwdArgs v[MF_MAX_VIEWS];
+};
+
 struct PreBwdArgs {
     int P, D, M, W, H;
     float tan_fovx, tan_fovy, focal_x, focal_y, scale_mod;
@@ -128,6 +134,7 @@ cudaError_t launch_adam(const AdamArgs& a, int total_blocks, cudaStream_t s);
 
 // forward.cu
 cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
+cudaError_t launch_preprocess_fwd_multi(const MultiFwdArgs& m, cudaStream_t s);
 cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,
                              cudaStream_t s);
 cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,

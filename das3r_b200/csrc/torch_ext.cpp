@@ -332,6 +332,116 @@ torch::Tensor distCUDA2(const torch::Tensor& points_) {
 
 }  // namespace
 
+// ---- split / multi-view forward (das3r_raster_forward_preprocess / _render; no reference counterpart) ------------
+// (bg, means3D, rotations, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos) per view
+using FwdView = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, float, float, int,
+                           int, torch::Tensor>;
+
+// First half for all views: -> per view (color, radii, geomBuffer, imgBuffer). SH colours + scale/rotation inputs only.
+static std::vector<std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>> ForwardPreprocessCUDA(
+    const std::vector<FwdView>& views, const torch::Tensor& opacity_, const torch::Tensor& scales_,
+    const torch::Tensor& sh_, const int degree, const float scale_modifier, const bool prefiltered, const bool debug) {
+    TORCH_CHECK(!views.empty(), "no views");
+    TORCH_CHECK(opacity_.is_cuda(), "opacities must be a CUDA tensor: this rasterizer has no CPU path");
+    const auto dev = opacity_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    auto opacity = prep(opacity_, "opacities", dev);
+    auto scales = prep(scales_, "scales", dev);
+    auto sh = prep(sh_, "shs", dev);
+    TORCH_CHECK(sh_.dim() == 3, "shs must be [P,M,3]");
+    const int P = opacity_.size(0), M = sh_.size(1);
+    const size_t n = views.size();
+    std::vector<das3r_raster_params> ps(n);
+    std::vector<das3r_raster_inputs> ins(n);
+    std::vector<das3r_raster_outputs> outs(n);
+    std::vector<das3r_raster_state> sts(n);
+    std::vector<das3r_raster_fwd_view> vs(n);
+    std::vector<BlobAlloc> geomA(n), imgA(n);
+    std::vector<torch::Tensor> keep, colors(n), radii(n);
+    auto fo = opacity.options();
+    for (size_t i = 0; i < n; i++) {
+        const auto& V = views[i];
+        TORCH_CHECK(std::get<1>(V).dim() == 2 && std::get<1>(V).size(0) == P && std::get<1>(V).size(1) == 3,
+                    "means3D must have dimensions (num_points, 3) with one row per opacity");
+        auto bg = prep(std::get<0>(V), "bg", dev);
+        auto means3D = prep(std::get<1>(V), "means3D", dev);
+        auto rotations = prep(std::get<2>(V), "rotations", dev);
+        auto view = prep(std::get<3>(V), "viewmatrix", dev);
+        auto proj = prep(std::get<4>(V), "projmatrix", dev);
+        auto campos = prep(std::get<9>(V), "campos", dev);
+        for (const auto& t : {bg, means3D, rotations, view, proj, campos}) keep.push_back(t);
+        const int H = std::get<7>(V), W = std::get<8>(V);
+        colors[i] = torch::empty({3, H, W}, fo);
+        radii[i] = torch::empty({P}, fo.dtype(torch::kInt32));
+        geomA[i].opts = torch::TensorOptions().dtype(torch::kByte).device(dev);
+        imgA[i].opts = geomA[i].opts;
+        memset(&ps[i], 0, sizeof(ps[i]));
+        ps[i].P = P; ps[i].D = degree; ps[i].M = M; ps[i].width = W; ps[i].height = H;
+        ps[i].tan_fovx = std::get<5>(V); ps[i].tan_fovy = std::get<6>(V);
+        ps[i].scale_modifier = scale_modifier; ps[i].prefiltered = prefiltered; ps[i].debug = debug;
+        ps[i].background = fptr(bg); ps[i].viewmatrix = fptr(view); ps[i].projmatrix = fptr(proj);
+        ps[i].campos = fptr(campos);
+        memset(&ins[i], 0, sizeof(ins[i]));
+        ins[i].means3D = fptr(means3D); ins[i].shs = fptr(sh); ins[i].opacities = fptr(opacity);
+        ins[i].scales = fptr(scales); ins[i].rotations = fptr(rotations);
+        memset(&outs[i], 0, sizeof(outs[i]));
+        outs[i].out_color = colors[i].data_ptr<float>();
+        outs[i].radii = radii[i].data_ptr<int>();
+        memset(&vs[i], 0, sizeof(vs[i]));
+        vs[i].params = &ps[i]; vs[i].in = &ins[i]; vs[i].out = &outs[i]; vs[i].state = &sts[i];
+        vs[i].geom_alloc = &BlobAlloc::fn; vs[i].geom_ctx = &geomA[i];
+        vs[i].image_alloc = &BlobAlloc::fn; vs[i].image_ctx = &imgA[i];
+    }
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    check(das3r_raster_forward_preprocess((int32_t)n, vs.data(), stream), "rasterize_gaussians_forward_preprocess");
+    std::vector<std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>> res;
+    auto bo = torch::TensorOptions().dtype(torch::kByte).device(dev);
+    for (size_t i = 0; i < n; i++) {
+        if (!geomA[i].t.defined()) geomA[i].t = torch::empty({0}, bo);
+        if (!imgA[i].t.defined()) imgA[i].t = torch::empty({0}, bo);
+        res.emplace_back(colors[i], radii[i], geomA[i].t, imgA[i].t);
+    }
+    return res;
+}
+
+// Second half for one view (current stream): -> (num_rendered, binningBuffer). color / radii are completed in place.
+static std::tuple<int, torch::Tensor> ForwardRenderCUDA(const torch::Tensor& background, const torch::Tensor& color,
+                                                        const torch::Tensor& radii, const torch::Tensor& geomBuffer,
+                                                        const torch::Tensor& imgBuffer, const bool debug) {
+    TORCH_CHECK(color.is_cuda() && color.dim() == 3, "color must be the [3,H,W] tensor forward_preprocess returned");
+    const auto dev = color.device();
+    c10::cuda::CUDAGuard guard(dev);
+    auto bg = prep(background, "bg", dev);
+    das3r_raster_params p;
+    memset(&p, 0, sizeof(p));
+    p.P = (int32_t)radii.size(0);
+    p.height = (int32_t)color.size(1);
+    p.width = (int32_t)color.size(2);
+    p.debug = debug;
+    p.background = fptr(bg);
+    das3r_raster_outputs out;
+    memset(&out, 0, sizeof(out));
+    out.out_color = color.data_ptr<float>();
+    out.radii = radii.data_ptr<int>();
+    das3r_raster_state st;
+    memset(&st, 0, sizeof(st));
+    st.geom = geomBuffer.numel() ? reinterpret_cast<char*>(geomBuffer.data_ptr()) : nullptr;
+    st.geom_bytes = geomBuffer.numel();
+    st.image = imgBuffer.numel() ? reinterpret_cast<char*>(imgBuffer.data_ptr()) : nullptr;
+    st.image_bytes = imgBuffer.numel();
+    BlobAlloc binA;
+    binA.opts = torch::TensorOptions().dtype(torch::kByte).device(dev);
+    das3r_raster_fwd_view v;
+    memset(&v, 0, sizeof(v));
+    v.params = &p; v.out = &out; v.state = &st;
+    v.binning_alloc = &BlobAlloc::fn; v.binning_ctx = &binA;
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    const int R = das3r_raster_forward_render(&v, stream);
+    check(R, "rasterize_gaussians_forward_render");
+    if (!binA.t.defined()) binA.t = torch::empty({0}, binA.opts);
+    return std::make_tuple(R, binA.t);
+}
+
 // ---- split / multi-view backward (das3r_raster_backward_blend / _finish; no reference counterpart) --------------
 // First half for one view: returns the [P,12] float32 accumulator tensor the finish half reads.
 static torch::Tensor BackwardBlendCUDA(const torch::Tensor& background, const torch::Tensor& dL_dout_color_, const int P,
@@ -700,6 +810,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians_ex", &RasterizeGaussiansExCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardIntoCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_forward_preprocess", &ForwardPreprocessCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_forward_render", &ForwardRenderCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_blend", &BackwardBlendCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_finish", &BackwardFinishCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("frontend_forward", &FrontendForwardCUDA, py::call_guard<py::gil_scoped_release>());

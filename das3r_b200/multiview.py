@@ -76,13 +76,24 @@ class _RasterizeViews(torch.autograd.Function):
         rots = mr[1::2]
         main = torch.cuda.current_stream(opacities.device)
 
+        # first half for all views at once on the caller's stream: views that share the SH rows are preprocessed by one
+        # kernel that reads them once (das3r_raster_forward_preprocess)
+        rs0 = settings[0]
+        pre = _C.rasterize_gaussians_forward_preprocess(
+            [(rs.bg, means[i], rots[i], rs.viewmatrix, rs.projmatrix, float(rs.tanfovx), float(rs.tanfovy),
+              int(rs.image_height), int(rs.image_width), rs.campos) for i, rs in enumerate(settings)],
+            opacities, scales, shs, rs0.sh_degree, float(rs0.scale_modifier), bool(rs0.prefiltered), bool(rs0.debug))
+
         def fwd(i):
-            rs = settings[i]
-            out = _C.rasterize_gaussians(rs.bg, means[i], _EMPTY, opacities, scales, rots[i], rs.scale_modifier, _EMPTY,
-                                         rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
-                                         rs.image_width, shs, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
-            _crosses_to(main, out[1], out[2], out[3])  # colour, radii, geom blob are read on the caller's stream
-            return out
+            # second half per view on its lane: read-back of num_rendered, binning, sort, rect lists, blend
+            color, radii, geom, img = pre[i]
+            lane_stream = torch.cuda.current_stream(opacities.device)
+            for t in (color, radii, geom, img):  # allocated on the caller's stream, used on this lane
+                if t.numel():
+                    t.record_stream(lane_stream)
+            R, binning = _C.rasterize_gaussians_forward_render(settings[i].bg, color, radii, geom, img,
+                                                               bool(settings[i].debug))
+            return (R, color, radii, geom, binning, img)
 
         res = lanes.run(n, fwd)
         ctx.settings, ctx.lanes, ctx.n = settings, lanes, n
@@ -170,9 +181,9 @@ class MultiViewRasterizer:
         if shs is None or shs.dim() != 3 or scales is None:
             raise Exception("MultiViewRasterizer takes SH colours and scale/rotation inputs; use GaussianRasterizer "
                             "for precomputed colours or covariances")
-        if any(rs.sh_degree != settings[0].sh_degree or rs.scale_modifier != settings[0].scale_modifier
-               for rs in settings):
-            raise ValueError("all views must use the same sh_degree and scale_modifier")
+        if any(rs.sh_degree != settings[0].sh_degree or rs.scale_modifier != settings[0].scale_modifier or
+               rs.prefiltered != settings[0].prefiltered or rs.debug != settings[0].debug for rs in settings):
+            raise ValueError("all views must use the same sh_degree, scale_modifier, prefiltered and debug flags")
         mr = []
         for m, r in zip(means3D, rotations):
             mr += [m, r]

@@ -121,6 +121,36 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
                          das3r_alloc_fn image_alloc, void* image_ctx,
                          das3r_raster_state* state, void* stream);
 
+/* The forward in two halves, for hosts that render several views of the same Gaussians per step (a data-parallel
+ * training step, render.py's frame loop). No counterpart in the reference, whose Rasterizer::forward
+ * (rasterizer_impl.cu:198-336) handles one view per call.
+ *
+ *   das3r_raster_forward_preprocess(n, views, stream)   first half for n >= 1 views at once (replaces preprocessCUDA,
+ *                                                       forward.cu:155-256, and the prefix sum, rasterizer_impl.cu:277):
+ *                                                       allocates every view's geom and image blobs through its
+ *                                                       callbacks, projects the Gaussians, counts tile instances,
+ *                                                       builds the tile ranges. Views that share their `shs` array
+ *                                                       (degree 3, 16 coefficients), P and the image size are handled
+ *                                                       by ONE kernel that reads every SH row once - two thirds of the
+ *                                                       traffic of this stage; other views get the one-view kernel.
+ *                                                       Every output is bit-identical to das3r_raster_forward's.
+ *   das3r_raster_forward_render(view, stream_v)         second half for ONE view, on any stream ordered after the
+ *                                                       first half: reads back num_rendered (blocks the host like
+ *                                                       das3r_raster_forward), then binning, per-tile sort, rect lists,
+ *                                                       blend. Returns num_rendered or a negative code.
+ * das3r_raster_forward(...) == preprocess(1 view) + render. */
+typedef struct das3r_raster_fwd_view {
+    const das3r_raster_params* params;
+    const das3r_raster_inputs* in;
+    const das3r_raster_outputs* out;
+    das3r_alloc_fn geom_alloc;    void* geom_ctx;
+    das3r_alloc_fn binning_alloc; void* binning_ctx;
+    das3r_alloc_fn image_alloc;   void* image_ctx;
+    das3r_raster_state* state;    /* filled by the two halves */
+} das3r_raster_fwd_view;
+int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view* views, void* stream);
+int das3r_raster_forward_render(const das3r_raster_fwd_view* view, void* stream);
+
 /* Backward. Replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:55-84, rasterizer_impl.cu:340-434):
  * backward blend -> cov2D/projection/SH/cov3D gradients. `radii` is the forward's output. `dL_dpix` is [3,H,W]. */
 int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in,

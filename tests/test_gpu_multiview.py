@@ -204,3 +204,32 @@ def test_multiview_rasterizer_matches_the_per_view_module(D):
     for v, ((ma, ra), (mb, rb)) in enumerate(zip(per_a, per_b)):
         assert Hn.rel_err(mb.grad, ma.grad) <= Hn.GRAD_RTOL, f"means3D of view {v}"
         assert Hn.rel_err(rb.grad, ra.grad) <= Hn.GRAD_RTOL, f"rotations of view {v}"
+
+
+@pytest.mark.parametrize("D,V", [(3, 5), (1, 2), (3, 18)])
+def test_forward_split_is_bit_identical_to_the_one_call_forward(D, V):
+    """das3r_raster_forward_preprocess (all views in one call: one kernel when they share degree-3 SH rows, the one-view
+    kernel otherwise, chunks of 16) + das3r_raster_forward_render per view against das3r_raster_forward: image, radii,
+    num_rendered and the whole geometry blob byte for byte."""
+    dev = torch.device("cuda:0")
+    C = load_native()
+    P, W, H = 30_000, 176, 112
+    views, _ = _scene_views(P, V, W, H, D, seed=40 + D, dev=dev)
+    want = [_forward(C, vi, D) for vi in views]
+    pre = C.rasterize_gaussians_forward_preprocess(
+        [(vi["bg"], vi["means3D"], vi["rotations"], vi["viewmatrix"], vi["projmatrix"], float(vi["tanfovx"]),
+          float(vi["tanfovy"]), H, W, vi["campos"]) for vi in views], views[0]["opacities"], views[0]["scales"],
+        views[0]["shs"], D, 1.0, False, False)
+    for vi, (color, radii, geom, img), w in zip(views, pre, want):
+        R, binning = C.rasterize_gaussians_forward_render(vi["bg"], color, radii, geom, img, False)
+        torch.cuda.synchronize()
+        assert R == w[0]
+        assert torch.equal(color, w[1]) and torch.equal(radii, w[2])
+        L = Hn.layout(P, W, H, R)
+        vis = radii > 0  # records and clamp bits of Gaussians that are not rendered are never written
+        rec = lambda g: g[L.g_recA:L.g_recA + 48 * P].view(torch.int32).view(P, 12)[vis]
+        assert torch.equal(rec(geom), rec(w[3]))
+        tiles = lambda g: g[L.g_tiles_touched:L.g_tiles_touched + 4 * P].view(torch.int32)
+        assert torch.equal(tiles(geom), tiles(w[3]))
+        clamp = lambda g: g[L.g_clamped:L.g_clamped + P][vis]
+        assert torch.equal(clamp(geom), clamp(w[3]))
