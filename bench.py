@@ -302,6 +302,7 @@ def main():
             # other threads keep their streams fed meanwhile
             main = torch.cuda.current_stream()
             pre = preprocess_all() if fused_bwd else None
+            launch_pending_reduce()  # ordered after this step's preprocess pass: it then runs under the blend kernels
             ev = torch.cuda.Event()
             ev.record(main)
             fviews = [None] * len(pool)
@@ -333,9 +334,22 @@ def main():
                 for si in range(1, S_):
                     buckets[b][0].flat.add_(buckets[b][si].flat)
         if world > 1:
-            handles[b] = buckets[b][0].all_reduce(async_op=True)
+            # The all-reduce of this step's bucket is not started here but after the NEXT step's preprocess pass (or in
+            # drain()): started right away it shares HBM with that bandwidth-bound pass; a little later it overlaps
+            # the issue-bound blend kernels, which leave the memory system idle.
+            launch_pending_reduce()
+            pending[0] = b
+
+    pending = [None]
+
+    def launch_pending_reduce():
+        if world > 1 and pending[0] is not None:
+            pb = pending[0]
+            pending[0] = None
+            handles[pb] = buckets[pb][0].all_reduce(async_op=True)
 
     def drain():
+        launch_pending_reduce()
         for b in range(len(handles)):
             if handles[b] is not None:
                 handles[b].wait()
