@@ -55,6 +55,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-views", type=int, default=4, help="views timed for the CPU baseline sample")
+    ap.add_argument("--eager-allreduce", action="store_true",
+                    help="start a step's gradient all-reduce right after its backward instead of after the next "
+                         "step's preprocess pass")
     ap.add_argument("--per-view-backward", action="store_true",
                     help="sum the views with the per-view accumulating backward instead of the fused multi-view pass")
     ap.add_argument("--streams", type=int, default=3,
@@ -339,6 +342,8 @@ def main():
             # the issue-bound blend kernels, which leave the memory system idle.
             launch_pending_reduce()
             pending[0] = b
+            if args.eager_allreduce:
+                launch_pending_reduce()
 
     pending = [None]
 
@@ -361,6 +366,11 @@ def main():
         torch.cuda.synchronize()
 
     # ---- warm-up, then the timed region -------------------------------------------------------------------------
+    if world > 1:  # NCCL sets up its channels and buffers lazily: not inside the W warm-up steps, let alone the timed ones
+        for _ in range(3):
+            for bb in range(nbuf):
+                buckets[bb][0].all_reduce(async_op=True).wait()
+        torch.cuda.synchronize()
     for i in range(args.warmup):
         step(i)
     drain()
