@@ -241,6 +241,8 @@ static int forward_check(const char* who, const das3r_raster_params* params, con
         return fail_msg(DAS3R_EINVAL, std::string(who) + ": provide exactly one of (scales, rotations) / cov3D_precomp");
     if (in->shs && (params->M < (params->D + 1) * (params->D + 1) || params->M > 16))
         return fail_msg(DAS3R_EINVAL, std::string(who) + ": M must satisfy (D+1)^2 <= M <= 16");
+    if (in->rotations && (reinterpret_cast<uintptr_t>(in->rotations) & 15) != 0)
+        return fail_msg(DAS3R_EINVAL, std::string(who) + ": rotations must be 16-byte aligned (they are read as float4)");
     return DAS3R_OK;
 }
 
@@ -286,80 +288,117 @@ static int forward_begin(const das3r_raster_params* params, const das3r_raster_i
     return DAS3R_OK;
 }
 
-static int forward_scan(const das3r_raster_params* params, const das3r_raster_state* state, cudaStream_t stream) {
-    const int W = params->width, H = params->height;
-    const int T = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-    das3r_raster_state_layout L;
-    memset(&L, 0, sizeof(L));
-    image_layout(W, H, &L);
-    char* img = state->image;
-    STAGE(launch_tile_scan(reinterpret_cast<uint32_t*>(img + L.i_tile_counts), T,
-                           reinterpret_cast<uint2*>(img + L.i_ranges), reinterpret_cast<uint32_t*>(img + L.i_cursors),
-                           reinterpret_cast<uint32_t*>(img + L.i_totals), stream),
-          "tile_scan", ST_TILE_SCAN, 1);
-    return DAS3R_OK;
-}
-
-// Second half: read back num_rendered, size the binning blob, scatter, per-tile sort, rect lists, blend.
-static int forward_finish(const das3r_raster_params* params, const das3r_raster_outputs* out, das3r_alloc_fn binning_alloc,
-                          void* binning_ctx, das3r_raster_state* state, cudaStream_t stream) {
-    const int P = params->P, W = params->width, H = params->height;
-    const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-    const int T = (int)(gx * gy);
+// Per-view pointers of the binning / blend kernels that live in the geom and image blobs.
+static void bin_fill_state(ViewBin& vb, int P, int W, int H, char* geom, char* img, const int32_t* radii) {
     das3r_raster_state_layout L;
     memset(&L, 0, sizeof(L));
     geom_layout(P, &L);
     image_layout(W, H, &L);
-    char* geom = state->geom;
-    char* img = state->image;
-    GaussRec* rec = reinterpret_cast<GaussRec*>(geom + L.g_recA);
-    uint32_t* tiles_touched = reinterpret_cast<uint32_t*>(geom + L.g_tiles_touched);
-    float* final_T = reinterpret_cast<float*>(img + L.i_final_T);
-    uint32_t* n_contrib = reinterpret_cast<uint32_t*>(img + L.i_n_contrib);
-    uint2* ranges = reinterpret_cast<uint2*>(img + L.i_ranges);
-    uint32_t* cursors = reinterpret_cast<uint32_t*>(img + L.i_cursors);
-    uint32_t* totals = reinterpret_cast<uint32_t*>(img + L.i_totals);
+    vb.tile_counts = reinterpret_cast<uint32_t*>(img + L.i_tile_counts);
+    vb.ranges = reinterpret_cast<uint2*>(img + L.i_ranges);
+    vb.cursors = reinterpret_cast<uint32_t*>(img + L.i_cursors);
+    vb.totals = reinterpret_cast<uint32_t*>(img + L.i_totals);
+    vb.final_T = reinterpret_cast<float*>(img + L.i_final_T);
+    vb.n_contrib = reinterpret_cast<uint32_t*>(img + L.i_n_contrib);
+    vb.rec = reinterpret_cast<const GaussRec*>(geom + L.g_recA);
+    vb.tiles_touched = reinterpret_cast<const uint32_t*>(geom + L.g_tiles_touched);
+    vb.radii = radii;
+}
 
-    // The one host round trip of the forward (the reference has the same one, rasterizer_impl.cu:281).
-    uint32_t host_totals[4] = {0, 0, 0, 0};
-    cudaError_t e = cudaMemcpyAsync(host_totals, totals, sizeof(host_totals), cudaMemcpyDeviceToHost, stream);
+// ... and those in the binning blob.
+static void bin_fill_binning(ViewBin& vb, const das3r_raster_state_layout& L, char* bin, bool debug) {
+    vb.unsorted = reinterpret_cast<uint64_t*>(bin + L.b_unsorted);
+    vb.point_list = reinterpret_cast<uint32_t*>(bin + L.b_point_list);
+    vb.sA = reinterpret_cast<float4*>(bin + L.b_sA);
+    vb.sBC = reinterpret_cast<float4*>(bin + L.b_sB);
+    vb.rect_off = reinterpret_cast<uint32_t*>(bin + L.b_rect_off);
+    vb.rect_cnt = reinterpret_cast<uint32_t*>(bin + L.b_rect_cnt);
+    vb.rect_list = reinterpret_cast<uint2*>(bin + L.b_rect_list);
+    vb.keys_sorted = debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
+}
+
+static void batch_header(BatchArgs& b, int n, int P, int W, int H) {
+    memset(&b, 0, sizeof(b));
+    b.n = n; b.P = P; b.W = W; b.H = H;
+    b.gx = (unsigned)((W + TILE_X - 1) / TILE_X);
+    b.gy = (unsigned)((H + TILE_Y - 1) / TILE_Y);
+    b.T = (int)(b.gx * b.gy);
+}
+
+// Tile ranges of n views that share P and the image size: one launch, one block per view.
+static int forward_scan(int n, const das3r_raster_fwd_view* const* views, cudaStream_t stream) {
+    const das3r_raster_params* params = views[0]->params;
+    BatchArgs b;
+    batch_header(b, n, params->P, params->width, params->height);
+    for (int v = 0; v < n; v++)
+        bin_fill_state(b.v[v], params->P, params->width, params->height, views[v]->state->geom, views[v]->state->image,
+                       views[v]->out->radii);
+    STAGE(launch_tile_scan(b, stream), "tile_scan", ST_TILE_SCAN, 1);
+    return DAS3R_OK;
+}
+
+// Second half of the forward for n <= RB_MAX_VIEWS views that share P and the image size: ONE read-back of every
+// view's num_rendered, then binning, per-tile sort, rect lists and the blend, each as one launch over all views.
+// rendered[v] receives num_rendered of view v.
+static int forward_finish(int n, const das3r_raster_fwd_view* const* views, int* rendered, cudaStream_t stream) {
+    const das3r_raster_params* params = views[0]->params;
+    const int P = params->P, W = params->width, H = params->height;
+    BatchArgs b;
+    batch_header(b, n, P, W, H);
+    const int T = b.T;
+    for (int v = 0; v < n; v++)
+        bin_fill_state(b.v[v], P, W, H, views[v]->state->geom, views[v]->state->image, views[v]->out->radii);
+
+    // The one host round trip of the forward (the reference has one per view, rasterizer_impl.cu:281).
+    uint32_t host_totals[RB_MAX_VIEWS][4];
+    cudaError_t e = cudaSuccess;
+    for (int v = 0; v < n && e == cudaSuccess; v++)
+        e = cudaMemcpyAsync(host_totals[v], b.v[v].totals, sizeof(host_totals[v]), cudaMemcpyDeviceToHost, stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "read-back of num_rendered", e);
-    if (host_totals[0] > 0x7fffffffu) return fail_msg(DAS3R_ELIMIT, "forward: more than 2^31-1 tile instances");
-    const int R = (int)host_totals[0];
-    const uint32_t max_count = host_totals[1];
-    state->num_rendered = R;
 
-    const bool fallback = max_count > (uint32_t)tile_sort_capacity();
-    BinExtra X;
-    binning_layout(R, T, params->debug != 0, fallback, &L, &X);
-    char* bin = binning_alloc(L.binning_bytes, binning_ctx);
-    if (!bin && L.binning_bytes > 0) return fail_msg(DAS3R_ENOMEM, "forward: binning allocator returned NULL");
-    state->binning = bin;
-    state->binning_bytes = L.binning_bytes;
-    uint64_t* unsorted = reinterpret_cast<uint64_t*>(bin + L.b_unsorted);
-    uint32_t* point_list = reinterpret_cast<uint32_t*>(bin + L.b_point_list);
-    float4* sA = reinterpret_cast<float4*>(bin + L.b_sA);
-    float4* sBC = reinterpret_cast<float4*>(bin + L.b_sB);
-    uint32_t* rect_off = reinterpret_cast<uint32_t*>(bin + L.b_rect_off);
-    uint32_t* rect_cnt = reinterpret_cast<uint32_t*>(bin + L.b_rect_cnt);
-    uint2* rect_list = reinterpret_cast<uint2*>(bin + L.b_rect_list);
-    uint64_t* keys_sorted = params->debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
-
-    if (R > 0) {
-        STAGE(launch_scatter(P, gx, gy, rec, out->radii, tiles_touched, cursors, unsorted, stream), "scatter", ST_SCATTER, 1);
-        STAGE(launch_tile_sort(R, T, max_count, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted,
-                               fallback ? bin + X.b_fallback : nullptr, X.fallback_bytes, stream),
-              "tile_sort", ST_TILE_SORT,
-              2 + (max_count > 4096 ? 1 : 0) + (max_count > 8192 ? 1 : 0) + (fallback ? 3 : 0));
+    int R[RB_MAX_VIEWS];
+    uint32_t view_max[RB_MAX_VIEWS];
+    void* temp[RB_MAX_VIEWS];
+    size_t temp_bytes[RB_MAX_VIEWS];
+    uint32_t max_count = 0;
+    long long R_total = 0;
+    bool any_fallback = false;
+    for (int v = 0; v < n; v++) {
+        if (host_totals[v][0] > 0x7fffffffu) return fail_msg(DAS3R_ELIMIT, "forward: more than 2^31-1 tile instances");
+        R[v] = (int)host_totals[v][0];
+        view_max[v] = host_totals[v][1];
+        max_count = std::max(max_count, view_max[v]);
+        R_total += R[v];
+        das3r_raster_state* state = views[v]->state;
+        state->num_rendered = R[v];
+        rendered[v] = R[v];
+        const bool fallback = view_max[v] > (uint32_t)tile_sort_capacity();
+        any_fallback = any_fallback || fallback;
+        das3r_raster_state_layout L;
+        memset(&L, 0, sizeof(L));
+        BinExtra X;
+        binning_layout(R[v], T, views[v]->params->debug != 0, fallback, &L, &X);
+        char* bin = views[v]->binning_alloc(L.binning_bytes, views[v]->binning_ctx);
+        if (!bin && L.binning_bytes > 0) return fail_msg(DAS3R_ENOMEM, "forward: binning allocator returned NULL");
+        state->binning = bin;
+        state->binning_bytes = L.binning_bytes;
+        bin_fill_binning(b.v[v], L, bin, views[v]->params->debug != 0);
+        temp[v] = fallback ? bin + X.b_fallback : nullptr;
+        temp_bytes[v] = X.fallback_bytes;
+        b.v[v].bg = views[v]->params->background;
+        b.v[v].out_color = views[v]->out->out_color;
+        b.v[v].out_depth = views[v]->out->out_depth;
+        b.v[v].out_alpha = views[v]->out->out_alpha;
     }
-    if (R > 0)
-        STAGE(launch_rect_lists(T, gx, W, H, ranges, sA, sBC, rect_off, rect_cnt, rect_list, stream), "rect_lists",
-              ST_RECT_LISTS, 1);
-    STAGE(launch_blend_fwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, rec, W, H, params->background, final_T, n_contrib, out->out_color,
-                           out->out_depth, out->out_alpha, stream),
-          "blend_fwd", ST_BLEND_FWD, 1);
-    return R;
+    if (R_total > 0) {
+        STAGE(launch_scatter(b, stream), "scatter", ST_SCATTER, 1);
+        STAGE(launch_tile_sort(b, max_count, R, view_max, temp, temp_bytes, stream), "tile_sort", ST_TILE_SORT,
+              2 + (max_count > 4096 ? 1 : 0) + (max_count > 8192 ? 1 : 0) + (any_fallback ? 3 : 0));
+        STAGE(launch_rect_lists(b, stream), "rect_lists", ST_RECT_LISTS, 1);
+    }
+    STAGE(launch_blend_fwd(b, stream), "blend_fwd", ST_BLEND_FWD, 1);
+    return DAS3R_OK;
 }
 
 int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_inputs* in,
@@ -376,9 +415,16 @@ int das3r_raster_forward(const das3r_raster_params* params, const das3r_raster_i
     if (rc != DAS3R_OK) return rc;
     static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
     STAGE(launch_preprocess_fwd(a, stage_sh, stream), "preprocess_fwd", ST_PREPROCESS_FWD, 1);
-    rc = forward_scan(params, state, stream);
+    das3r_raster_fwd_view fv;
+    memset(&fv, 0, sizeof(fv));
+    fv.params = params; fv.in = in; fv.out = out; fv.state = state;
+    fv.binning_alloc = binning_alloc; fv.binning_ctx = binning_ctx;
+    const das3r_raster_fwd_view* one = &fv;
+    rc = forward_scan(1, &one, stream);
     if (rc != DAS3R_OK) return rc;
-    return forward_finish(params, out, binning_alloc, binning_ctx, state, stream);
+    int rendered = 0;
+    rc = forward_finish(1, &one, &rendered, stream);
+    return rc != DAS3R_OK ? rc : rendered;
 }
 
 int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view* views, void* stream_v) {
@@ -402,11 +448,13 @@ int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view
     }
     if (!params) return DAS3R_OK;
     static const bool stage_sh = getenv("DAS3R_NO_SH_STAGE") == nullptr;
-    // Views that can share one pass: same SH rows (degree 3, 16 coefficients, aligned), same P and image size.
+    // Views that can share one pass: same SH rows, same P and image size. Degree 3 stages the 16-coefficient rows
+    // through shared memory (needs 16-byte alignment); lower degrees read their few active floats per thread.
     auto fusable = [&](int v) {
         const PreFwdArgs& a = args[v];
-        return live[v] && stage_sh && a.shs && !a.colors_precomp && a.D == 3 && a.M == 16 &&
-               ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+        if (!live[v] || !stage_sh || !a.shs || a.colors_precomp) return false;
+        if (a.D == 3) return a.M == 16 && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+        return true;
     };
     std::vector<char> done((size_t)n_views, 0);
     for (int v0 = 0; v0 < n_views; v0++) {
@@ -423,7 +471,9 @@ int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view
         for (int v = v0; v < n_views && m.n_views < MF_MAX_VIEWS; v++) {
             if (done[v] || !fusable(v)) continue;
             const PreFwdArgs& a = args[v];
-            if (a.shs != args[v0].shs || a.P != args[v0].P || a.W != args[v0].W || a.H != args[v0].H) continue;
+            if (a.shs != args[v0].shs || a.P != args[v0].P || a.W != args[v0].W || a.H != args[v0].H ||
+                a.D != args[v0].D || a.M != args[v0].M)
+                continue;
             m.v[m.n_views++] = a;
             done[v] = 1;
         }
@@ -433,23 +483,79 @@ int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view
         else
             STAGE(launch_preprocess_fwd_multi(m, stream), "preprocess_fwd_multi", ST_PREPROCESS_FWD, 1);
     }
-    for (int v = 0; v < n_views; v++)
-        if (live[v]) {
-            int rc = forward_scan(views[v].params, views[v].state, stream);
-            if (rc != DAS3R_OK) return rc;
+    // tile ranges: one launch per group of views with the same P and image size
+    std::fill(done.begin(), done.end(), 0);
+    for (int v0 = 0; v0 < n_views; v0++) {
+        if (!live[v0] || done[v0]) continue;
+        const das3r_raster_fwd_view* grp[RB_MAX_VIEWS];
+        int n = 0;
+        for (int v = v0; v < n_views && n < RB_MAX_VIEWS; v++) {
+            if (!live[v] || done[v]) continue;
+            if (views[v].params->P != views[v0].params->P || views[v].params->width != views[v0].params->width ||
+                views[v].params->height != views[v0].params->height)
+                continue;
+            grp[n++] = &views[v];
+            done[v] = 1;
         }
+        int rc = forward_scan(n, grp, stream);
+        if (rc != DAS3R_OK) return rc;
+    }
+    return DAS3R_OK;
+}
+
+static int render_view_check(const das3r_raster_fwd_view* view) {
+    if (!view || !check_params(view->params) || !view->out || !view->state || !view->binning_alloc)
+        return fail_msg(DAS3R_EINVAL, "forward_render: null or invalid argument");
+    if (view->params->P == 0) return 1;  // the preprocess half has zeroed the image
+    if (!view->state->geom || !view->state->image || !view->out->out_color || !view->out->radii)
+        return fail_msg(DAS3R_EINVAL, "forward_render: the view has not been through das3r_raster_forward_preprocess");
     return DAS3R_OK;
 }
 
 int das3r_raster_forward_render(const das3r_raster_fwd_view* view, void* stream_v) {
     g_err.clear();
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
-    if (!view || !check_params(view->params) || !view->out || !view->state || !view->binning_alloc)
-        return fail_msg(DAS3R_EINVAL, "forward_render: null or invalid argument");
-    if (view->params->P == 0) return 0;  // the preprocess half has zeroed the image
-    if (!view->state->geom || !view->state->image || !view->out->out_color || !view->out->radii)
-        return fail_msg(DAS3R_EINVAL, "forward_render: the view has not been through das3r_raster_forward_preprocess");
-    return forward_finish(view->params, view->out, view->binning_alloc, view->binning_ctx, view->state, stream);
+    int rc = render_view_check(view);
+    if (rc != DAS3R_OK) return rc < 0 ? rc : 0;
+    int rendered = 0;
+    rc = forward_finish(1, &view, &rendered, stream);
+    return rc != DAS3R_OK ? rc : rendered;
+}
+
+int das3r_raster_forward_render_batch(int32_t n_views, const das3r_raster_fwd_view* views, int32_t* num_rendered,
+                                      void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (n_views < 1 || !views || !num_rendered)
+        return fail_msg(DAS3R_EINVAL, "forward_render_batch: null or invalid argument");
+    std::vector<char> todo((size_t)n_views, 0);
+    for (int v = 0; v < n_views; v++) {
+        num_rendered[v] = 0;
+        int rc = render_view_check(&views[v]);
+        if (rc < 0) return rc;
+        todo[v] = rc == DAS3R_OK;
+    }
+    // groups of views with the same P and image size (normally: all of them) share their launches
+    for (int v0 = 0; v0 < n_views; v0++) {
+        if (!todo[v0]) continue;
+        const das3r_raster_fwd_view* grp[RB_MAX_VIEWS];
+        int idx[RB_MAX_VIEWS];
+        int n = 0;
+        for (int v = v0; v < n_views && n < RB_MAX_VIEWS; v++) {
+            if (!todo[v]) continue;
+            if (views[v].params->P != views[v0].params->P || views[v].params->width != views[v0].params->width ||
+                views[v].params->height != views[v0].params->height || views[v].params->debug != views[v0].params->debug)
+                continue;
+            grp[n] = &views[v];
+            idx[n++] = v;
+            todo[v] = 0;
+        }
+        int rendered[RB_MAX_VIEWS];
+        int rc = forward_finish(n, grp, rendered, stream);
+        if (rc != DAS3R_OK) return rc;
+        for (int i = 0; i < n; i++) num_rendered[idx[i]] = rendered[i];
+    }
+    return DAS3R_OK;
 }
 
 size_t das3r_raster_backward_scratch_bytes(int32_t P) {
@@ -457,40 +563,52 @@ size_t das3r_raster_backward_scratch_bytes(int32_t P) {
 }
 
 // The two halves of the backward, shared by das3r_raster_backward and the split / multi-view entry points.
-static int backward_blend_impl(const char* who, const das3r_raster_params* params, const das3r_raster_state* state,
-                               const float* dL_dpix, float* scratch, cudaStream_t stream,
-                               das3r_raster_state_layout* L_out) {
-    const int P = params->P, W = params->width, H = params->height;
-    if (!dL_dpix || !state->geom || !state->image || !scratch)
-        return fail_msg(DAS3R_EINVAL, std::string(who) + ": null buffer");
-    const int R = state->num_rendered;
-    if (R > 0 && !state->binning) return fail_msg(DAS3R_EINVAL, std::string(who) + ": binning blob is null");
-    const unsigned gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
-    const int T = (int)(gx * gy);
-    das3r_raster_state_layout L;
-    memset(&L, 0, sizeof(L));
-    geom_layout(P, &L);
-    image_layout(W, H, &L);
-    BinExtra X;
-    binning_layout(R, T, params->debug != 0, false, &L, &X);
-    if (state->geom_bytes < L.geom_bytes || state->image_bytes < L.image_bytes)
-        return fail_msg(DAS3R_EINVAL, std::string(who) + ": state blobs are smaller than the forward's layout");
-    if (L_out) *L_out = L;
-    const float* final_T = reinterpret_cast<const float*>(state->image + L.i_final_T);
-    const uint32_t* n_contrib = reinterpret_cast<const uint32_t*>(state->image + L.i_n_contrib);
-    const uint2* ranges = reinterpret_cast<const uint2*>(state->image + L.i_ranges);
+// First half for n <= RB_MAX_VIEWS views that share P and the image size: every view's accumulators are cleared, then
+// ONE launch runs the backward blend of all views.
+struct BlendView {
+    const das3r_raster_params* params;
+    const das3r_raster_state* state;
+    const float* dL_dpix;
+    float* scratch;
+};
 
-    STAGE(cudaMemsetAsync(scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)", ST_MEMSET, 0);
-    if (R > 0) {
-        const float4* sA = reinterpret_cast<const float4*>(state->binning + L.b_sA);
-        const float4* sBC = reinterpret_cast<const float4*>(state->binning + L.b_sB);
-        const uint32_t* rect_off = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_off);
-        const uint32_t* rect_cnt = reinterpret_cast<const uint32_t*>(state->binning + L.b_rect_cnt);
-        const uint2* rect_list = reinterpret_cast<const uint2*>(state->binning + L.b_rect_list);
-        STAGE(launch_blend_bwd(gx, gy, ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, params->background, final_T, n_contrib,
-                               dL_dpix, scratch, stream),
-              "blend_bwd", ST_BLEND_BWD, 1);
+static int backward_blend_impl(const char* who, int n, const BlendView* views, cudaStream_t stream) {
+    const das3r_raster_params* params = views[0].params;  // the STAGE macro reads params->debug
+    const int P = params->P, W = params->width, H = params->height;
+    BatchArgs b;
+    batch_header(b, n, P, W, H);
+    const int T = b.T;
+    long long R_total = 0;
+    for (int v = 0; v < n; v++) {
+        const BlendView& V = views[v];
+        const das3r_raster_state* state = V.state;
+        if (!V.dL_dpix || !state->geom || !state->image || !V.scratch)
+            return fail_msg(DAS3R_EINVAL, std::string(who) + ": null buffer");
+        if ((reinterpret_cast<uintptr_t>(V.scratch) & 15) != 0)
+            return fail_msg(DAS3R_EINVAL, std::string(who) + ": the accumulator scratch must be 16-byte aligned");
+        const int R = state->num_rendered;
+        if (R < 0) return fail_msg(DAS3R_EINVAL, std::string(who) + ": negative num_rendered");
+        if (R > 0 && !state->binning) return fail_msg(DAS3R_EINVAL, std::string(who) + ": binning blob is null");
+        das3r_raster_state_layout L;
+        memset(&L, 0, sizeof(L));
+        geom_layout(P, &L);
+        image_layout(W, H, &L);
+        BinExtra X;
+        binning_layout(R, T, V.params->debug != 0, false, &L, &X);
+        if (state->geom_bytes < L.geom_bytes || state->image_bytes < L.image_bytes ||
+            (R > 0 && state->binning_bytes < L.binning_bytes))
+            return fail_msg(DAS3R_EINVAL, std::string(who) + ": state blobs are smaller than the forward's layout for "
+                                                              "this num_rendered");
+        bin_fill_state(b.v[v], P, W, H, state->geom, state->image, nullptr);
+        if (R > 0) bin_fill_binning(b.v[v], L, state->binning, V.params->debug != 0);
+        b.v[v].bg = V.params->background;
+        b.v[v].dL_dpix = V.dL_dpix;
+        b.v[v].acc = V.scratch;
+        R_total += R;
+        STAGE(cudaMemsetAsync(V.scratch, 0, (size_t)P * ACC_STRIDE * sizeof(float), stream), "memset(accumulators)",
+              ST_MEMSET, 0);
     }
+    if (R_total > 0) STAGE(launch_blend_bwd(b, stream), "blend_bwd", ST_BLEND_BWD, 1);
     return DAS3R_OK;
 }
 
@@ -514,6 +632,9 @@ static void fill_prebwd_args(PreBwdArgs& a, const das3r_raster_params* params, c
     a.accumulate = accumulate;
 }
 
+// The kernels read rotations and write dL_drotations / the accumulators with 128-bit accesses.
+static bool misaligned16(const void* p) { return p != nullptr && (reinterpret_cast<uintptr_t>(p) & 15) != 0; }
+
 int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in, const int32_t* radii,
                           const das3r_raster_state* state, const float* dL_dpix, const das3r_raster_grads* g,
                           void* stream_v) {
@@ -525,9 +646,14 @@ int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_
     if (!radii || !g->dL_dopacity || !g->dL_dmeans3D || !g->dL_dscales || !g->dL_drotations)
         return fail_msg(DAS3R_EINVAL, "backward: null buffer");
     if (in->shs && !g->dL_dsh) return fail_msg(DAS3R_EINVAL, "backward: dL_dsh is null although shs is given");
-    das3r_raster_state_layout L;
-    int rc = backward_blend_impl("backward", params, state, dL_dpix, g->scratch, stream, &L);
+    if (misaligned16(in->rotations) || misaligned16(g->dL_drotations) || misaligned16(g->scratch))
+        return fail_msg(DAS3R_EINVAL, "backward: rotations, dL_drotations and scratch must be 16-byte aligned");
+    BlendView bv{params, state, dL_dpix, g->scratch};
+    int rc = backward_blend_impl("backward", 1, &bv, stream);
     if (rc != DAS3R_OK) return rc;
+    das3r_raster_state_layout L;
+    memset(&L, 0, sizeof(L));
+    geom_layout(P, &L);
     const uint8_t* clamped = reinterpret_cast<const uint8_t*>(state->geom + L.g_clamped);
     PreBwdArgs a;
     fill_prebwd_args(a, params, in, radii, clamped, g->scratch, g, g->accumulate);
@@ -541,13 +667,39 @@ int das3r_raster_backward_blend(const das3r_raster_view* view, void* stream_v) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (!view || !check_params(view->params) || !view->state)
         return fail_msg(DAS3R_EINVAL, "backward_blend: null or invalid argument");
-    const das3r_raster_params* params = view->params;  // the STAGE macro reads params->debug
-    if (params->P == 0) return DAS3R_OK;
-    return backward_blend_impl("backward_blend", params, view->state, view->dL_dpix, view->scratch, stream, nullptr);
+    if (view->params->P == 0) return DAS3R_OK;
+    BlendView bv{view->params, view->state, view->dL_dpix, view->scratch};
+    return backward_blend_impl("backward_blend", 1, &bv, stream);
 }
 
-int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* g,
-                                 void* stream_v) {
+int das3r_raster_backward_blend_batch(int32_t n_views, const das3r_raster_view* views, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (n_views < 1 || !views) return fail_msg(DAS3R_EINVAL, "backward_blend_batch: null or invalid argument");
+    for (int v = 0; v < n_views; v++)
+        if (!check_params(views[v].params) || !views[v].state)
+            return fail_msg(DAS3R_EINVAL, "backward_blend_batch: null or invalid view");
+    std::vector<char> todo((size_t)n_views, 1);
+    for (int v0 = 0; v0 < n_views; v0++) {
+        if (!todo[v0] || views[v0].params->P == 0) continue;
+        BlendView grp[RB_MAX_VIEWS];
+        int n = 0;
+        for (int v = v0; v < n_views && n < RB_MAX_VIEWS; v++) {
+            const das3r_raster_params* p = views[v].params;
+            if (!todo[v] || p->P != views[v0].params->P || p->width != views[v0].params->width ||
+                p->height != views[v0].params->height || p->debug != views[v0].params->debug)
+                continue;
+            grp[n++] = BlendView{p, views[v].state, views[v].dL_dpix, views[v].scratch};
+            todo[v] = 0;
+        }
+        int rc = backward_blend_impl("backward_blend_batch", n, grp, stream);
+        if (rc != DAS3R_OK) return rc;
+    }
+    return DAS3R_OK;
+}
+
+int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* g,
+                                    int32_t dsh_coeffs, int32_t first, int32_t count, void* stream_v) {
     g_err.clear();
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (n_views < 1 || !views || !g) return fail_msg(DAS3R_EINVAL, "backward_finish: null or invalid argument");
@@ -561,8 +713,16 @@ int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views
             return fail_msg(DAS3R_EINVAL, "backward_finish: the views differ in their colour input");
     }
     const das3r_raster_params* params = views[0].params;  // for the STAGE macro
-    const int P = params->P;
-    if (P == 0) return DAS3R_OK;
+    const int P = params->P, D = params->D;
+    const int M = views[0].in->shs ? params->M : 0;
+    if (dsh_coeffs <= 0) dsh_coeffs = M;
+    if (first < 0) return fail_msg(DAS3R_EINVAL, "backward_finish: negative first");
+    if (count < 0) count = P - first;
+    if (count < 0 || (long long)first + count > P)
+        return fail_msg(DAS3R_EINVAL, "backward_finish: Gaussian range outside [0, P)");
+    if (M > 0 && (dsh_coeffs < (D + 1) * (D + 1) || dsh_coeffs > M))
+        return fail_msg(DAS3R_EINVAL, "backward_finish: dsh_coeffs must satisfy (D+1)^2 <= dsh_coeffs <= M");
+    if (P == 0 || count == 0) return DAS3R_OK;
     for (int v = 0; v < n_views; v++)
         if (!views[v].radii || !views[v].scratch || !views[v].state->geom)
             return fail_msg(DAS3R_EINVAL, "backward_finish: null buffer in a view");
@@ -576,40 +736,49 @@ int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views
     das3r_raster_state_layout L;
     memset(&L, 0, sizeof(L));
     geom_layout(P, &L);
+    for (int v = 0; v < n_views; v++) {
+        if (views[v].state->geom_bytes < L.geom_bytes)
+            return fail_msg(DAS3R_EINVAL, "backward_finish: geom blob is smaller than the forward's layout");
+        if (misaligned16(views[v].in->rotations) || misaligned16(views[v].dL_drotations) || misaligned16(views[v].scratch))
+            return fail_msg(DAS3R_EINVAL, "backward_finish: rotations, per-view dL_drotations and the accumulators must be "
+                                          "16-byte aligned");
+    }
+    if (misaligned16(g->dL_drotations))
+        return fail_msg(DAS3R_EINVAL, "backward_finish: dL_drotations must be 16-byte aligned");
 
-    // One fused pass when the views share their SH rows (degree 3) and use scale / rotation inputs; otherwise one
-    // accumulating pass per view, which gives the same sums.
-    bool fused = params->D == 3 && params->M == 16 && views[0].in->shs != nullptr &&
-                 ((reinterpret_cast<uintptr_t>(views[0].in->shs) & 15) == 0) &&
-                 ((reinterpret_cast<uintptr_t>(g->dL_dsh) & 15) == 0) &&
-                 ((reinterpret_cast<uintptr_t>(g->dL_drotations) & 15) == 0) && n_views > 1;
+    // One fused pass when the views share 16-coefficient SH rows and use scale / rotation inputs; otherwise one
+    // accumulating pass per view, which gives the same sums (full rows only).
+    const size_t o = (size_t)first;  // every pointer below is moved to the first Gaussian of the range
+    bool fused = M == 16 && views[0].in->shs != nullptr && !misaligned16(views[0].in->shs) &&
+                 (n_views > 1 || dsh_coeffs != M);
     for (int v = 0; v < n_views && fused; v++) {
         const das3r_raster_inputs* in = views[v].in;
-        fused = in->shs == views[0].in->shs && in->scales && in->rotations && !in->cov3D_precomp && !in->colors_precomp &&
-                ((reinterpret_cast<uintptr_t>(in->rotations) & 15) == 0) &&
-                ((reinterpret_cast<uintptr_t>(views[v].dL_drotations) & 15) == 0) &&
-                views[v].state->geom_bytes >= L.geom_bytes;
+        fused = in->shs == views[0].in->shs && in->scales && in->rotations && !in->cov3D_precomp && !in->colors_precomp;
     }
     if (fused) {
         for (int v0 = 0; v0 < n_views; v0 += MV_MAX_VIEWS) {
             MultiBwdArgs a;
             memset(&a, 0, sizeof(a));
-            a.P = P;
+            a.P = count;
             a.n_views = std::min(MV_MAX_VIEWS, n_views - v0);
-            a.accumulate = (v0 == 0) ? g->accumulate : 1;
-            a.shs = views[0].in->shs;
-            a.dL_dopacity = g->dL_dopacity; a.dL_dmeans3D = g->dL_dmeans3D; a.dL_dsh = g->dL_dsh;
-            a.dL_dscales = g->dL_dscales; a.dL_drots = g->dL_drotations;
+            a.accumulate_shared = (v0 == 0) ? g->accumulate : 1;
+            a.accumulate_view = g->accumulate;
+            a.D = D;
+            a.dsh_coeffs = dsh_coeffs;
+            a.shs = views[0].in->shs + o * 48;
+            a.dL_dopacity = g->dL_dopacity + o; a.dL_dmeans3D = g->dL_dmeans3D + o * 3;
+            a.dL_dsh = g->dL_dsh + o * 3 * dsh_coeffs;
+            a.dL_dscales = g->dL_dscales + o * 3; a.dL_drots = g->dL_drotations + o * 4;
             for (int i = 0; i < a.n_views; i++) {
                 const das3r_raster_view& V = views[v0 + i];
                 MultiBwdView& m = a.v[i];
-                m.means = V.in->means3D; m.scales = V.in->scales; m.rots = V.in->rotations;
+                m.means = V.in->means3D + o * 3; m.scales = V.in->scales + o * 3; m.rots = V.in->rotations + o * 4;
                 m.view = V.params->viewmatrix; m.proj = V.params->projmatrix; m.campos = V.params->campos;
-                m.radii = V.radii;
-                m.clamped = reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped);
-                m.acc = V.scratch;
-                m.dL_dmeans3D = V.dL_dmeans3D;
-                m.dL_drots = V.dL_drotations;
+                m.radii = V.radii + o;
+                m.clamped = reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped) + o;
+                m.acc = V.scratch + o * ACC_STRIDE;
+                m.dL_dmeans3D = V.dL_dmeans3D ? V.dL_dmeans3D + o * 3 : nullptr;
+                m.dL_drots = V.dL_drotations ? V.dL_drotations + o * 4 : nullptr;
                 m.tan_fovx = V.params->tan_fovx; m.tan_fovy = V.params->tan_fovy;
                 m.focal_x = V.params->width / (2.0f * V.params->tan_fovx);
                 m.focal_y = V.params->height / (2.0f * V.params->tan_fovy);
@@ -619,31 +788,54 @@ int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views
         }
         return DAS3R_OK;
     }
+    if (dsh_coeffs != M)
+        return fail_msg(DAS3R_EINVAL, "backward_finish: dL_dsh rows trimmed to the active bands need the fused path (views "
+                                      "sharing 16-coefficient, 16-byte aligned shs with scale / rotation inputs)");
+    // The one-view kernel has one accumulate switch for all its outputs. A view with outputs of its own (they follow
+    // grads->accumulate) and the summed outputs (which accumulate from the second view on) can only share a launch
+    // if both agree; otherwise the view's own outputs are cleared first and the launch accumulates.
     for (int v = 0; v < n_views; v++) {
         const das3r_raster_view& V = views[v];
-        if (V.state->geom_bytes < L.geom_bytes)
-            return fail_msg(DAS3R_EINVAL, "backward_finish: geom blob is smaller than the forward's layout");
+        das3r_raster_inputs in = *V.in;
+        in.means3D += o * 3;
+        if (in.shs) in.shs += o * 3 * M;
+        if (in.scales) in.scales += o * 3;
+        if (in.rotations) in.rotations += o * 4;
+        if (in.cov3D_precomp) in.cov3D_precomp += o * 6;
+        das3r_raster_grads gg = *g;
+        gg.dL_dopacity += o; gg.dL_dmeans3D += o * 3; gg.dL_dscales += o * 3; gg.dL_drotations += o * 4;
+        if (gg.dL_dsh) gg.dL_dsh += o * 3 * M;
+        if (gg.dL_dmeans2D) gg.dL_dmeans2D += o * 3;
+        if (gg.dL_dcolors) gg.dL_dcolors += o * 3;
+        if (gg.dL_dcov3D) gg.dL_dcov3D += o * 6;
+        das3r_raster_params pp = *V.params;
+        pp.P = count;
         PreBwdArgs a;
-        fill_prebwd_args(a, V.params, V.in, V.radii, reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped),
-                         V.scratch, g, v == 0 ? g->accumulate : 1);
+        fill_prebwd_args(a, &pp, &in, V.radii + o, reinterpret_cast<const uint8_t*>(V.state->geom + L.g_clamped) + o,
+                         V.scratch + o * ACC_STRIDE, &gg, v == 0 ? g->accumulate : 1);
         if (V.dL_dmeans3D || V.dL_drotations) {
-            // The one-view kernel has one accumulate switch for all outputs: a view with outputs of its own (which
-            // follow grads->accumulate) cannot share a launch with the summed ones (which accumulate from the second
-            // view on) unless both agree.
-            if (a.accumulate != g->accumulate)
-                return fail_msg(DAS3R_EINVAL, "backward_finish: per-view dL_dmeans3D / dL_drotations outside the fused "
-                                              "path need grads->accumulate = 1 (or a single view)");
+            float* vm = V.dL_dmeans3D ? V.dL_dmeans3D + o * 3 : nullptr;
+            float* vr = V.dL_drotations ? V.dL_drotations + o * 4 : nullptr;
+            if (a.accumulate != g->accumulate) {  // the launch accumulates, the view's own outputs must be overwritten
+                if (vm) STAGE(cudaMemsetAsync(vm, 0, (size_t)count * 3 * sizeof(float), stream), "memset(view dL_dmeans3D)", ST_MEMSET, 0);
+                if (vr) STAGE(cudaMemsetAsync(vr, 0, (size_t)count * 4 * sizeof(float), stream), "memset(view dL_drotations)", ST_MEMSET, 0);
+            }
             // the summed output this view does not feed still has to be defined
-            if (!g->accumulate && V.dL_dmeans3D)
-                STAGE(cudaMemsetAsync(g->dL_dmeans3D, 0, (size_t)P * 3 * sizeof(float), stream), "memset(dL_dmeans3D)", ST_MEMSET, 0);
-            if (!g->accumulate && V.dL_drotations)
-                STAGE(cudaMemsetAsync(g->dL_drotations, 0, (size_t)P * 4 * sizeof(float), stream), "memset(dL_drotations)", ST_MEMSET, 0);
-            if (V.dL_dmeans3D) a.dL_dmeans3D = V.dL_dmeans3D;
-            if (V.dL_drotations) a.dL_drots = V.dL_drotations;
+            if (!a.accumulate && vm)
+                STAGE(cudaMemsetAsync(gg.dL_dmeans3D, 0, (size_t)count * 3 * sizeof(float), stream), "memset(dL_dmeans3D)", ST_MEMSET, 0);
+            if (!a.accumulate && vr)
+                STAGE(cudaMemsetAsync(gg.dL_drotations, 0, (size_t)count * 4 * sizeof(float), stream), "memset(dL_drotations)", ST_MEMSET, 0);
+            if (vm) a.dL_dmeans3D = vm;
+            if (vr) a.dL_drots = vr;
         }
         STAGE(launch_preprocess_bwd(a, stream), "preprocess_bwd", ST_PREPROCESS_BWD, 1);
     }
     return DAS3R_OK;
+}
+
+int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* g,
+                                 void* stream_v) {
+    return das3r_raster_backward_finish_ex(n_views, views, g, 0, 0, -1, stream_v);
 }
 
 // ---- backward without any device allocation (see include/das3r_raster.h) ---------------------------------------

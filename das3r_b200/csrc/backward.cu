@@ -26,11 +26,22 @@ struct BwdPair {
 };
 
 __global__ void __launch_bounds__(32 * BLEND_WARPS, DAS3R_BWD_MIN_BLOCKS) blend_bwd_kernel(
-    const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
-    const uint2* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC, int W, int H,
-    unsigned gx, const float* __restrict__ bg, const float* __restrict__ final_Ts,
-    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, float* __restrict__ acc_out) {
+    const __grid_constant__ BatchArgs b) {
     __shared__ __align__(16) BlendSmem<BWD_K> sm;
+    const ViewBin& V = b.v[blockIdx.y];
+    const uint2* __restrict__ ranges = V.ranges;
+    const uint32_t* __restrict__ rect_off = V.rect_off;
+    const uint32_t* __restrict__ rect_cnt = V.rect_cnt;
+    const uint2* __restrict__ rect_list = V.rect_list;
+    const float4* __restrict__ sA = V.sA;
+    const float4* __restrict__ sBC = V.sBC;
+    const float* __restrict__ bg = V.bg;
+    const float* __restrict__ final_Ts = V.final_T;
+    const uint32_t* __restrict__ n_contrib = V.n_contrib;
+    const float* __restrict__ dL_dpixels = V.dL_dpix;
+    float* __restrict__ acc_out = V.acc;
+    const int W = b.W, H = b.H;
+    const unsigned gx = b.gx;
     const int warp = threadIdx.x >> 5;
     const WarpRect wr = warp_rect(W, H, gx);
     const uint2 range = ranges[wr.tile];
@@ -121,14 +132,11 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, DAS3R_BWD_MIN_BLOCKS) blend_
         });
 }
 
-cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
-                             int W, int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
-                             const float* dL_dpix, float* acc, cudaStream_t s) {
-    const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)blocks, 32 * BLEND_WARPS, sizeof(BlendSmem<BWD_K>));
-    blend_bwd_kernel<<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC, W, H, gx, bg,
-                                                           final_T, n_contrib, dL_dpix, acc);
+cudaError_t launch_blend_bwd(const BatchArgs& b, cudaStream_t s) {
+    const unsigned per_view = b.gx * b.gy * (8 / BLEND_WARPS);
+    const size_t pad = spread_pad_smem((const void*)blend_bwd_kernel, (int)(per_view * b.n), 32 * BLEND_WARPS,
+                                       sizeof(BlendSmem<BWD_K>));
+    blend_bwd_kernel<<<dim3(per_view, b.n), 32 * BLEND_WARPS, pad, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -543,26 +551,34 @@ __global__ void __launch_bounds__(PB_THREADS, 3) preprocess_bwd_kernel(const Pre
 
 // ---------------------------------------------------------------------------------------------------------------
 // preprocess_bwd_multi: the same gradients for SEVERAL views of one step in one pass, summed over the views in
-// registers / shared memory. What the views share - the SH rows (192 B per Gaussian at degree 3) - is read once, and
-// every gradient row is written (or added to the caller's buffer) once instead of once per view; per view only the
-// 48-byte accumulator row, mean, rotation, scale, radius and clamp bits are read. A Gaussian invisible in a view
-// contributes nothing for it. Sums are formed in view order. Fast path only: degree 3, M == 16, scale/rotation inputs.
+// registers / shared memory. What the views share - the SH rows - is read once, and every gradient row is written (or
+// added to the caller's buffer) once instead of once per view; per view only the 48-byte accumulator row, mean,
+// rotation, scale, radius and clamp bits are read. A Gaussian invisible in a view contributes nothing for it. Sums are
+// formed in view order. Scale/rotation inputs, 16-coefficient SH rows, any active degree DEG: only the 3*(DEG+1)^2
+// active floats of a row are read (staged through shared memory at degree 3, straight into registers below), and the
+// dL_dsh rows the kernel writes have `dsh_coeffs` coefficients - 16 (the reference's layout; the inactive bands are
+// written as zeros) or fewer, down to (DEG+1)^2 (rows trimmed to what can be non-zero: DAS3R trains at degree 0 for
+// 3000 of its 4000 iterations, train_gui.py:541-543, where 180 of the 192 bytes of a full row are identically zero).
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int MV_THREADS = 128;
 constexpr int MV_OUT_PITCH = MV_THREADS + 1;  // [coefficient][thread] accumulators, odd pitch: conflict-free both ways
 
+template <int DEG>
 __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(const __grid_constant__ MultiBwdArgs a) {
+    constexpr int NW = 3 * (DEG + 1) * (DEG + 1);  // active floats of an SH row
+    constexpr bool STAGE = DEG == 3;
     extern __shared__ __align__(16) unsigned char mv_smem[];
-    float4* in_rows = reinterpret_cast<float4*>(mv_smem);                                     // [MV_THREADS][13]
-    float* out_acc = reinterpret_cast<float*>(mv_smem + (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16);  // [48][MV_OUT_PITCH]
+    float4* in_rows = reinterpret_cast<float4*>(mv_smem);  // [MV_THREADS][13] (STAGE only)
+    float* out_acc = reinterpret_cast<float*>(mv_smem + (STAGE ? (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 : 0));  // [NW][pitch]
     __shared__ uint8_t row_vis[MV_THREADS];
     const int tid = threadIdx.x;
     const int base = blockIdx.x * MV_THREADS;
     const int idx = base + tid;
     const bool in_range = idx < a.P;
-    const bool accum = a.accumulate != 0;
+    const bool accum = a.accumulate_shared != 0;
+    const bool accum_view = a.accumulate_view != 0;
     const int nvalid = min(MV_THREADS, a.P - base);
-    {
+    if (STAGE) {
         const float4* src = reinterpret_cast<const float4*>(a.shs) + (size_t)base * PB_ROW_F4;
         const int total = nvalid * PB_ROW_F4;
 #pragma unroll
@@ -576,23 +592,25 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
         cp_async_commit();
     }
 #pragma unroll
-    for (int k = 0; k < 48; k++) out_acc[k * MV_OUT_PITCH + tid] = 0.f;
+    for (int k = 0; k < NW; k++) out_acc[k * MV_OUT_PITCH + tid] = 0.f;
 
     float3 s_mean = {0.f, 0.f, 0.f}, s_scale = {0.f, 0.f, 0.f};
     float4 s_rot = {0.f, 0.f, 0.f, 0.f};
     float s_opac = 0.f;
     bool any_vis = false;
 
-    cp_async_wait_all();
-    __syncthreads();
     float f[48];
-    {
+    if (STAGE) {
+        cp_async_wait_all();
+        __syncthreads();
         const float4* myrow = &in_rows[tid * PB_ROW_PAD_F4];
 #pragma unroll
         for (int j = 0; j < PB_ROW_F4; j++) {
             const float4 v = myrow[j];
             f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
         }
+    } else if (in_range) {
+        load_sh_row(a.shs + (size_t)idx * 48, DEG, true, f);
     }
 
 #pragma unroll 1
@@ -601,7 +619,7 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
         if (!in_range) continue;
         if (V.radii[idx] <= 0) {
             // not rendered in this view: a per-view output still has to be defined
-            if (!accum) {
+            if (!accum_view) {
                 if (V.dL_dmeans3D) {
                     V.dL_dmeans3D[3 * idx] = 0.f; V.dL_dmeans3D[3 * idx + 1] = 0.f; V.dL_dmeans3D[3 * idx + 2] = 0.f;
                 }
@@ -623,7 +641,7 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
         geom_backward(vc, mean, cov3D, true, sc, rq, q0.x, q0.y, make_float3(q0.z, q0.w, q1.x), gg);
         const float3 cam = {V.campos[0], V.campos[1], V.campos[2]};
         const float3 dm = sh_backward(
-            3, mean, cam, cl, make_float3(q1.z, q1.w, q2.x),
+            DEG, mean, cam, cl, make_float3(q1.z, q1.w, q2.x),
             [&](int k) { return make_float3(f[3 * k], f[3 * k + 1], f[3 * k + 2]); },
             [&](int k, float3 g) {
                 out_acc[(3 * k + 0) * MV_OUT_PITCH + tid] += g.x;
@@ -633,16 +651,16 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
         const float3 gm = {gg.dmean.x + dm.x, gg.dmean.y + dm.y, gg.dmean.z + dm.z};
         if (V.dL_dmeans3D) {
             float* o = V.dL_dmeans3D + 3 * (size_t)idx;
-            o[0] = accum ? o[0] + gm.x : gm.x;
-            o[1] = accum ? o[1] + gm.y : gm.y;
-            o[2] = accum ? o[2] + gm.z : gm.z;
+            o[0] = accum_view ? o[0] + gm.x : gm.x;
+            o[1] = accum_view ? o[1] + gm.y : gm.y;
+            o[2] = accum_view ? o[2] + gm.z : gm.z;
         } else {
             s_mean.x += gm.x; s_mean.y += gm.y; s_mean.z += gm.z;
         }
         if (V.dL_drots) {
             float4* o = reinterpret_cast<float4*>(V.dL_drots) + idx;
             float4 r = gg.drot;
-            if (accum) {
+            if (accum_view) {
                 const float4 p = *o;
                 r.x += p.x; r.y += p.y; r.z += p.z; r.w += p.w;
             }
@@ -672,34 +690,56 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
         *dr = s_rot;
     }
     __syncthreads();
-    {
-        const int total = nvalid * PB_ROW_F4;
-        float4* dst = reinterpret_cast<float4*>(a.dL_dsh) + (size_t)base * PB_ROW_F4;
-#pragma unroll
-        for (int k = 0; k < PB_ROW_F4; k++) {
-            const int e = tid + k * MV_THREADS;
-            if (e < total) {
-                const int g = e / PB_ROW_F4, j = e - g * PB_ROW_F4;
-                if (accum && !row_vis[g]) continue;  // nothing to add
-                float4 o = make_float4(out_acc[(4 * j + 0) * MV_OUT_PITCH + g], out_acc[(4 * j + 1) * MV_OUT_PITCH + g],
-                                       out_acc[(4 * j + 2) * MV_OUT_PITCH + g], out_acc[(4 * j + 3) * MV_OUT_PITCH + g]);
-                if (accum) {
-                    const float4 p = dst[e];
-                    o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
-                }
-                dst[e] = o;
+    // dL_dsh rows of the block, [nvalid][3 * dsh_coeffs] floats, contiguous in memory: coalesced write-out from the
+    // transposed accumulators; floats beyond the active bands are zeros (overwrite mode) or left alone (accumulate)
+    const int row_f = 3 * a.dsh_coeffs;
+    float* dst_f = a.dL_dsh + (size_t)base * row_f;
+    if ((row_f & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst_f) & 15) == 0)) {
+        const int row_f4 = row_f >> 2;
+        const int total = nvalid * row_f4;
+        float4* dst = reinterpret_cast<float4*>(dst_f);
+        for (int e = tid; e < total; e += MV_THREADS) {
+            const int g = e / row_f4, j = e - g * row_f4;
+            if (accum && (!row_vis[g] || 4 * j >= NW)) continue;  // nothing to add
+            float4 o;
+            o.x = (4 * j + 0 < NW) ? out_acc[(4 * j + 0) * MV_OUT_PITCH + g] : 0.f;
+            o.y = (4 * j + 1 < NW) ? out_acc[(4 * j + 1) * MV_OUT_PITCH + g] : 0.f;
+            o.z = (4 * j + 2 < NW) ? out_acc[(4 * j + 2) * MV_OUT_PITCH + g] : 0.f;
+            o.w = (4 * j + 3 < NW) ? out_acc[(4 * j + 3) * MV_OUT_PITCH + g] : 0.f;
+            if (accum) {
+                const float4 p = dst[e];
+                o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
             }
+            dst[e] = o;
+        }
+    } else {
+        const int total = nvalid * row_f;
+        for (int e = tid; e < total; e += MV_THREADS) {
+            const int g = e / row_f, j = e - g * row_f;
+            if (accum && (!row_vis[g] || j >= NW)) continue;
+            float o = (j < NW) ? out_acc[j * MV_OUT_PITCH + g] : 0.f;
+            if (accum) o += dst_f[e];
+            dst_f[e] = o;
         }
     }
 }
 
 cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s) {
     const int blocks = (a.P + MV_THREADS - 1) / MV_THREADS;
-    const size_t smem = (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 + (size_t)48 * MV_OUT_PITCH * sizeof(float);
-    cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
+    const int nw = 3 * (a.D + 1) * (a.D + 1);
+    const size_t smem = (a.D == 3 ? (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 : 0) + (size_t)nw * MV_OUT_PITCH * sizeof(float);
+    const void* fn = a.D == 0   ? (const void*)preprocess_bwd_multi_kernel<0>
+                     : a.D == 1 ? (const void*)preprocess_bwd_multi_kernel<1>
+                     : a.D == 2 ? (const void*)preprocess_bwd_multi_kernel<2>
+                                : (const void*)preprocess_bwd_multi_kernel<3>;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    preprocess_bwd_multi_kernel<<<blocks, MV_THREADS, smem, s>>>(a);
+    switch (a.D) {
+        case 0: preprocess_bwd_multi_kernel<0><<<blocks, MV_THREADS, smem, s>>>(a); break;
+        case 1: preprocess_bwd_multi_kernel<1><<<blocks, MV_THREADS, smem, s>>>(a); break;
+        case 2: preprocess_bwd_multi_kernel<2><<<blocks, MV_THREADS, smem, s>>>(a); break;
+        default: preprocess_bwd_multi_kernel<3><<<blocks, MV_THREADS, smem, s>>>(a); break;
+    }
     return cudaGetLastError();
 }
 

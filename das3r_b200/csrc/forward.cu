@@ -265,21 +265,25 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
     }
 }
 
-// preprocess_fwd for SEVERAL views that share their SH rows (degree 3): the block's 256 rows are staged once, every
-// thread then runs the geometry and colour halves for each view with the row in registers - the 192 bytes of SH per
-// Gaussian, two thirds of the kernel's traffic, are read once per step instead of once per view. Same device functions
-// as the one-view kernel, so every output is bit-identical to it (tests/test_gpu_multiview.py).
+// preprocess_fwd for SEVERAL views that share their SH rows. STAGE (degree 3, 16 coefficients): the block's 256 rows are
+// staged once, every thread then runs the geometry and colour halves for each view with the row in shared memory - the
+// 192 bytes of SH per Gaussian, two thirds of the kernel's traffic, are read once per step instead of once per view.
+// !STAGE (degrees 0..2, the regime DAS3R trains in: train_gui.py:541-543): a thread reads the 12..108 active bytes of
+// its row per view (first view from HBM, the others from L1/L2); what the views share here is the launch, the tile
+// histograms and the Gaussian-major sweep. Same device functions as the one-view kernel, so every output is
+// bit-identical to it (tests/test_gpu_multiview.py).
+template <bool STAGE>
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_multi_kernel(const __grid_constant__ MultiFwdArgs m) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* sh_stage = reinterpret_cast<float4*>(smem_raw);
-    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + PRE_THREADS * SH_ROW_PAD_F4 * 16);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + (STAGE ? PRE_THREADS * SH_ROW_PAD_F4 * 16 : 0));
     const int tid = threadIdx.x;
     const int base = blockIdx.x * PRE_THREADS;
     const int idx = base + tid;
     const int P = m.v[0].P, T = m.T;
     if (m.smem_hist)
         for (int i = tid; i < T * m.n_views; i += PRE_THREADS) hist[i] = 0;
-    {
+    if (STAGE) {
         const int nvalid = min(PRE_THREADS, P - base);
         const float4* src = reinterpret_cast<const float4*>(m.v[0].shs) + (size_t)base * SH_ROW_F4;
         const int total = nvalid * SH_ROW_F4;
@@ -292,14 +296,14 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_multi_kernel(const
             }
         }
         cp_async_commit();
+        cp_async_wait_all();
     }
-    cp_async_wait_all();
     __syncthreads();
 #pragma unroll 1
     for (int v = 0; v < m.n_views; v++) {
         const PreFwdArgs& a = m.v[v];
         const PreGeom g = pre_geometry(a, idx);
-        pre_finish<true>(a, idx, g, sh_stage + tid * SH_ROW_PAD_F4, hist + (size_t)v * T);
+        pre_finish<STAGE>(a, idx, g, sh_stage + tid * SH_ROW_PAD_F4, hist + (size_t)v * T);
     }
     if (m.smem_hist) {
         __syncthreads();
@@ -312,14 +316,20 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_multi_kernel(const
 
 cudaError_t launch_preprocess_fwd_multi(const MultiFwdArgs& m_in, cudaStream_t s) {
     MultiFwdArgs m = m_in;
+    const bool stage = m.v[0].D == 3 && m.v[0].M == 16;
+    const size_t stage_bytes = stage ? (size_t)PRE_THREADS * SH_ROW_PAD_F4 * 16 : 0;
     const size_t hist_bytes = (size_t)m.T * m.n_views * 4;
     m.smem_hist = hist_bytes <= 96 * 1024 ? 1 : 0;
     for (int v = 0; v < m.n_views; v++) m.v[v].smem_hist = m.smem_hist;
-    const size_t smem = (size_t)PRE_THREADS * SH_ROW_PAD_F4 * 16 + (m.smem_hist ? hist_bytes : 0);
-    cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = stage_bytes + (m.smem_hist ? hist_bytes : 0);
+    const void* fn = stage ? (const void*)preprocess_fwd_multi_kernel<true> : (const void*)preprocess_fwd_multi_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int blocks = (m.v[0].P + PRE_THREADS - 1) / PRE_THREADS;
-    preprocess_fwd_multi_kernel<<<blocks, PRE_THREADS, smem, s>>>(m);
+    if (stage)
+        preprocess_fwd_multi_kernel<true><<<blocks, PRE_THREADS, smem, s>>>(m);
+    else
+        preprocess_fwd_multi_kernel<false><<<blocks, PRE_THREADS, smem, s>>>(m);
     return cudaGetLastError();
 }
 
@@ -350,12 +360,15 @@ cudaError_t launch_preprocess_fwd(const PreFwdArgs& a_in, bool stage_sh, cudaStr
 // reference's memset + identifyTileRanges leave behind (rasterizer_impl.cu:310-318).
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int SCAN_THREADS = 1024;
-__global__ void __launch_bounds__(SCAN_THREADS) tile_scan_kernel(const uint32_t* __restrict__ counts, int T,
-                                                                 uint2* __restrict__ ranges,
-                                                                 uint32_t* __restrict__ cursors,
-                                                                 uint32_t* __restrict__ totals) {
+__global__ void __launch_bounds__(SCAN_THREADS) tile_scan_kernel(const __grid_constant__ BatchArgs b) {
     __shared__ uint32_t warp_sum[32];
     __shared__ uint32_t warp_max[32];
+    const ViewBin& V = b.v[blockIdx.x];  // one block per view
+    const uint32_t* __restrict__ counts = V.tile_counts;
+    uint2* __restrict__ ranges = V.ranges;
+    uint32_t* __restrict__ cursors = V.cursors;
+    uint32_t* __restrict__ totals = V.totals;
+    const int T = b.T;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int per = (T + SCAN_THREADS - 1) / SCAN_THREADS;
     const int beg = tid * per, end = min(T, beg + per);
@@ -405,9 +418,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) tile_scan_kernel(const uint32_t*
     }
 }
 
-cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,
-                             cudaStream_t s) {
-    tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(counts, T, ranges, cursors, totals);
+cudaError_t launch_tile_scan(const BatchArgs& b, cudaStream_t s) {
+    tile_scan_kernel<<<b.n, SCAN_THREADS, 0, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -419,12 +431,16 @@ cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint3
 // with a single global atomic, then hands out slots with shared-memory atomics. Consecutive Gaussians of a pointmap
 // land in the same few tiles, so this replaces ~R same-address global atomics by a handful per block.
 template <bool SMEM>
-__global__ void __launch_bounds__(256) scatter_kernel(int P, unsigned gx, unsigned gy, const GaussRec* __restrict__ rec,
-                                                      const int* __restrict__ radii,
-                                                      const uint32_t* __restrict__ tiles_touched,
-                                                      uint32_t* __restrict__ cursors,
-                                                      uint64_t* __restrict__ unsorted) {
+__global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ BatchArgs b) {
     extern __shared__ uint32_t s_u32[];
+    const ViewBin& V = b.v[blockIdx.y];
+    const int P = b.P;
+    const unsigned gx = b.gx, gy = b.gy;
+    const GaussRec* __restrict__ rec = V.rec;
+    const int* __restrict__ radii = V.radii;
+    const uint32_t* __restrict__ tiles_touched = V.tiles_touched;
+    uint32_t* __restrict__ cursors = V.cursors;
+    uint64_t* __restrict__ unsorted = V.unsorted;
     const int T = (int)(gx * gy);
     uint32_t* s_cnt = s_u32;
     uint32_t* s_base = s_u32 + T;
@@ -467,13 +483,13 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, unsigned gx, unsign
         }
 }
 
-cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,
-                           const uint32_t* tiles_touched, uint32_t* cursors, uint64_t* unsorted, cudaStream_t s) {
-    const size_t smem = (size_t)gx * gy * 8;
+cudaError_t launch_scatter(const BatchArgs& b, cudaStream_t s) {
+    const size_t smem = (size_t)b.T * 8;
+    const dim3 grid((b.P + 255) / 256, b.n);
     if (smem <= 48 * 1024)
-        scatter_kernel<true><<<(P + 255) / 256, 256, smem, s>>>(P, gx, gy, rec, radii, tiles_touched, cursors, unsorted);
+        scatter_kernel<true><<<grid, 256, smem, s>>>(b);
     else
-        scatter_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, rec, radii, tiles_touched, cursors, unsorted);
+        scatter_kernel<false><<<grid, 256, 0, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -578,9 +594,12 @@ constexpr int MED_CAP = 2048;  // buckets with more than 8 keys: at most 16384 /
 
 template <int MAXE, int MIN_N, int LOG_NB>
 __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
-    tile_sort_kernel(const uint2* __restrict__ ranges, const uint64_t* __restrict__ unsorted,
-                     const GaussRec* __restrict__ rec, uint32_t* __restrict__ point_list, float4* __restrict__ sA,
-                     float4* __restrict__ sBC, uint64_t* __restrict__ keys_sorted) {
+    tile_sort_kernel(const __grid_constant__ BatchArgs b) {
+    const ViewBin& V = b.v[blockIdx.y];
+    const uint2* __restrict__ ranges = V.ranges;
+    const uint64_t* __restrict__ unsorted = V.unsorted;
+    uint32_t* __restrict__ point_list = V.point_list;
+    uint64_t* __restrict__ keys_sorted = V.keys_sorted;
     constexpr int NB = 1 << LOG_NB;
     constexpr int PER = NB / SORT_THREADS;  // bucket counters per thread in the scan
     static_assert(NB % SORT_THREADS == 0 && PER >= 1, "bucket count must be a multiple of the block size");
@@ -782,24 +801,22 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
 }
 
 // gather_records: entry i of the sorted list -> sA[i] = {x, y, h, -tau'}, sBC[i] = {conic, opacity}, {rgb, index}.
-__global__ void __launch_bounds__(256) gather_records_kernel(int R, const uint32_t* __restrict__ point_list,
-                                                             const GaussRec* __restrict__ rec, float4* __restrict__ sA,
-                                                             float4* __restrict__ sBC) {
+// grid.y = view; the view's entry count is read from its totals (the grid is sized for the largest view).
+__global__ void __launch_bounds__(256) gather_records_kernel(const __grid_constant__ BatchArgs b) {
+    const ViewBin& V = b.v[blockIdx.y];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= R) return;
-    const uint32_t g = point_list[i];
-    const GaussRec r = rec[g];
-    sA[i] = r.A;
-    sBC[2 * (size_t)i] = r.B;
-    sBC[2 * (size_t)i + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
+    if ((uint32_t)i >= V.totals[0]) return;
+    const uint32_t g = V.point_list[i];
+    const GaussRec r = V.rec[g];
+    V.sA[i] = r.A;
+    V.sBC[2 * (size_t)i] = r.B;
+    V.sBC[2 * (size_t)i + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
 }
 
 int tile_sort_capacity() { return SORT_THREADS * SORT_MAX_E; }
 
 template <int MAXE, int MIN_N, int LOG_NB>
-static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const uint64_t* unsorted, const GaussRec* rec,
-                                            uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
-                                            cudaStream_t s) {
+static cudaError_t launch_tile_sort_variant(const BatchArgs& b, cudaStream_t s) {
     const size_t smem = (size_t)SORT_THREADS * MAXE * sizeof(uint64_t) + 3 * ((size_t)1 << LOG_NB) * sizeof(uint32_t) +
                         MED_CAP * sizeof(uint16_t);
     if (smem + 2048 > 48 * 1024) {  // + the kernel's static shared memory
@@ -807,8 +824,7 @@ static cudaError_t launch_tile_sort_variant(int T, const uint2* ranges, const ui
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
     }
-    tile_sort_kernel<MAXE, MIN_N, LOG_NB><<<T, SORT_THREADS, smem, s>>>(ranges, unsorted, rec, point_list, sA, sBC,
-                                                                        keys_sorted);
+    tile_sort_kernel<MAXE, MIN_N, LOG_NB><<<dim3(b.T, b.n), SORT_THREADS, smem, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -845,16 +861,19 @@ cudaError_t side_streams(cudaStream_t out[2]) {
 static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint64_t* unsorted, uint32_t* point_list,
                                         uint64_t* keys_sorted, void* temp, size_t temp_bytes, cudaStream_t s);
 
-cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, uint64_t* unsorted,
-                             const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
-                             void* temp, size_t temp_bytes, cudaStream_t s) {
+cudaError_t launch_tile_sort(const BatchArgs& b, uint32_t max_count, const int* R, const uint32_t* view_max,
+                             void* const* temp, const size_t* temp_bytes, cudaStream_t s) {
     // Tiles are sorted by the cheapest variant that fits them (<= 4096, <= 8192, <= 16384 entries in shared memory;
-    // beyond that a library segmented radix sort restricted to those tiles): every launch covers all tiles and a block
-    // whose tile belongs to another size class exits at once. The crowded classes (one block per SM, a few dozen
-    // tiles) run on auxiliary streams next to the common one instead of in front of it.
+    // beyond that a library segmented radix sort restricted to those tiles): every launch covers all tiles of all views
+    // and a block whose tile belongs to another size class exits at once. The crowded classes (one block per SM, a few
+    // dozen tiles) run on auxiliary streams next to the common one instead of in front of it.
     const bool need16 = max_count > SORT_THREADS * 8, need32 = max_count > SORT_THREADS * 16;
     const bool need_lib = max_count > (uint32_t)tile_sort_capacity();
-    if (need_lib && (temp == nullptr || temp_bytes < tile_sort_fallback_bytes(R, T))) return cudaErrorInvalidValue;
+    if (need_lib)
+        for (int v = 0; v < b.n; v++)
+            if (view_max[v] > (uint32_t)tile_sort_capacity() &&
+                (temp[v] == nullptr || temp_bytes[v] < tile_sort_fallback_bytes(R[v], b.T)))
+                return cudaErrorInvalidValue;
     cudaError_t e = cudaSuccess;
     cudaStream_t side[2] = {nullptr, nullptr};
     cudaEvent_t fork = nullptr, join[2] = {nullptr, nullptr};
@@ -866,21 +885,21 @@ cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* rang
             if (c == 1 && !need32) break;
             e = cudaStreamWaitEvent(side[c], fork, 0);
             if (e != cudaSuccess) break;
-            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8, DAS3R_SORT16_LOGNB>(T, ranges, unsorted, rec, point_list, sA, sBC,
-                                                                             keys_sorted, side[c])
-                         : launch_tile_sort_variant<32, SORT_THREADS * 16, 12>(T, ranges, unsorted, rec, point_list, sA,
-                                                                              sBC, keys_sorted, side[c]);
+            e = (c == 0) ? launch_tile_sort_variant<16, SORT_THREADS * 8, DAS3R_SORT16_LOGNB>(b, side[c])
+                         : launch_tile_sort_variant<32, SORT_THREADS * 16, 12>(b, side[c]);
             if (e != cudaSuccess) break;
             if (c == 1 && need_lib) {
-                e = sort_oversized_tiles(R, T, ranges, unsorted, point_list, keys_sorted, temp, temp_bytes, side[c]);
+                for (int v = 0; v < b.n && e == cudaSuccess; v++)
+                    if (view_max[v] > (uint32_t)tile_sort_capacity())
+                        e = sort_oversized_tiles(R[v], b.T, b.v[v].ranges, b.v[v].unsorted, b.v[v].point_list,
+                                                 b.v[v].keys_sorted, temp[v], temp_bytes[v], side[c]);
                 if (e != cudaSuccess) break;
             }
             if ((e = cudaEventCreateWithFlags(&join[c], cudaEventDisableTiming)) != cudaSuccess) break;
             e = cudaEventRecord(join[c], side[c]);
         }
     }
-    if (e == cudaSuccess)
-        e = launch_tile_sort_variant<8, 0, 10>(T, ranges, unsorted, rec, point_list, sA, sBC, keys_sorted, s);
+    if (e == cudaSuccess) e = launch_tile_sort_variant<8, 0, 10>(b, s);
     for (int c = 0; c < 2; c++)
         if (join[c]) {
             if (e == cudaSuccess) e = cudaStreamWaitEvent(s, join[c], 0);
@@ -888,7 +907,9 @@ cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* rang
         }
     if (fork) cudaEventDestroy(fork);
     if (e != cudaSuccess) return e;
-    gather_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, point_list, rec, sA, sBC);
+    int Rmax = 0;
+    for (int v = 0; v < b.n; v++) Rmax = R[v] > Rmax ? R[v] : Rmax;
+    if (Rmax > 0) gather_records_kernel<<<dim3((Rmax + 255) / 256, b.n), 256, 0, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -1008,12 +1029,17 @@ static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint6
 #ifndef DAS3R_RECT_MIN_BLOCKS
 #define DAS3R_RECT_MIN_BLOCKS 4
 #endif
-__global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(const uint2* __restrict__ ranges,
-                                                         const float4* __restrict__ sA, const float4* __restrict__ sBC,
-                                                         unsigned gx, int W, int H, uint32_t* __restrict__ rect_off,
-                                                         uint32_t* __restrict__ rect_cnt,
-                                                         uint2* __restrict__ rect_list) {
+__global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(const __grid_constant__ BatchArgs b) {
     __shared__ uint32_t cand_s[8][256];  // per warp: circular buffer of tile-list positions that reach the rectangle
+    const ViewBin& V = b.v[blockIdx.y];
+    const uint2* __restrict__ ranges = V.ranges;
+    const float4* __restrict__ sA = V.sA;
+    const float4* __restrict__ sBC = V.sBC;
+    uint32_t* __restrict__ rect_off = V.rect_off;
+    uint32_t* __restrict__ rect_cnt = V.rect_cnt;
+    uint2* __restrict__ rect_list = V.rect_list;
+    const unsigned gx = b.gx;
+    const int W = b.W, H = b.H;
     const int tile = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
@@ -1091,10 +1117,8 @@ __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(
     }
 }
 
-cudaError_t launch_rect_lists(int T, unsigned gx, int W, int H, const uint2* ranges, const float4* sA,
-                              const float4* sBC, uint32_t* rect_off, uint32_t* rect_cnt, uint2* rect_list,
-                              cudaStream_t s) {
-    rect_lists_kernel<<<T, 256, 0, s>>>(ranges, sA, sBC, gx, W, H, rect_off, rect_cnt, rect_list);
+cudaError_t launch_rect_lists(const BatchArgs& b, cudaStream_t s) {
+    rect_lists_kernel<<<dim3(b.T, b.n), 256, 0, s>>>(b);
     return cudaGetLastError();
 }
 
@@ -1126,13 +1150,24 @@ struct FwdPair {
 };
 
 template <bool EXTRAS>
-__global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
-    const uint2* __restrict__ ranges, const uint32_t* __restrict__ rect_off, const uint32_t* __restrict__ rect_cnt,
-    const uint2* __restrict__ rect_list, const float4* __restrict__ sA, const float4* __restrict__ sBC,
-    const GaussRec* __restrict__ rec_by_id, int W, int H, unsigned gx, const float* __restrict__ bg,
-    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
-    float* __restrict__ out_depth, float* __restrict__ out_alpha) {
+__global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(const __grid_constant__ BatchArgs b) {
     __shared__ __align__(16) BlendSmem<FWD_K> sm;
+    const ViewBin& V = b.v[blockIdx.y];
+    const uint2* __restrict__ ranges = V.ranges;
+    const uint32_t* __restrict__ rect_off = V.rect_off;
+    const uint32_t* __restrict__ rect_cnt = V.rect_cnt;
+    const uint2* __restrict__ rect_list = V.rect_list;
+    const float4* __restrict__ sA = V.sA;
+    const float4* __restrict__ sBC = V.sBC;
+    const GaussRec* __restrict__ rec_by_id = V.rec;
+    const float* __restrict__ bg = V.bg;
+    float* __restrict__ final_T = V.final_T;
+    uint32_t* __restrict__ n_contrib = V.n_contrib;
+    float* __restrict__ out_color = V.out_color;
+    float* __restrict__ out_depth = V.out_depth;
+    float* __restrict__ out_alpha = V.out_alpha;
+    const int W = b.W, H = b.H;
+    const unsigned gx = b.gx;
     const int warp = threadIdx.x >> 5;
     const WarpRect wr = warp_rect(W, H, gx);
     const uint2 range = ranges[wr.tile];
@@ -1215,20 +1250,17 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(
     }
 }
 
-cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
-                             const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
-                             uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
-                             cudaStream_t s) {
-    const unsigned blocks = gx * gy * (8 / BLEND_WARPS);
-    if (out_depth || out_alpha) {
-        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<true>, (int)blocks, 32 * BLEND_WARPS,
+cudaError_t launch_blend_fwd(const BatchArgs& b, cudaStream_t s) {
+    const unsigned per_view = b.gx * b.gy * (8 / BLEND_WARPS);
+    bool extras = false;  // depth / alpha wanted by any view: all views take the EXTRAS kernel (it tests the pointers)
+    for (int v = 0; v < b.n; v++) extras = extras || b.v[v].out_depth || b.v[v].out_alpha;
+    const dim3 grid(per_view, b.n);
+    if (extras) {
+        const size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<true>, (int)(per_view * b.n), 32 * BLEND_WARPS,
                                            sizeof(BlendSmem<FWD_K>));
-        blend_fwd_kernel<true><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
-                                                                     rec_by_id, W, H, gx, bg, final_T, n_contrib,
-                                                                     out_color, out_depth, out_alpha);
+        blend_fwd_kernel<true><<<grid, 32 * BLEND_WARPS, pad, s>>>(b);
     } else {
-        size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)blocks, 32 * BLEND_WARPS,
+        size_t pad = spread_pad_smem((const void*)blend_fwd_kernel<false>, (int)(per_view * b.n), 32 * BLEND_WARPS,
                                      sizeof(BlendSmem<FWD_K>));
 #ifdef DAS3R_BLEND_TIMING  // occupancy experiments
         if (const char* ex = getenv("DAS3R_BLEND_EXTRA_SMEM")) {
@@ -1236,9 +1268,7 @@ cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, cons
             cudaFuncSetAttribute(blend_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
         }
 #endif
-        blend_fwd_kernel<false><<<blocks, 32 * BLEND_WARPS, pad, s>>>(ranges, rect_off, rect_cnt, rect_list, sA, sBC,
-                                                                      rec_by_id, W, H, gx, bg, final_T, n_contrib,
-                                                                      out_color, out_depth, out_alpha);
+        blend_fwd_kernel<false><<<grid, 32 * BLEND_WARPS, pad, s>>>(b);
     }
     return cudaGetLastError();
 }

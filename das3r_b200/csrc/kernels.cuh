@@ -71,11 +71,55 @@ struct MultiBwdView {
     int pad_;
 };
 struct MultiBwdArgs {
-    int P, n_views, accumulate, pad_;
+    int P, n_views;
+    int accumulate_shared;  // the summed outputs: 1 = add to what the buffers hold (and leave unrendered Gaussians alone)
+    int accumulate_view;    // the per-view outputs (MultiBwdView::dL_dmeans3D / dL_drots), likewise
+    int D;                  // active SH degree 0..3 (rows of `shs` always have 16 coefficients)
+    int dsh_coeffs;         // coefficients per row of dL_dsh: (D+1)^2 .. 16 (rows trimmed to the active bands or full)
     const float* shs;  // [P,16,3], shared by all views
     float *dL_dopacity, *dL_dmeans3D, *dL_dsh, *dL_dscales, *dL_drots;
     MultiBwdView v[MV_MAX_VIEWS];
 };
+
+// Batched binning + blend (forward.cu, backward.cu): the per-view pointers of up to RB_MAX_VIEWS views that share P and
+// the image size; every stage is ONE launch with blockIdx.y = view.
+constexpr int RB_MAX_VIEWS = 16;
+struct ViewBin {
+    // image blob
+    uint32_t* tile_counts;
+    uint2* ranges;
+    uint32_t* cursors;
+    uint32_t* totals;  // {num_rendered, largest tile, 0, 0}
+    float* final_T;
+    uint32_t* n_contrib;
+    // geometry blob + the forward's radii
+    const GaussRec* rec;
+    const int* radii;
+    const uint32_t* tiles_touched;
+    // binning blob
+    uint64_t* unsorted;
+    uint32_t* point_list;
+    float4* sA;
+    float4* sBC;
+    uint32_t* rect_off;
+    uint32_t* rect_cnt;
+    uint2* rect_list;
+    uint64_t* keys_sorted;  // debug only
+    // per-view inputs / outputs of the blends
+    const float* bg;
+    float* out_color;
+    float* out_depth;
+    float* out_alpha;
+    const float* dL_dpix;
+    float* acc;
+};
+struct BatchArgs {
+    int n, P, W, H;
+    unsigned gx, gy;
+    int T, pad_;
+    ViewBin v[RB_MAX_VIEWS];
+};
+static_assert(sizeof(BatchArgs) <= 4000, "BatchArgs must fit the 4 KB kernel parameter space");
 
 // Fused DAS3R render front-end (frontend.cu, include/das3r_frontend.h)
 constexpr int FE_MAX_VIEWS = 16;
@@ -135,33 +179,23 @@ cudaError_t launch_adam(const AdamArgs& a, int total_blocks, cudaStream_t s);
 // forward.cu
 cudaError_t launch_preprocess_fwd(const PreFwdArgs& a, bool stage_sh, cudaStream_t s);
 cudaError_t launch_preprocess_fwd_multi(const MultiFwdArgs& m, cudaStream_t s);
-cudaError_t launch_tile_scan(const uint32_t* counts, int T, uint2* ranges, uint32_t* cursors, uint32_t* totals,
-                             cudaStream_t s);
-cudaError_t launch_scatter(int P, unsigned gx, unsigned gy, const GaussRec* rec, const int* radii,
-                           const uint32_t* tiles_touched, uint32_t* cursors, uint64_t* unsorted, cudaStream_t s);
-// Per-tile sort + tile-ordered record streams. Tiles with more than tile_sort_capacity() entries need `temp`
-// (tile_sort_fallback_bytes(R, T) bytes) for the library segmented sort that handles just them.
+// Binning and blend stages, batched over the views of `b` (one launch per stage, blockIdx.y = view).
+cudaError_t launch_tile_scan(const BatchArgs& b, cudaStream_t s);
+cudaError_t launch_scatter(const BatchArgs& b, cudaStream_t s);
+// Per-tile sort + tile-ordered record streams. max_count = largest tile over all views. A view whose largest tile has
+// more than tile_sort_capacity() entries needs temp[v] (tile_sort_fallback_bytes(R_v, T) bytes) for the library
+// segmented sort that handles just those tiles; R[v] = that view's num_rendered.
 int tile_sort_capacity();
 size_t tile_sort_fallback_bytes(int R, int T);
-cudaError_t launch_tile_sort(int R, int T, uint32_t max_count, const uint2* ranges, uint64_t* unsorted,
-                             const GaussRec* rec, uint32_t* point_list, float4* sA, float4* sBC, uint64_t* keys_sorted,
-                             void* temp, size_t temp_bytes, cudaStream_t s);
-cudaError_t launch_rect_lists(int T, unsigned gx, int W, int H, const uint2* ranges, const float4* sA,
-                              const float4* sBC, uint32_t* rect_off, uint32_t* rect_cnt, uint2* rect_list,
-                              cudaStream_t s);
-cudaError_t launch_blend_fwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
-                             const GaussRec* rec_by_id, int W, int H, const float* bg, float* final_T,
-                             uint32_t* n_contrib, float* out_color, float* out_depth, float* out_alpha,
-                             cudaStream_t s);
+cudaError_t launch_tile_sort(const BatchArgs& b, uint32_t max_count, const int* R, const uint32_t* view_max,
+                             void* const* temp, const size_t* temp_bytes, cudaStream_t s);
+cudaError_t launch_rect_lists(const BatchArgs& b, cudaStream_t s);
+cudaError_t launch_blend_fwd(const BatchArgs& b, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means, const float* view, const float* proj, uint8_t* present,
                                 cudaStream_t s);
 
 // backward.cu
-cudaError_t launch_blend_bwd(unsigned gx, unsigned gy, const uint2* ranges, const uint32_t* rect_off,
-                             const uint32_t* rect_cnt, const uint2* rect_list, const float4* sA, const float4* sBC,
-                             int W, int H, const float* bg, const float* final_T, const uint32_t* n_contrib,
-                             const float* dL_dpix, float* acc, cudaStream_t s);
+cudaError_t launch_blend_bwd(const BatchArgs& b, cudaStream_t s);
 cudaError_t launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t s);
 cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s);
 

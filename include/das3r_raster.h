@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define DAS3R_ABI_VERSION 1
+#define DAS3R_ABI_VERSION 2
 
 #define DAS3R_OK 0
 #define DAS3R_EINVAL (-1)   /* bad argument (shape, null, size) */
@@ -64,7 +64,7 @@ typedef struct das3r_raster_inputs {
     const float* colors_precomp; /* [P,3] or NULL */
     const float* opacities;      /* [P] */
     const float* scales;         /* [P,3] or NULL */
-    const float* rotations;      /* [P,4] or NULL (used un-normalised, forward.cu:127) */
+    const float* rotations;      /* [P,4] or NULL (used un-normalised, forward.cu:127); 16-byte aligned */
     const float* cov3D_precomp;  /* [P,6] or NULL */
 } das3r_raster_inputs;
 
@@ -95,8 +95,9 @@ typedef struct das3r_raster_grads {
     float* dL_dcov3D;      /* [P,6]; may be NULL = not wanted */
     float* dL_dsh;         /* [P,M,3] or NULL when M == 0 */
     float* dL_dscales;     /* [P,3] */
-    float* dL_drotations;  /* [P,4] */
-    float* scratch;        /* device scratch, das3r_raster_backward_scratch_bytes(P) bytes; contents undefined */
+    float* dL_drotations;  /* [P,4]; 16-byte aligned */
+    float* scratch;        /* device scratch, das3r_raster_backward_scratch_bytes(P) bytes, 16-byte aligned; contents
+                              undefined */
     int32_t accumulate;    /* 0: every gradient element is overwritten (reference behaviour: fresh zero-filled
                               tensors). 1: gradients are ADDED to what the buffers hold and Gaussians that were not
                               rendered are left untouched - used to sum several views of a step without a second pass
@@ -151,6 +152,15 @@ typedef struct das3r_raster_fwd_view {
 int das3r_raster_forward_preprocess(int32_t n_views, const das3r_raster_fwd_view* views, void* stream);
 int das3r_raster_forward_render(const das3r_raster_fwd_view* view, void* stream);
 
+/* Second half for n >= 1 views in ONE call (no reference counterpart; the reference renders one view per call,
+ * rasterizer_impl.cu:277-336): a single host read-back fetches every view's num_rendered (the reference blocks once per
+ * view, rasterizer_impl.cu:281), then duplicateWithKeys / sort / identifyTileRanges / renderCUDA run as ONE launch per
+ * stage over all views (grid.y = view). Views that share P and the image size are batched, 16 at a time; the others are
+ * grouped by size. Every output is bit-identical to das3r_raster_forward_render. num_rendered[v] receives view v's count.
+ * Returns 0 or a negative code. */
+int das3r_raster_forward_render_batch(int32_t n_views, const das3r_raster_fwd_view* views, int32_t* num_rendered,
+                                      void* stream);
+
 /* Backward. Replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:55-84, rasterizer_impl.cu:340-434):
  * backward blend -> cov2D/projection/SH/cov3D gradients. `radii` is the forward's output. `dL_dpix` is [3,H,W]. */
 int das3r_raster_backward(const das3r_raster_params* params, const das3r_raster_inputs* in,
@@ -194,6 +204,26 @@ typedef struct das3r_raster_view {
 int das3r_raster_backward_blend(const das3r_raster_view* view, void* stream);
 int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* grads,
                                  void* stream);
+
+/* The blend half for n >= 1 views in ONE launch (grid.y = view; views grouped by P and image size, 16 per launch).
+ * Same results as n das3r_raster_backward_blend calls. No reference counterpart (renderCUDA, backward.cu:399-557, is
+ * launched once per view). */
+int das3r_raster_backward_blend_batch(int32_t n_views, const das3r_raster_view* views, void* stream);
+
+/* das3r_raster_backward_finish with two extras (no reference counterpart):
+ *   dsh_coeffs   coefficients per ROW of grads->dL_dsh: M (the reference's [P,M,3] layout, rasterize_points.cu:156; 0
+ *                means M) down to (D+1)^2. At active degree D only the first (D+1)^2 coefficients of a gradient row can
+ *                be non-zero (backward.cu:62-137); DAS3R trains at D = 0 for 3000 of 4000 iterations
+ *                (train_gui.py:541-543), where a trimmed row is 12 bytes instead of 192 - less to write, and less to
+ *                all-reduce in the data-parallel step. Trimmed rows need the fused path (views sharing 16-coefficient,
+ *                16-byte aligned shs, scale / rotation inputs).
+ *   first, count only Gaussians [first, first + count) are processed (count < 0: to the end): the caller can hand a
+ *                finished slice of the gradient buffers to a collective while the next slice is computed. grads and the
+ *                per-view outputs are still addressed by ABSOLUTE Gaussian index (row `first` is the first one written).
+ * Alignment: rotations, dL_drotations (shared and per-view) and the accumulators must be 16-byte aligned (float4
+ * accesses); violations are refused with DAS3R_EINVAL. */
+int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* grads,
+                                    int32_t dsh_coeffs, int32_t first, int32_t count, void* stream);
 
 /* Backward for hosts that cannot allocate device memory. It has no counterpart in the reference.
  *

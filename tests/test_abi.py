@@ -43,7 +43,7 @@ def test_every_entry_point_cites_the_reference():
 
 def test_version_and_error_string():
     lib = Hn.cabi()
-    assert lib.das3r_abi_version() == 1
+    assert lib.das3r_abi_version() == 2
     assert lib.das3r_last_error() in (b"",) or isinstance(lib.das3r_last_error(), bytes)
 
 
