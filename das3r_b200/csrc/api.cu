@@ -917,20 +917,29 @@ static bool frontend_model_ok(const das3r_frontend_model* m) {
                           m->conf_static && ((reinterpret_cast<uintptr_t>(m->rotation) & 15) == 0)));
 }
 
-int das3r_frontend_forward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
-                           const das3r_frontend_outputs* out, void* stream_v) {
+static int frontend_rows(const das3r_frontend_model* model, const das3r_frontend_options* opt) {
+    return (opt && opt->filter_index) ? opt->n_rows : model->P;
+}
+
+int das3r_frontend_forward_ex(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                              const das3r_frontend_outputs* out, const das3r_frontend_options* opt, void* stream_v) {
     g_err.clear();
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (!frontend_model_ok(model) || !out || n_views < 1 || n_views > DAS3R_FRONTEND_MAX_VIEWS || !poses)
         return fail_msg(DAS3R_EINVAL, "frontend_forward: null or invalid argument (1..16 views, rotation 16-byte aligned)");
-    if (model->P == 0) return DAS3R_OK;
+    const int D = opt ? opt->sh_degree : 3;
+    if (D < 0 || D > 3) return fail_msg(DAS3R_EINVAL, "frontend_forward: sh_degree must be 0..3");
+    const int rows = frontend_rows(model, opt);
+    if (rows < 0) return fail_msg(DAS3R_EINVAL, "frontend_forward: negative n_rows");
+    if (rows == 0) return DAS3R_OK;
     if (!out->opacity || !out->scales || !out->shs) return fail_msg(DAS3R_EINVAL, "frontend_forward: null output");
     FrontendFwdArgs a;
     memset(&a, 0, sizeof(a));
-    a.P = model->P; a.n_views = n_views;
+    a.P = rows; a.n_views = n_views; a.K = (D + 1) * (D + 1);
     a.xyz = model->xyz; a.rotation = model->rotation; a.opacity_raw = model->opacity; a.scaling_raw = model->scaling;
     a.features_dc = model->features_dc; a.features_rest = model->features_rest; a.conf_static = model->conf_static;
     a.conf_index = model->conf_index; a.poses = poses;
+    a.filter_index = opt ? opt->filter_index : nullptr;
     a.opacity = out->opacity; a.scales = out->scales; a.shs = out->shs;
     for (int v = 0; v < n_views; v++) {
         if (!out->means3D[v] || !out->rotations[v] || (reinterpret_cast<uintptr_t>(out->rotations[v]) & 15))
@@ -944,31 +953,53 @@ int das3r_frontend_forward(const das3r_frontend_model* model, int32_t n_views, c
     return DAS3R_OK;
 }
 
+int das3r_frontend_forward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                           const das3r_frontend_outputs* out, void* stream_v) {
+    return das3r_frontend_forward_ex(model, n_views, poses, out, nullptr, stream_v);
+}
+
 size_t das3r_frontend_backward_scratch_bytes(int32_t P, int32_t n_views) {
     return frontend_backward_scratch_bytes(P > 0 ? P : 0, n_views > 0 ? n_views : 0);
 }
 
-int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
-                            const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout, void* stream_v) {
+int das3r_frontend_backward_ex(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                               const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout,
+                               const das3r_frontend_options* opt, void* stream_v) {
     g_err.clear();
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (!frontend_model_ok(model) || !gin || !gout || n_views < 1 || n_views > DAS3R_FRONTEND_MAX_VIEWS || !poses)
         return fail_msg(DAS3R_EINVAL, "frontend_backward: null or invalid argument (1..16 views)");
     if (!gout->dL_dposes) return fail_msg(DAS3R_EINVAL, "frontend_backward: dL_dposes is null");
-    if (model->P == 0) {
+    const int D = opt ? opt->sh_degree : 3;
+    if (D < 0 || D > 3) return fail_msg(DAS3R_EINVAL, "frontend_backward: sh_degree must be 0..3");
+    const int K = (D + 1) * (D + 1);
+    const int dsh = (opt && opt->dsh_coeffs > 0) ? opt->dsh_coeffs : 16;
+    const int rest = (opt && opt->rest_coeffs > 0) ? opt->rest_coeffs : ((opt && opt->rest_coeffs < 0) ? K - 1 : 15);
+    if (dsh < K || dsh > 16 || (rest != 15 && rest != K - 1))
+        return fail_msg(DAS3R_EINVAL, "frontend_backward: dsh_coeffs must be (D+1)^2..16 and rest_coeffs 15 or (D+1)^2-1");
+    const int rows = frontend_rows(model, opt);
+    const int first = opt ? opt->first : 0;
+    int count = opt ? opt->count : -1;
+    const bool finish = opt ? opt->finish_poses != 0 : true;
+    if (rows < 0 || first < 0 || first > rows || (first % 256) != 0)
+        return fail_msg(DAS3R_EINVAL, "frontend_backward: bad row range (first must be a multiple of 256 within the rows)");
+    if (count < 0 || first + count > rows) count = rows - first;
+    if (rows == 0) {
         cudaError_t e = cudaMemsetAsync(gout->dL_dposes, 0, sizeof(float) * 7 * n_views, stream);
         if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_backward memset", e);
         return DAS3R_OK;
     }
     if (!gin->dL_dopacity || !gin->dL_dscales || !gin->dL_dshs || !gout->dL_dxyz || !gout->dL_drotation ||
-        !gout->dL_dopacity || !gout->dL_dscaling || !gout->dL_dfeatures_dc || !gout->dL_dfeatures_rest ||
+        !gout->dL_dopacity || !gout->dL_dscaling || !gout->dL_dfeatures_dc || (!gout->dL_dfeatures_rest && rest > 0) ||
         !gout->dL_dconf || !gout->scratch || (reinterpret_cast<uintptr_t>(gout->dL_drotation) & 15))
         return fail_msg(DAS3R_EINVAL, "frontend_backward: null or misaligned buffer");
     FrontendBwdArgs a;
     memset(&a, 0, sizeof(a));
-    a.P = model->P; a.n_views = n_views;
+    a.P = rows; a.n_views = n_views; a.K = K; a.dsh_coeffs = dsh; a.rest_coeffs = rest;
+    a.row0 = first; a.row_end = first + count;
     a.xyz = model->xyz; a.rotation = model->rotation; a.opacity_raw = model->opacity; a.scaling_raw = model->scaling;
     a.conf_static = model->conf_static; a.conf_index = model->conf_index; a.poses = poses;
+    a.filter_index = opt ? opt->filter_index : nullptr;
     a.dL_dopacity = gin->dL_dopacity; a.dL_dscales = gin->dL_dscales; a.dL_dshs = gin->dL_dshs;
     for (int v = 0; v < n_views; v++) {
         if (!gin->dL_dmeans3D[v] || !gin->dL_drotations[v] || (reinterpret_cast<uintptr_t>(gin->dL_drotations[v]) & 15))
@@ -980,10 +1011,15 @@ int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, 
     a.dL_dscaling_raw = gout->dL_dscaling; a.dL_dfeatures_dc = gout->dL_dfeatures_dc;
     a.dL_dfeatures_rest = gout->dL_dfeatures_rest; a.dL_dconf = gout->dL_dconf;
     a.partials = gout->scratch;
-    cudaError_t e = launch_frontend_bwd(a, gout->dL_dposes, stream);
-    g_launches += 2;
+    cudaError_t e = launch_frontend_bwd(a, finish ? gout->dL_dposes : nullptr, stream);
+    g_launches += (count > 0 ? 1 : 0) + (finish ? 1 : 0);
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_bwd", e);
     return DAS3R_OK;
+}
+
+int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                            const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout, void* stream_v) {
+    return das3r_frontend_backward_ex(model, n_views, poses, gin, gout, nullptr, stream_v);
 }
 
 

@@ -86,19 +86,31 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_fwd_kernel(const __grid_c
     const int idx = base + tid;
     const int nvalid = min(FE_THREADS, a.P - base);
     if (tid < a.n_views) pose_to_smem(a.poses + 7 * tid, s_pose + FE_POSE_F * tid);
-    sh_rows_copy<true>(a.features_dc, a.features_rest, a.shs, base, nvalid);
+    // all 16 coefficients, no row selection: block-cooperative flat copy; otherwise every thread copies the active
+    // coefficients of its own row (the rasterizer never reads the bands above the active degree)
+    const bool flat = a.K == 16 && a.filter_index == nullptr;
+    if (flat) sh_rows_copy<true>(a.features_dc, a.features_rest, a.shs, base, nvalid);
     __syncthreads();
     if (idx >= a.P) return;
+    // gaussian_renderer/__init__.py:85-86,:95,:107,:126: `[filtering]` selects model rows; output row idx = model row src
+    const size_t src = a.filter_index ? (size_t)a.filter_index[idx] : (size_t)idx;
+    if (!flat) {
+        float* row = a.shs + (size_t)idx * 48;
+#pragma unroll
+        for (int j = 0; j < 3; j++) row[j] = a.features_dc[src * 3 + j];
+        const int nrest = 3 * (a.K - 1);
+        for (int j = 0; j < nrest; j++) row[3 + j] = a.features_rest[src * 45 + j];
+    }
 
     // activations (scene/gaussian_model.py:103-105,:193-194; gaussian_renderer/__init__.py:95-97)
-    const float o = a.opacity_raw[idx];
+    const float o = a.opacity_raw[src];
     const float conf = a.conf_static[a.conf_index ? a.conf_index[idx] : (int64_t)idx];
     a.opacity[idx] = (1.0f / (1.0f + expf(-o))) * conf;
 #pragma unroll
-    for (int k = 0; k < 3; k++) a.scales[3 * idx + k] = expf(a.scaling_raw[3 * idx + k]);
+    for (int k = 0; k < 3; k++) a.scales[3 * idx + k] = expf(a.scaling_raw[3 * src + k]);
 
-    const float X = a.xyz[3 * idx], Y = a.xyz[3 * idx + 1], Z = a.xyz[3 * idx + 2];
-    const float4 rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + idx);  // (w2, x2, y2, z2)
+    const float X = a.xyz[3 * src], Y = a.xyz[3 * src + 1], Z = a.xyz[3 * src + 2];
+    const float4 rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + src);  // (w2, x2, y2, z2)
 #pragma unroll 1
     for (int v = 0; v < a.n_views; v++) {
         const float* p = s_pose + FE_POSE_F * v;
@@ -161,29 +173,41 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
     __shared__ float s_pose[FE_MAX_VIEWS * FE_POSE_F];
     __shared__ float s_warp[FE_MAX_VIEWS][FE_THREADS / 32][FE_PART_F];  // per view: every warp's 16 sums
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int base = blockIdx.x * FE_THREADS;
+    const int base = a.row0 + blockIdx.x * FE_THREADS;
     const int idx = base + tid;
-    const int nvalid = min(FE_THREADS, a.P - base);
-    const bool in_range = idx < a.P;
+    const int nvalid = min(FE_THREADS, a.row_end - base);
+    const bool in_range = idx < a.row_end;
     if (tid < a.n_views) pose_to_smem(a.poses + 7 * tid, s_pose + FE_POSE_F * tid);
-    sh_rows_copy<false>(a.dL_dfeatures_dc, a.dL_dfeatures_rest, a.dL_dshs, base, nvalid);
+    const bool flat = a.K == 16 && a.dsh_coeffs == 16 && a.rest_coeffs == 15 && a.filter_index == nullptr;
+    if (flat) sh_rows_copy<false>(a.dL_dfeatures_dc, a.dL_dfeatures_rest, a.dL_dshs, base, nvalid);
     __syncthreads();
+    // output row idx of the forward = model row src (render()'s `[filtering]`); parameter gradients go to row src
+    const size_t src = (in_range && a.filter_index) ? (size_t)a.filter_index[idx] : (size_t)idx;
 
     float X = 0.f, Y = 0.f, Z = 0.f;
     float4 rq = {0.f, 0.f, 0.f, 0.f};
     if (in_range) {
+        if (!flat) {
+            // dL_dshs rows have dsh_coeffs coefficients of which K are active; the rest rows written have rest_coeffs
+            const float* g = a.dL_dshs + (size_t)idx * 3 * a.dsh_coeffs;
+#pragma unroll
+            for (int j = 0; j < 3; j++) a.dL_dfeatures_dc[src * 3 + j] = g[j];
+            const int nact = 3 * (a.K - 1), nrest = 3 * a.rest_coeffs;
+            float* r = a.dL_dfeatures_rest + src * (size_t)nrest;
+            for (int j = 0; j < nrest; j++) r[j] = (j < nact) ? g[3 + j] : 0.f;
+        }
         // activation derivatives
-        const float o = a.opacity_raw[idx];
+        const float o = a.opacity_raw[src];
         const float sg = 1.0f / (1.0f + expf(-o));
         const float conf = a.conf_static[a.conf_index ? a.conf_index[idx] : (int64_t)idx];
         const float go = a.dL_dopacity[idx];
-        a.dL_dopacity_raw[idx] = go * conf * sg * (1.0f - sg);
+        a.dL_dopacity_raw[src] = go * conf * sg * (1.0f - sg);
         a.dL_dconf[idx] = go * sg;
 #pragma unroll
         for (int k = 0; k < 3; k++)
-            a.dL_dscaling_raw[3 * idx + k] = a.dL_dscales[3 * idx + k] * expf(a.scaling_raw[3 * idx + k]);
-        X = a.xyz[3 * idx]; Y = a.xyz[3 * idx + 1]; Z = a.xyz[3 * idx + 2];
-        rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + idx);
+            a.dL_dscaling_raw[3 * src + k] = a.dL_dscales[3 * idx + k] * expf(a.scaling_raw[3 * src + k]);
+        X = a.xyz[3 * src]; Y = a.xyz[3 * src + 1]; Z = a.xyz[3 * src + 2];
+        rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + src);
     }
 
     float dX = 0.f, dY = 0.f, dZ = 0.f;
@@ -224,8 +248,8 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
         if ((lane & 1) == 0) s_warp[v][warp][pi] = ps;
     }
     if (in_range) {
-        a.dL_dxyz[3 * idx] = dX; a.dL_dxyz[3 * idx + 1] = dY; a.dL_dxyz[3 * idx + 2] = dZ;
-        reinterpret_cast<float4*>(a.dL_drotation)[idx] = dr;
+        a.dL_dxyz[3 * src] = dX; a.dL_dxyz[3 * src + 1] = dY; a.dL_dxyz[3 * src + 2] = dZ;
+        reinterpret_cast<float4*>(a.dL_drotation)[src] = dr;
     }
     // this block's partial sums -> scratch[block][view][16] (summed by frontend_pose_kernel)
     __syncthreads();
@@ -234,7 +258,7 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < FE_THREADS / 32; w++) t += s_warp[v][w][k];
-        a.partials[(size_t)blockIdx.x * a.n_views * FE_PART_F + e] = t;
+        a.partials[(size_t)(a.row0 / FE_THREADS + blockIdx.x) * a.n_views * FE_PART_F + e] = t;
     }
 }
 
@@ -281,11 +305,16 @@ size_t frontend_backward_scratch_bytes(int P, int n_views) {
 }
 
 cudaError_t launch_frontend_bwd(const FrontendBwdArgs& a, float* dL_dposes, cudaStream_t s) {
-    const int blocks = (a.P + FE_THREADS - 1) / FE_THREADS;
-    frontend_bwd_kernel<<<blocks, FE_THREADS, 0, s>>>(a);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    frontend_pose_kernel<<<a.n_views, FE_THREADS, 0, s>>>(a.partials, blocks, a.n_views, a.poses, dL_dposes);
+    const int blocks = (a.row_end - a.row0 + FE_THREADS - 1) / FE_THREADS;
+    if (blocks > 0) {
+        frontend_bwd_kernel<<<blocks, FE_THREADS, 0, s>>>(a);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (dL_dposes) {
+        const int all_blocks = (a.P + FE_THREADS - 1) / FE_THREADS;
+        frontend_pose_kernel<<<a.n_views, FE_THREADS, 0, s>>>(a.partials, all_blocks, a.n_views, a.poses, dL_dposes);
+    }
     return cudaGetLastError();
 }
 

@@ -125,16 +125,25 @@ static_assert(sizeof(BatchArgs) <= 4000, "BatchArgs must fit the 4 KB kernel par
 constexpr int FE_MAX_VIEWS = 16;
 struct FrontendFwdArgs {
     int P, n_views;
+    int K;  // active SH coefficients (D+1)^2: only these are copied into the joint [P,16,3] rows
+    int pad_;
     const float *xyz, *rotation, *opacity_raw, *scaling_raw, *features_dc, *features_rest, *conf_static, *poses;
     const int64_t* conf_index;
+    const int64_t* filter_index;  // optional [P]: model row of output row i (render()'s boolean `filtering`, as indices)
     float *opacity, *scales, *shs;
     float* means3D[FE_MAX_VIEWS];
     float* rotations[FE_MAX_VIEWS];
 };
 struct FrontendBwdArgs {
     int P, n_views;
+    int K;            // active SH coefficients
+    int dsh_coeffs;   // coefficients per row of the incoming dL_dshs (K..16)
+    int rest_coeffs;  // coefficients per row of the outgoing dL_dfeatures_rest (K-1 = trimmed, or 15)
+    int row0, row_end;  // output rows [row0, row_end) are processed by this launch (row0 a multiple of 256)
+    int pad_;
     const float *xyz, *rotation, *opacity_raw, *scaling_raw, *conf_static, *poses;
     const int64_t* conf_index;
+    const int64_t* filter_index;
     const float *dL_dopacity, *dL_dscales, *dL_dshs;
     const float* dL_dmeans3D[FE_MAX_VIEWS];
     const float* dL_drotations[FE_MAX_VIEWS];
@@ -143,6 +152,8 @@ struct FrontendBwdArgs {
 };
 cudaError_t launch_frontend_fwd(const FrontendFwdArgs& a, cudaStream_t s);
 size_t frontend_backward_scratch_bytes(int P, int n_views);
+// dL_dposes != NULL: also reduce the per-block partial sums of ALL ceil(P/256) blocks to the pose gradients (the last
+// range of a step)
 cudaError_t launch_frontend_bwd(const FrontendBwdArgs& a, float* dL_dposes, cudaStream_t s);
 
 // Fused photometric loss (loss.cu, include/das3r_loss.h)

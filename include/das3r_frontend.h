@@ -82,6 +82,38 @@ size_t das3r_frontend_backward_scratch_bytes(int32_t P, int32_t n_views);
 int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, const float* poses,
                             const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout, void* stream);
 
+/* Options of the _ex variants below (no reference counterpart beyond the lines cited). Zero-initialise, then set:
+ *   sh_degree     active SH degree D (pc.active_sh_degree, gaussian_renderer/__init__.py:73): only the (D+1)^2 active
+ *                 coefficients are copied into / out of the joint SH rows; the rasterizer never touches the others
+ *                 (forward.cu:20-71). Default 3.
+ *   filter_index  render()'s boolean `filtering` (gaussian_renderer/__init__.py:38-46,:85-86,:95,:107,:126) as the int64
+ *                 device array of selected model rows, n_rows entries; NULL = all rows (n_rows = model->P). Outputs of
+ *                 the forward have n_rows rows; the backward writes parameter gradients to the selected rows only (the
+ *                 caller zero-fills the gradient buffers). conf_index / conf_static are indexed by OUTPUT row, as the
+ *                 reference's `opacity * _conf_static[...]` product is.
+ *   dsh_coeffs    backward: coefficients per row of gin->dL_dshs, (D+1)^2 .. 16 (0 = 16), matching
+ *                 das3r_raster_backward_finish_ex.
+ *   rest_coeffs   backward: coefficients per row of gout->dL_dfeatures_rest: 15 (0 = 15; inactive bands written as zeros)
+ *                 or trimmed to the (D+1)^2 - 1 active ones for a gradient bucket that skips the zero bands (pass that
+ *                 number, or -1; at degree 0 the rows are empty and the pointer may be NULL).
+ *   first, count  backward: only output rows [first, first+count) (count < 0: to the end; first a multiple of 256).
+ *   finish_poses  backward: after this range, reduce the per-block partial sums of ALL rows to gout->dL_dposes (set on
+ *                 the last range of a step; every range must have been processed by then). */
+typedef struct das3r_frontend_options {
+    int32_t sh_degree;
+    int32_t n_rows;
+    const int64_t* filter_index;
+    int32_t dsh_coeffs, rest_coeffs;
+    int32_t first, count;
+    int32_t finish_poses;
+} das3r_frontend_options;
+
+int das3r_frontend_forward_ex(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                              const das3r_frontend_outputs* out, const das3r_frontend_options* opt, void* stream);
+int das3r_frontend_backward_ex(const das3r_frontend_model* model, int32_t n_views, const float* poses,
+                               const das3r_frontend_grads_in* gin, const das3r_frontend_grads_out* gout,
+                               const das3r_frontend_options* opt, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
