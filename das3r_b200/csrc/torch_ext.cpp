@@ -442,7 +442,112 @@ static std::tuple<int, torch::Tensor> ForwardRenderCUDA(const torch::Tensor& bac
     return std::make_tuple(R, binA.t);
 }
 
+// Second half for ALL views (current stream): views = (bg, color, radii, geomBuffer, imgBuffer) per view as returned by
+// forward_preprocess; -> per view (num_rendered, binningBuffer). One host read-back, one launch per stage.
+using RenderView = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>;
+static std::vector<std::tuple<int, torch::Tensor>> ForwardRenderBatchCUDA(const std::vector<RenderView>& views,
+                                                                          const bool debug) {
+    TORCH_CHECK(!views.empty(), "no views");
+    const auto dev = std::get<1>(views[0]).device();
+    TORCH_CHECK(dev.is_cuda(), "color must be a CUDA tensor: this rasterizer has no CPU path");
+    c10::cuda::CUDAGuard guard(dev);
+    const size_t n = views.size();
+    std::vector<das3r_raster_params> ps(n);
+    std::vector<das3r_raster_outputs> outs(n);
+    std::vector<das3r_raster_state> sts(n);
+    std::vector<das3r_raster_fwd_view> vs(n);
+    std::vector<BlobAlloc> binA(n);
+    std::vector<torch::Tensor> keep;
+    for (size_t i = 0; i < n; i++) {
+        const auto& color = std::get<1>(views[i]);
+        const auto& radii = std::get<2>(views[i]);
+        const auto& geom = std::get<3>(views[i]);
+        const auto& img = std::get<4>(views[i]);
+        TORCH_CHECK(color.is_cuda() && color.dim() == 3, "color must be the [3,H,W] tensor forward_preprocess returned");
+        auto bg = prep(std::get<0>(views[i]), "bg", dev);
+        keep.push_back(bg);
+        memset(&ps[i], 0, sizeof(ps[i]));
+        ps[i].P = (int32_t)radii.size(0);
+        ps[i].height = (int32_t)color.size(1);
+        ps[i].width = (int32_t)color.size(2);
+        ps[i].debug = debug;
+        ps[i].background = fptr(bg);
+        memset(&outs[i], 0, sizeof(outs[i]));
+        outs[i].out_color = color.data_ptr<float>();
+        outs[i].radii = radii.numel() ? radii.data_ptr<int>() : nullptr;
+        memset(&sts[i], 0, sizeof(sts[i]));
+        sts[i].geom = geom.numel() ? reinterpret_cast<char*>(geom.data_ptr()) : nullptr;
+        sts[i].geom_bytes = geom.numel();
+        sts[i].image = img.numel() ? reinterpret_cast<char*>(img.data_ptr()) : nullptr;
+        sts[i].image_bytes = img.numel();
+        binA[i].opts = torch::TensorOptions().dtype(torch::kByte).device(dev);
+        memset(&vs[i], 0, sizeof(vs[i]));
+        vs[i].params = &ps[i]; vs[i].out = &outs[i]; vs[i].state = &sts[i];
+        vs[i].binning_alloc = &BlobAlloc::fn; vs[i].binning_ctx = &binA[i];
+    }
+    std::vector<int32_t> R(n, 0);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    check(das3r_raster_forward_render_batch((int32_t)n, vs.data(), R.data(), stream),
+          "rasterize_gaussians_forward_render_batch");
+    std::vector<std::tuple<int, torch::Tensor>> res;
+    for (size_t i = 0; i < n; i++) {
+        if (!binA[i].t.defined()) binA[i].t = torch::empty({0}, binA[i].opts);
+        res.emplace_back((int)R[i], binA[i].t);
+    }
+    return res;
+}
+
 // ---- split / multi-view backward (das3r_raster_backward_blend / _finish; no reference counterpart) --------------
+// First half for ALL views in one launch: views = (bg, dL_dout_color, geomBuffer, R, binningBuffer, imgBuffer);
+// -> per view the [P,12] accumulator tensor the finish half reads.
+using BlendViewT = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, int, torch::Tensor, torch::Tensor>;
+static std::vector<torch::Tensor> BackwardBlendBatchCUDA(const std::vector<BlendViewT>& views, const int P,
+                                                         const bool debug) {
+    TORCH_CHECK(!views.empty(), "no views");
+    const auto dev = std::get<1>(views[0]).device();
+    TORCH_CHECK(dev.is_cuda(), "dL_dout_color must be a CUDA tensor: this rasterizer has no CPU path");
+    c10::cuda::CUDAGuard guard(dev);
+    const size_t n = views.size();
+    std::vector<das3r_raster_params> ps(n);
+    std::vector<das3r_raster_state> sts(n);
+    std::vector<das3r_raster_view> vs(n);
+    std::vector<torch::Tensor> keep, accs;
+    for (size_t i = 0; i < n; i++) {
+        auto bg = prep(std::get<0>(views[i]), "bg", dev);
+        auto dL = prep(std::get<1>(views[i]), "dL_dout_color", dev);
+        TORCH_CHECK(dL.dim() == 3 && dL.size(0) == 3, "dL_dout_color must be [3,H,W]");
+        keep.push_back(bg);
+        keep.push_back(dL);
+        const auto& geom = std::get<2>(views[i]);
+        const auto& binning = std::get<4>(views[i]);
+        const auto& img = std::get<5>(views[i]);
+        accs.push_back(torch::empty({(long long)P, 12}, torch::TensorOptions().dtype(torch::kFloat32).device(dev)));
+        memset(&ps[i], 0, sizeof(ps[i]));
+        ps[i].P = P;
+        ps[i].height = (int32_t)dL.size(1);
+        ps[i].width = (int32_t)dL.size(2);
+        ps[i].debug = debug;
+        ps[i].background = fptr(bg);
+        memset(&sts[i], 0, sizeof(sts[i]));
+        sts[i].geom = geom.numel() ? reinterpret_cast<char*>(geom.data_ptr()) : nullptr;
+        sts[i].geom_bytes = geom.numel();
+        sts[i].binning = binning.numel() > 0 ? reinterpret_cast<char*>(binning.data_ptr()) : nullptr;
+        sts[i].binning_bytes = binning.numel();
+        sts[i].image = img.numel() ? reinterpret_cast<char*>(img.data_ptr()) : nullptr;
+        sts[i].image_bytes = img.numel();
+        sts[i].num_rendered = std::get<3>(views[i]);
+        memset(&vs[i], 0, sizeof(vs[i]));
+        vs[i].params = &ps[i];
+        vs[i].state = &sts[i];
+        vs[i].dL_dpix = dL.data_ptr<float>();
+        vs[i].scratch = P > 0 ? accs.back().data_ptr<float>() : nullptr;
+    }
+    if (P == 0) return accs;
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    check(das3r_raster_backward_blend_batch((int32_t)n, vs.data(), stream), "rasterize_gaussians_backward_blend_batch");
+    return accs;
+}
+
 // First half for one view: returns the [P,12] float32 accumulator tensor the finish half reads.
 static torch::Tensor BackwardBlendCUDA(const torch::Tensor& background, const torch::Tensor& dL_dout_color_, const int P,
                                        const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
@@ -489,9 +594,12 @@ using FinishView = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch
 
 // Second half for all views of a step: outs = {dL_dopacity [P,1], dL_dmeans3D [P,3], dL_dsh [P,M,3], dL_dscales [P,3],
 // dL_drotations [P,4]} receive (accumulate: are increased by) the sum over the views.
-static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch::Tensor& sh_, const int degree,
-                               const float scale_modifier, const std::vector<torch::Tensor>& outs,
-                               const bool accumulate, const bool debug) {
+// dsh_coeffs: coefficients per row of outs[2] (0 = M: the reference's [P,M,3]; (degree+1)^2 = rows trimmed to the active
+// bands). first/count: only Gaussians [first, first+count) are processed (count < 0: to the end).
+static void BackwardFinishExCUDA(const std::vector<FinishView>& views, const torch::Tensor& sh_, const int degree,
+                                 const float scale_modifier, const std::vector<torch::Tensor>& outs,
+                                 const bool accumulate, const bool debug, const int dsh_coeffs_, const int first,
+                                 const int count) {
     TORCH_CHECK(!views.empty(), "no views");
     TORCH_CHECK(outs.size() == 5, "expected 5 gradient tensors (opacity, means3D, sh, scales, rotations)");
     const auto dev = std::get<0>(views[0]).device();
@@ -500,7 +608,8 @@ static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch
     const int P = std::get<0>(views[0]).size(0);
     int M = 0;
     if (sh_.defined() && sh_.dim() == 3) M = sh_.size(1);
-    const int64_t want[5] = {(int64_t)P, 3LL * P, 3LL * M * P, 3LL * P, 4LL * P};
+    const int dsh_coeffs = dsh_coeffs_ > 0 ? dsh_coeffs_ : M;
+    const int64_t want[5] = {(int64_t)P, 3LL * P, 3LL * dsh_coeffs * P, 3LL * P, 4LL * P};
     for (int i = 0; i < 5; i++)
         TORCH_CHECK(outs[i].is_cuda() && outs[i].device() == dev && outs[i].scalar_type() == torch::kFloat32 &&
                         outs[i].is_contiguous() && outs[i].numel() == want[i],
@@ -568,7 +677,14 @@ static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch
     g.dL_drotations = outs[4].data_ptr<float>();
     g.accumulate = accumulate ? 1 : 0;
     cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
-    check(das3r_raster_backward_finish((int32_t)n, vs.data(), &g, stream), "rasterize_gaussians_backward_finish");
+    check(das3r_raster_backward_finish_ex((int32_t)n, vs.data(), &g, dsh_coeffs, first, count, stream),
+          "rasterize_gaussians_backward_finish");
+}
+
+static void BackwardFinishCUDA(const std::vector<FinishView>& views, const torch::Tensor& sh_, const int degree,
+                               const float scale_modifier, const std::vector<torch::Tensor>& outs,
+                               const bool accumulate, const bool debug) {
+    BackwardFinishExCUDA(views, sh_, degree, scale_modifier, outs, accumulate, debug, 0, 0, -1);
 }
 
 // ---- fused DAS3R render front-end (include/das3r_frontend.h) ------------------------------------------------------
@@ -589,9 +705,10 @@ static void fill_model(das3r_frontend_model& m, const torch::Tensor& xyz, const 
 
 static void check_model(const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity,
                         const torch::Tensor& scaling, const torch::Tensor& conf_static, const torch::Tensor& conf_index,
-                        const torch::Tensor& poses) {
+                        const torch::Tensor& poses, int64_t rows = -1) {
     TORCH_CHECK(xyz.is_cuda(), "xyz must be a CUDA tensor: the front-end has no CPU path");
     const int64_t P = xyz.size(0);
+    if (rows < 0) rows = P;  // output rows: fewer than P when render()'s `filtering` selects a subset
     auto ok = [&](const torch::Tensor& t, int64_t n) {
         return t.is_cuda() && t.device() == xyz.device() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() &&
                t.numel() == n;
@@ -602,25 +719,34 @@ static void check_model(const torch::Tensor& xyz, const torch::Tensor& rotation,
                 "conf_static must be a contiguous float32 CUDA tensor");
     if (conf_index.defined() && conf_index.numel()) {
         TORCH_CHECK(conf_index.is_cuda() && conf_index.scalar_type() == torch::kInt64 && conf_index.is_contiguous() &&
-                        conf_index.numel() == P,
-                    "conf_index must be a contiguous int64 CUDA tensor with one entry per Gaussian");
+                        conf_index.numel() == rows,
+                    "conf_index must be a contiguous int64 CUDA tensor with one entry per (selected) Gaussian");
     } else {
-        TORCH_CHECK(conf_static.numel() >= P, "conf_static has fewer entries than there are Gaussians");
+        TORCH_CHECK(conf_static.numel() >= rows, "conf_static has fewer entries than there are (selected) Gaussians");
     }
     TORCH_CHECK(poses.is_cuda() && poses.scalar_type() == torch::kFloat32 && poses.is_contiguous() && poses.dim() == 2 &&
                     poses.size(1) == 7 && poses.size(0) >= 1 && poses.size(0) <= DAS3R_FRONTEND_MAX_VIEWS,
                 "poses must be a contiguous float32 CUDA tensor [V,7] with 1 <= V <= 16");
 }
 
+// sh_degree: active SH degree (only its (D+1)^2 coefficients are copied into the joint rows); filter_index: optional
+// int64 [rows] model rows selected by render()'s `filtering` (empty: all rows)
 static std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, std::vector<torch::Tensor>, std::vector<torch::Tensor>>
-FrontendForwardCUDA(const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity,
-                    const torch::Tensor& scaling, const torch::Tensor& f_dc, const torch::Tensor& f_rest,
-                    const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses) {
-    check_model(xyz, rotation, opacity, scaling, conf_static, conf_index, poses);
-    const int64_t P = xyz.size(0);
-    TORCH_CHECK(f_dc.is_cuda() && f_dc.is_contiguous() && f_dc.numel() == 3 * P && f_rest.is_cuda() &&
-                    f_rest.is_contiguous() && f_rest.numel() == 45 * P && f_dc.scalar_type() == torch::kFloat32 &&
-                    f_rest.scalar_type() == torch::kFloat32,
+FrontendForwardExCUDA(const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity,
+                      const torch::Tensor& scaling, const torch::Tensor& f_dc, const torch::Tensor& f_rest,
+                      const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses,
+                      const int sh_degree, const torch::Tensor& filter_index) {
+    const bool filtered = filter_index.defined() && filter_index.numel() > 0;
+    const int64_t Pm = xyz.size(0);
+    const int64_t P = filtered ? filter_index.numel() : Pm;
+    check_model(xyz, rotation, opacity, scaling, conf_static, conf_index, poses, P);
+    if (filtered) {
+        TORCH_CHECK(filter_index.is_cuda() && filter_index.scalar_type() == torch::kInt64 && filter_index.is_contiguous(),
+                    "filter_index must be a contiguous int64 CUDA tensor");
+    }
+    TORCH_CHECK(f_dc.numel() == 3 * Pm && f_rest.numel() == 45 * Pm, "features_dc [P,1,3] / features_rest [P,15,3] sizes");
+    TORCH_CHECK(f_dc.is_cuda() && f_dc.is_contiguous() && f_rest.is_cuda() && f_rest.is_contiguous() &&
+                    f_dc.scalar_type() == torch::kFloat32 && f_rest.scalar_type() == torch::kFloat32,
                 "features_dc [P,1,3] and features_rest [P,15,3] must be contiguous float32 CUDA tensors");
     c10::cuda::CUDAGuard guard(xyz.device());
     const int V = (int)poses.size(0);
@@ -640,20 +766,48 @@ FrontendForwardCUDA(const torch::Tensor& xyz, const torch::Tensor& rotation, con
     }
     das3r_frontend_model m;
     fill_model(m, xyz, rotation, opacity, scaling, f_dc, f_rest, conf_static, conf_index);
+    das3r_frontend_options opt;
+    memset(&opt, 0, sizeof(opt));
+    opt.sh_degree = sh_degree;
+    opt.n_rows = (int32_t)P;
+    opt.filter_index = filtered ? filter_index.data_ptr<int64_t>() : nullptr;
     cudaStream_t stream = c10::cuda::getCurrentCUDAStream(xyz.device().index()).stream();
-    check(das3r_frontend_forward(&m, V, poses.data_ptr<float>(), &out, stream), "frontend_forward");
+    check(das3r_frontend_forward_ex(&m, V, poses.data_ptr<float>(), &out, &opt, stream), "frontend_forward");
     return std::make_tuple(opac, scales, shs, means, rots);
 }
 
-static std::vector<torch::Tensor> FrontendBackwardCUDA(
+static std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, std::vector<torch::Tensor>, std::vector<torch::Tensor>>
+FrontendForwardCUDA(const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity,
+                    const torch::Tensor& scaling, const torch::Tensor& f_dc, const torch::Tensor& f_rest,
+                    const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses) {
+    return FrontendForwardExCUDA(xyz, rotation, opacity, scaling, f_dc, f_rest, conf_static, conf_index, poses, 3,
+                                 torch::Tensor());
+}
+
+// Backward of the front-end. outs: empty (the 8 gradient tensors are allocated: dxyz [P,3], drot [P,4], dop [P,1], dsc
+// [P,3], ddc [P,1,3], drest [P,15,3], dconf [rows], dposes [V,7]) or those 8 tensors provided by the caller (e.g. windows
+// of a gradient bucket; drest may be [P,(D+1)^2-1,3] = trimmed to the active bands; with filter_index the caller
+// zero-fills them). scratch: empty (allocated) or a uint8 tensor of das3r_frontend_backward_scratch_bytes(rows, V) bytes
+// that lives across the ranges of a step. first / count / finish_poses: see das3r_frontend_options.
+static std::vector<torch::Tensor> FrontendBackwardExCUDA(
     const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity, const torch::Tensor& scaling,
     const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses,
     const torch::Tensor& dL_dopacity, const torch::Tensor& dL_dscales, const torch::Tensor& dL_dshs,
-    const std::vector<torch::Tensor>& dL_dmeans, const std::vector<torch::Tensor>& dL_drots) {
-    check_model(xyz, rotation, opacity, scaling, conf_static, conf_index, poses);
-    const int64_t P = xyz.size(0);
+    const std::vector<torch::Tensor>& dL_dmeans, const std::vector<torch::Tensor>& dL_drots, const int sh_degree,
+    const torch::Tensor& filter_index, const std::vector<torch::Tensor>& outs_, const torch::Tensor& scratch_,
+    const int first, const int count, const bool finish_poses) {
+    const bool filtered = filter_index.defined() && filter_index.numel() > 0;
+    const int64_t Pm = xyz.size(0);
+    const int64_t P = filtered ? filter_index.numel() : Pm;
+    check_model(xyz, rotation, opacity, scaling, conf_static, conf_index, poses, P);
     const int V = (int)poses.size(0);
+    TORCH_CHECK(sh_degree >= 0 && sh_degree <= 3, "sh_degree must be 0..3");
+    const int K = (sh_degree + 1) * (sh_degree + 1);
     TORCH_CHECK((int)dL_dmeans.size() == V && (int)dL_drots.size() == V, "one dL_dmeans3D / dL_drotations per view");
+    if (filtered) {
+        TORCH_CHECK(filter_index.is_cuda() && filter_index.scalar_type() == torch::kInt64 && filter_index.is_contiguous(),
+                    "filter_index must be a contiguous int64 CUDA tensor");
+    }
     c10::cuda::CUDAGuard guard(xyz.device());
     const auto dev = xyz.device();
     auto o = xyz.options();
@@ -664,30 +818,53 @@ static std::vector<torch::Tensor> FrontendBackwardCUDA(
         keep.push_back(t.contiguous());
         return keep.back().data_ptr<float>();
     };
+    TORCH_CHECK(dL_dshs.numel() % (3 * std::max<int64_t>(P, 1)) == 0, "dL_dshs must be [rows, coeffs, 3]");
+    const int dsh = P > 0 ? (int)(dL_dshs.numel() / (3 * P)) : 16;
+    TORCH_CHECK(dsh >= K && dsh <= 16, "dL_dshs rows must have (D+1)^2 .. 16 coefficients");
     das3r_frontend_grads_in gin;
     memset(&gin, 0, sizeof(gin));
     gin.dL_dopacity = cg(dL_dopacity, P, "dL_dopacity");
     gin.dL_dscales = cg(dL_dscales, 3 * P, "dL_dscales");
-    gin.dL_dshs = cg(dL_dshs, 48 * P, "dL_dshs");
+    gin.dL_dshs = cg(dL_dshs, 3LL * dsh * P, "dL_dshs");
     for (int v = 0; v < V; v++) {
         gin.dL_dmeans3D[v] = cg(dL_dmeans[v], 3 * P, "dL_dmeans3D");
         gin.dL_drotations[v] = cg(dL_drots[v], 4 * P, "dL_drotations");
     }
-    auto dxyz = torch::empty({P, 3}, o), drot = torch::empty({P, 4}, o), dop = torch::empty({P, 1}, o);
-    auto dsc = torch::empty({P, 3}, o), ddc = torch::empty({P, 1, 3}, o), drest = torch::empty({P, 15, 3}, o);
-    auto dconf = torch::empty({P}, o), dposes = torch::empty({V, 7}, o);
-    auto scratch = torch::empty({(long long)das3r_frontend_backward_scratch_bytes((int32_t)P, V)},
-                                torch::TensorOptions().dtype(torch::kByte).device(dev));
+    std::vector<torch::Tensor> outs = outs_;
+    if (outs.empty()) {
+        auto mk = [&](std::initializer_list<int64_t> shape) {
+            return filtered ? torch::zeros(shape, o) : torch::empty(shape, o);
+        };
+        outs = {mk({Pm, 3}), mk({Pm, 4}), mk({Pm, 1}), mk({Pm, 3}), mk({Pm, 1, 3}), mk({Pm, 15, 3}),
+                torch::empty({P}, o), torch::empty({V, 7}, o)};
+    }
+    TORCH_CHECK(outs.size() == 8, "expected 8 gradient tensors");
+    const int64_t rest_numel = outs[5].defined() ? outs[5].numel() : 0;
+    TORCH_CHECK(rest_numel == 45 * Pm || rest_numel == 3LL * (K - 1) * Pm,
+                "dL_dfeatures_rest must be [P,15,3] or trimmed to [P,(D+1)^2-1,3]");
+    const int rest = rest_numel == 45 * Pm ? 15 : K - 1;
+    const int64_t want[8] = {3 * Pm, 4 * Pm, Pm, 3 * Pm, 3 * Pm, rest_numel, P, 7LL * V};
+    for (int i = 0; i < 8; i++) {
+        if (i == 5 && rest_numel == 0) continue;
+        TORCH_CHECK(outs[i].is_cuda() && outs[i].device() == dev && outs[i].scalar_type() == torch::kFloat32 &&
+                        outs[i].is_contiguous() && outs[i].numel() == want[i],
+                    "gradient tensor ", i, " must be a contiguous float32 CUDA tensor of ", want[i], " elements");
+    }
+    torch::Tensor scratch = scratch_;
+    const size_t need = das3r_frontend_backward_scratch_bytes((int32_t)P, V);
+    if (!scratch.defined() || scratch.numel() == 0)
+        scratch = torch::empty({(long long)need}, torch::TensorOptions().dtype(torch::kByte).device(dev));
+    TORCH_CHECK(scratch.is_cuda() && (size_t)scratch.numel() * scratch.element_size() >= need, "scratch too small");
     das3r_frontend_grads_out gout;
     memset(&gout, 0, sizeof(gout));
-    gout.dL_dxyz = dxyz.data_ptr<float>();
-    gout.dL_drotation = drot.data_ptr<float>();
-    gout.dL_dopacity = dop.data_ptr<float>();
-    gout.dL_dscaling = dsc.data_ptr<float>();
-    gout.dL_dfeatures_dc = ddc.data_ptr<float>();
-    gout.dL_dfeatures_rest = drest.data_ptr<float>();
-    gout.dL_dconf = dconf.data_ptr<float>();
-    gout.dL_dposes = dposes.data_ptr<float>();
+    gout.dL_dxyz = outs[0].data_ptr<float>();
+    gout.dL_drotation = outs[1].data_ptr<float>();
+    gout.dL_dopacity = outs[2].data_ptr<float>();
+    gout.dL_dscaling = outs[3].data_ptr<float>();
+    gout.dL_dfeatures_dc = outs[4].data_ptr<float>();
+    gout.dL_dfeatures_rest = rest_numel ? outs[5].data_ptr<float>() : nullptr;
+    gout.dL_dconf = outs[6].data_ptr<float>();
+    gout.dL_dposes = outs[7].data_ptr<float>();
     gout.scratch = reinterpret_cast<float*>(scratch.data_ptr());
     das3r_frontend_model m;
     torch::Tensor none;
@@ -695,9 +872,28 @@ static std::vector<torch::Tensor> FrontendBackwardCUDA(
     // the backward does not read the features, only their shapes matter; the C ABI wants non-null pointers
     m.features_dc = m.xyz;
     m.features_rest = m.xyz;
+    das3r_frontend_options opt;
+    memset(&opt, 0, sizeof(opt));
+    opt.sh_degree = sh_degree;
+    opt.n_rows = (int32_t)P;
+    opt.filter_index = filtered ? filter_index.data_ptr<int64_t>() : nullptr;
+    opt.dsh_coeffs = dsh;
+    opt.rest_coeffs = rest == 15 ? 15 : -1;
+    opt.first = first;
+    opt.count = count;
+    opt.finish_poses = finish_poses ? 1 : 0;
     cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
-    check(das3r_frontend_backward(&m, V, poses.data_ptr<float>(), &gin, &gout, stream), "frontend_backward");
-    return {dxyz, drot, dop, dsc, ddc, drest, dconf, dposes};
+    check(das3r_frontend_backward_ex(&m, V, poses.data_ptr<float>(), &gin, &gout, &opt, stream), "frontend_backward");
+    return outs;
+}
+
+static std::vector<torch::Tensor> FrontendBackwardCUDA(
+    const torch::Tensor& xyz, const torch::Tensor& rotation, const torch::Tensor& opacity, const torch::Tensor& scaling,
+    const torch::Tensor& conf_static, const torch::Tensor& conf_index, const torch::Tensor& poses,
+    const torch::Tensor& dL_dopacity, const torch::Tensor& dL_dscales, const torch::Tensor& dL_dshs,
+    const std::vector<torch::Tensor>& dL_dmeans, const std::vector<torch::Tensor>& dL_drots) {
+    return FrontendBackwardExCUDA(xyz, rotation, opacity, scaling, conf_static, conf_index, poses, dL_dopacity, dL_dscales,
+                                  dL_dshs, dL_dmeans, dL_drots, 3, torch::Tensor(), {}, torch::Tensor(), 0, -1, true);
 }
 
 // ---- fused photometric loss (include/das3r_loss.h) ----------------------------------------------------------------
@@ -814,6 +1010,11 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians_forward_render", &ForwardRenderCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_blend", &BackwardBlendCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("rasterize_gaussians_backward_finish", &BackwardFinishCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_backward_finish_ex", &BackwardFinishExCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_forward_render_batch", &ForwardRenderBatchCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("rasterize_gaussians_backward_blend_batch", &BackwardBlendBatchCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("frontend_forward_ex", &FrontendForwardExCUDA, py::call_guard<py::gil_scoped_release>());
+    m.def("frontend_backward_ex", &FrontendBackwardExCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("frontend_forward", &FrontendForwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("frontend_backward", &FrontendBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("loss_forward", &LossForwardCUDA, py::call_guard<py::gil_scoped_release>());
