@@ -699,7 +699,8 @@ int das3r_raster_backward_blend_batch(int32_t n_views, const das3r_raster_view* 
 }
 
 int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* g,
-                                    int32_t dsh_coeffs, int32_t first, int32_t count, void* stream_v) {
+                                    int32_t dsh_coeffs, int32_t first, int32_t count, int32_t grads_local,
+                                    void* stream_v) {
     g_err.clear();
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (n_views < 1 || !views || !g) return fail_msg(DAS3R_EINVAL, "backward_finish: null or invalid argument");
@@ -749,6 +750,7 @@ int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* vi
     // One fused pass when the views share 16-coefficient SH rows and use scale / rotation inputs; otherwise one
     // accumulating pass per view, which gives the same sums (full rows only).
     const size_t o = (size_t)first;  // every pointer below is moved to the first Gaussian of the range
+    const size_t og = grads_local ? 0 : o;  // ... except the summed outputs when they already address that Gaussian
     bool fused = M == 16 && views[0].in->shs != nullptr && !misaligned16(views[0].in->shs) &&
                  (n_views > 1 || dsh_coeffs != M);
     for (int v = 0; v < n_views && fused; v++) {
@@ -766,9 +768,9 @@ int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* vi
             a.D = D;
             a.dsh_coeffs = dsh_coeffs;
             a.shs = views[0].in->shs + o * 48;
-            a.dL_dopacity = g->dL_dopacity + o; a.dL_dmeans3D = g->dL_dmeans3D + o * 3;
-            a.dL_dsh = g->dL_dsh + o * 3 * dsh_coeffs;
-            a.dL_dscales = g->dL_dscales + o * 3; a.dL_drots = g->dL_drotations + o * 4;
+            a.dL_dopacity = g->dL_dopacity + og; a.dL_dmeans3D = g->dL_dmeans3D + og * 3;
+            a.dL_dsh = g->dL_dsh + og * 3 * dsh_coeffs;
+            a.dL_dscales = g->dL_dscales + og * 3; a.dL_drots = g->dL_drotations + og * 4;
             for (int i = 0; i < a.n_views; i++) {
                 const das3r_raster_view& V = views[v0 + i];
                 MultiBwdView& m = a.v[i];
@@ -803,11 +805,11 @@ int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* vi
         if (in.rotations) in.rotations += o * 4;
         if (in.cov3D_precomp) in.cov3D_precomp += o * 6;
         das3r_raster_grads gg = *g;
-        gg.dL_dopacity += o; gg.dL_dmeans3D += o * 3; gg.dL_dscales += o * 3; gg.dL_drotations += o * 4;
-        if (gg.dL_dsh) gg.dL_dsh += o * 3 * M;
-        if (gg.dL_dmeans2D) gg.dL_dmeans2D += o * 3;
-        if (gg.dL_dcolors) gg.dL_dcolors += o * 3;
-        if (gg.dL_dcov3D) gg.dL_dcov3D += o * 6;
+        gg.dL_dopacity += og; gg.dL_dmeans3D += og * 3; gg.dL_dscales += og * 3; gg.dL_drotations += og * 4;
+        if (gg.dL_dsh) gg.dL_dsh += og * 3 * M;
+        if (gg.dL_dmeans2D) gg.dL_dmeans2D += og * 3;
+        if (gg.dL_dcolors) gg.dL_dcolors += og * 3;
+        if (gg.dL_dcov3D) gg.dL_dcov3D += og * 6;
         das3r_raster_params pp = *V.params;
         pp.P = count;
         PreBwdArgs a;
@@ -835,7 +837,7 @@ int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* vi
 
 int das3r_raster_backward_finish(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* g,
                                  void* stream_v) {
-    return das3r_raster_backward_finish_ex(n_views, views, g, 0, 0, -1, stream_v);
+    return das3r_raster_backward_finish_ex(n_views, views, g, 0, 0, -1, 0, stream_v);
 }
 
 // ---- backward without any device allocation (see include/das3r_raster.h) ---------------------------------------
@@ -997,6 +999,9 @@ int das3r_frontend_backward_ex(const das3r_frontend_model* model, int32_t n_view
     memset(&a, 0, sizeof(a));
     a.P = rows; a.n_views = n_views; a.K = K; a.dsh_coeffs = dsh; a.rest_coeffs = rest;
     a.row0 = first; a.row_end = first + count;
+    a.out_row0 = (opt && opt->local_outputs) ? first : 0;
+    if (a.out_row0 && a.filter_index)
+        return fail_msg(DAS3R_EINVAL, "frontend_backward: local_outputs cannot be combined with filter_index");
     a.xyz = model->xyz; a.rotation = model->rotation; a.opacity_raw = model->opacity; a.scaling_raw = model->scaling;
     a.conf_static = model->conf_static; a.conf_index = model->conf_index; a.poses = poses;
     a.filter_index = opt ? opt->filter_index : nullptr;

@@ -179,10 +179,13 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
     const bool in_range = idx < a.row_end;
     if (tid < a.n_views) pose_to_smem(a.poses + 7 * tid, s_pose + FE_POSE_F * tid);
     const bool flat = a.K == 16 && a.dsh_coeffs == 16 && a.rest_coeffs == 15 && a.filter_index == nullptr;
-    if (flat) sh_rows_copy<false>(a.dL_dfeatures_dc, a.dL_dfeatures_rest, a.dL_dshs, base, nvalid);
+    if (flat)  // the split-layout outputs may be windows that start at row out_row0
+        sh_rows_copy<false>(a.dL_dfeatures_dc - 3 * (size_t)a.out_row0, a.dL_dfeatures_rest - 45 * (size_t)a.out_row0,
+                            a.dL_dshs, base, nvalid);
     __syncthreads();
     // output row idx of the forward = model row src (render()'s `[filtering]`); parameter gradients go to row src
     const size_t src = (in_range && a.filter_index) ? (size_t)a.filter_index[idx] : (size_t)idx;
+    const size_t dst = src - (size_t)a.out_row0;  // row of the parameter-gradient outputs
 
     float X = 0.f, Y = 0.f, Z = 0.f;
     float4 rq = {0.f, 0.f, 0.f, 0.f};
@@ -191,9 +194,9 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
             // dL_dshs rows have dsh_coeffs coefficients of which K are active; the rest rows written have rest_coeffs
             const float* g = a.dL_dshs + (size_t)idx * 3 * a.dsh_coeffs;
 #pragma unroll
-            for (int j = 0; j < 3; j++) a.dL_dfeatures_dc[src * 3 + j] = g[j];
+            for (int j = 0; j < 3; j++) a.dL_dfeatures_dc[dst * 3 + j] = g[j];
             const int nact = 3 * (a.K - 1), nrest = 3 * a.rest_coeffs;
-            float* r = a.dL_dfeatures_rest + src * (size_t)nrest;
+            float* r = a.dL_dfeatures_rest + dst * (size_t)nrest;
             for (int j = 0; j < nrest; j++) r[j] = (j < nact) ? g[3 + j] : 0.f;
         }
         // activation derivatives
@@ -201,11 +204,11 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
         const float sg = 1.0f / (1.0f + expf(-o));
         const float conf = a.conf_static[a.conf_index ? a.conf_index[idx] : (int64_t)idx];
         const float go = a.dL_dopacity[idx];
-        a.dL_dopacity_raw[src] = go * conf * sg * (1.0f - sg);
-        a.dL_dconf[idx] = go * sg;
+        a.dL_dopacity_raw[dst] = go * conf * sg * (1.0f - sg);
+        a.dL_dconf[idx - a.out_row0] = go * sg;
 #pragma unroll
         for (int k = 0; k < 3; k++)
-            a.dL_dscaling_raw[3 * src + k] = a.dL_dscales[3 * idx + k] * expf(a.scaling_raw[3 * src + k]);
+            a.dL_dscaling_raw[3 * dst + k] = a.dL_dscales[3 * idx + k] * expf(a.scaling_raw[3 * src + k]);
         X = a.xyz[3 * src]; Y = a.xyz[3 * src + 1]; Z = a.xyz[3 * src + 2];
         rq = __ldg(reinterpret_cast<const float4*>(a.rotation) + src);
     }
@@ -248,8 +251,8 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
         if ((lane & 1) == 0) s_warp[v][warp][pi] = ps;
     }
     if (in_range) {
-        a.dL_dxyz[3 * src] = dX; a.dL_dxyz[3 * src + 1] = dY; a.dL_dxyz[3 * src + 2] = dZ;
-        reinterpret_cast<float4*>(a.dL_drotation)[src] = dr;
+        a.dL_dxyz[3 * dst] = dX; a.dL_dxyz[3 * dst + 1] = dY; a.dL_dxyz[3 * dst + 2] = dZ;
+        reinterpret_cast<float4*>(a.dL_drotation)[dst] = dr;
     }
     // this block's partial sums -> scratch[block][view][16] (summed by frontend_pose_kernel)
     __syncthreads();

@@ -140,7 +140,7 @@ struct FrontendBwdArgs {
     int dsh_coeffs;   // coefficients per row of the incoming dL_dshs (K..16)
     int rest_coeffs;  // coefficients per row of the outgoing dL_dfeatures_rest (K-1 = trimmed, or 15)
     int row0, row_end;  // output rows [row0, row_end) are processed by this launch (row0 a multiple of 256)
-    int pad_;
+    int out_row0;       // the parameter-gradient outputs and dL_dconf address this row (0, or row0 for bucket windows)
     const float *xyz, *rotation, *opacity_raw, *scaling_raw, *conf_static, *poses;
     const int64_t* conf_index;
     const int64_t* filter_index;

@@ -609,7 +609,11 @@ static void BackwardFinishExCUDA(const std::vector<FinishView>& views, const tor
     int M = 0;
     if (sh_.defined() && sh_.dim() == 3) M = sh_.size(1);
     const int dsh_coeffs = dsh_coeffs_ > 0 ? dsh_coeffs_ : M;
-    const int64_t want[5] = {(int64_t)P, 3LL * P, 3LL * dsh_coeffs * P, 3LL * P, 4LL * P};
+    // outs either cover all P Gaussians or exactly the rows [first, first+count) (windows of a slice-major bucket)
+    const int64_t rows_in_range = count < 0 ? (int64_t)P - first : (int64_t)count;
+    const bool grads_local = rows_in_range != P && outs[0].numel() == rows_in_range;
+    const int64_t Pw = grads_local ? rows_in_range : (int64_t)P;
+    const int64_t want[5] = {Pw, 3LL * Pw, 3LL * dsh_coeffs * Pw, 3LL * Pw, 4LL * Pw};
     for (int i = 0; i < 5; i++)
         TORCH_CHECK(outs[i].is_cuda() && outs[i].device() == dev && outs[i].scalar_type() == torch::kFloat32 &&
                         outs[i].is_contiguous() && outs[i].numel() == want[i],
@@ -677,7 +681,7 @@ static void BackwardFinishExCUDA(const std::vector<FinishView>& views, const tor
     g.dL_drotations = outs[4].data_ptr<float>();
     g.accumulate = accumulate ? 1 : 0;
     cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
-    check(das3r_raster_backward_finish_ex((int32_t)n, vs.data(), &g, dsh_coeffs, first, count, stream),
+    check(das3r_raster_backward_finish_ex((int32_t)n, vs.data(), &g, dsh_coeffs, first, count, grads_local ? 1 : 0, stream),
           "rasterize_gaussians_backward_finish");
 }
 
@@ -839,11 +843,15 @@ static std::vector<torch::Tensor> FrontendBackwardExCUDA(
                 torch::empty({P}, o), torch::empty({V, 7}, o)};
     }
     TORCH_CHECK(outs.size() == 8, "expected 8 gradient tensors");
+    // outs either cover all model rows or exactly the rows [first, first+count) (windows of a slice-major bucket)
+    const int64_t rows_in_range = std::min<int64_t>(count < 0 ? P - first : count, P - first);
+    const bool local = !filtered && rows_in_range != Pm && outs[0].numel() == 3 * rows_in_range;
+    const int64_t Pw = local ? rows_in_range : Pm;
     const int64_t rest_numel = outs[5].defined() ? outs[5].numel() : 0;
-    TORCH_CHECK(rest_numel == 45 * Pm || rest_numel == 3LL * (K - 1) * Pm,
+    TORCH_CHECK(rest_numel == 45 * Pw || rest_numel == 3LL * (K - 1) * Pw,
                 "dL_dfeatures_rest must be [P,15,3] or trimmed to [P,(D+1)^2-1,3]");
-    const int rest = rest_numel == 45 * Pm ? 15 : K - 1;
-    const int64_t want[8] = {3 * Pm, 4 * Pm, Pm, 3 * Pm, 3 * Pm, rest_numel, P, 7LL * V};
+    const int rest = rest_numel == 45 * Pw ? 15 : K - 1;
+    const int64_t want[8] = {3 * Pw, 4 * Pw, Pw, 3 * Pw, 3 * Pw, rest_numel, local ? rows_in_range : P, 7LL * V};
     for (int i = 0; i < 8; i++) {
         if (i == 5 && rest_numel == 0) continue;
         TORCH_CHECK(outs[i].is_cuda() && outs[i].device() == dev && outs[i].scalar_type() == torch::kFloat32 &&
@@ -882,6 +890,7 @@ static std::vector<torch::Tensor> FrontendBackwardExCUDA(
     opt.first = first;
     opt.count = count;
     opt.finish_poses = finish_poses ? 1 : 0;
+    opt.local_outputs = local ? 1 : 0;
     cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
     check(das3r_frontend_backward_ex(&m, V, poses.data_ptr<float>(), &gin, &gout, &opt, stream), "frontend_backward");
     return outs;

@@ -35,7 +35,9 @@ typedef struct das3r_frontend_model {
     const float* features_dc;    /* [P,1,3] _features_dc */
     const float* features_rest;  /* [P,15,3] _features_rest */
     const float* conf_static;    /* flat _conf_static (one value per pointmap pixel) */
-    const int64_t* conf_index;   /* [P] position of Gaussian i in conf_static = nonzero(aggregated_mask); NULL: i */
+    const int64_t* conf_index;   /* [P] position of Gaussian i in conf_static = nonzero(aggregated_mask); NULL: i.
+                                    Precondition (not checked, it would cost a device round trip): every entry is a
+                                    valid index into conf_static */
 } das3r_frontend_model;
 
 typedef struct das3r_frontend_outputs {
@@ -97,6 +99,8 @@ int das3r_frontend_backward(const das3r_frontend_model* model, int32_t n_views, 
  *                 or trimmed to the (D+1)^2 - 1 active ones for a gradient bucket that skips the zero bands (pass that
  *                 number, or -1; at degree 0 the rows are empty and the pointer may be NULL).
  *   first, count  backward: only output rows [first, first+count) (count < 0: to the end; first a multiple of 256).
+ *   local_outputs backward: nonzero = the parameter-gradient pointers of gout (and dL_dconf) address row `first` (windows
+ *                 of a slice-major gradient bucket) instead of row 0. Not with filter_index.
  *   finish_poses  backward: after this range, reduce the per-block partial sums of ALL rows to gout->dL_dposes (set on
  *                 the last range of a step; every range must have been processed by then). */
 typedef struct das3r_frontend_options {
@@ -106,6 +110,7 @@ typedef struct das3r_frontend_options {
     int32_t dsh_coeffs, rest_coeffs;
     int32_t first, count;
     int32_t finish_poses;
+    int32_t local_outputs;
 } das3r_frontend_options;
 
 int das3r_frontend_forward_ex(const das3r_frontend_model* model, int32_t n_views, const float* poses,

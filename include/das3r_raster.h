@@ -219,11 +219,14 @@ int das3r_raster_backward_blend_batch(int32_t n_views, const das3r_raster_view* 
  *                16-byte aligned shs, scale / rotation inputs).
  *   first, count only Gaussians [first, first + count) are processed (count < 0: to the end): the caller can hand a
  *                finished slice of the gradient buffers to a collective while the next slice is computed. grads and the
- *                per-view outputs are still addressed by ABSOLUTE Gaussian index (row `first` is the first one written).
+ *                per-view outputs are still addressed by ABSOLUTE Gaussian index (row `first` is the first one written),
+ *                unless grads_local != 0: then the pointers in `grads` address Gaussian `first` (a window of a
+ *                slice-major gradient bucket); the per-view outputs stay absolute.
  * Alignment: rotations, dL_drotations (shared and per-view) and the accumulators must be 16-byte aligned (float4
  * accesses); violations are refused with DAS3R_EINVAL. */
 int das3r_raster_backward_finish_ex(int32_t n_views, const das3r_raster_view* views, const das3r_raster_grads* grads,
-                                    int32_t dsh_coeffs, int32_t first, int32_t count, void* stream);
+                                    int32_t dsh_coeffs, int32_t first, int32_t count, int32_t grads_local,
+                                    void* stream);
 
 /* Backward for hosts that cannot allocate device memory. It has no counterpart in the reference.
  *
