@@ -2,27 +2,36 @@
 """bench.py — the headline benchmark of the rasterizer hot path (BASELINE.json metric:
 "raster fwd+bwd views/s @1M Gaussians 512x288").
 
-    python bench.py --gpus N --steps K --warmup W [--impl ours|reference|oracle-cpu]
+    python bench.py --gpus N --steps K --warmup W [--impl ours|reference|oracle-cpu] [--config C1..C5] [--sh-degree D]
 
 For N > 1 the driver launches it under torchrun (one rank per GPU, NCCL); RANK/LOCAL_RANK/WORLD_SIZE come from the env.
 
-A STEP is one pass of the hot path over one batch: every rank rasterizes `--views-per-step` disjoint camera views of
-the (replicated) synthetic scene, forward + backward with a dense dL/d(colour), summing the Gaussian-parameter
-gradients of its views in place into one flat fp32 bucket; for N > 1 the bucket is then summed across ranks with ONE
-NCCL all-reduce per step (double-buffered, overlapping the next step). `value` = views of all ranks / device time, with
-all inputs resident in HBM; `e2e` = the same metric through the public drop-in API (GaussianRasterizer + autograd) with
-the per-view host inputs (camera bundle, dL/d(colour)) copied from pinned memory and the rendered image + loss read
-back inside the timed region.
+A STEP is one data-parallel DAS3R training step without the loss and the optimizer: every rank takes
+`--views-per-step` disjoint camera views of the (replicated) synthetic scene and runs
+
+    ours       raw parameters + the views' poses -> fused front-end (what render() does before the rasterizer call)
+               -> rasterizer forward of all views -> rasterizer backward with a dense dL/d(colour)
+               -> front-end backward -> gradients of _xyz/_rotation/_opacity/_scaling/_features_*/conf and the poses,
+               summed over the rank's views, in one flat fp32 bucket.  Every stage is ONE launch for all views.
+    reference  the reference CUDA rasterizer (oracle/_ref) forward + backward per view on pre-posed inputs; its fresh
+               gradient tensors are added into a bucket with torch ops (no front-end: less work per step than `ours`).
+
+For N > 1 the bucket is summed across ranks inside the step: the gradient pass produces it slice by slice and every
+finished slice starts its own NCCL all-reduce, which overlaps the REMAINING slices of the same step; the step ends when
+the last all-reduce has completed (the next step's forward would need the reduced gradients - nothing is stale).
+
+`value` = views of all ranks / device time, with all inputs resident in HBM; `e2e` = the same step through the public
+Python API (das3r_b200.frontend.render_inputs + MultiViewRasterizer + autograd) with the per-step host inputs (poses,
+camera bundles, dL/d(colour)) copied from pinned memory and the rendered images + loss read back inside the timed
+region.
 
 `--impl reference` times the reference CUDA rasterizer (oracle/_ref, built from /root/reference by
-oracle/build_ref.sh) through its own pybind API in the same step structure (its fresh zero-filled gradients are added
-to the bucket with torch ops, the bucket is all-reduced the same way). `--impl oracle-cpu` times the C port of the
-reference algorithm on the host cores (rank 0 only). Only this file's cpu_baseline / reference legs touch oracle/.
+oracle/build_ref.sh) through its own pybind API. `--impl oracle-cpu` times the C port of the reference algorithm on the
+host cores (rank 0 only). Only this file's cpu_baseline / reference legs touch oracle/.
 """
 from __future__ import annotations
 
 import argparse
-from concurrent.futures import ThreadPoolExecutor
 import json
 import os
 import subprocess
@@ -45,29 +54,27 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=300)  # ~1 s timed region: enough clock samples
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "oracle-cpu"])
+    ap.add_argument("--config", default="C2", choices=["C1", "C2", "C3", "C4", "C5"],
+                    help="BASELINE.json config shape (C2 = the metric's; C5 is forward-only like render.py)")
     ap.add_argument("--views-per-step", type=int, default=8)
-    ap.add_argument("--P", type=int, default=1_000_000)
-    ap.add_argument("--V", type=int, default=50)
-    ap.add_argument("--W", type=int, default=512)
-    ap.add_argument("--H", type=int, default=288)
+    ap.add_argument("--P", type=int, default=None)
+    ap.add_argument("--V", type=int, default=None)
+    ap.add_argument("--W", type=int, default=None)
+    ap.add_argument("--H", type=int, default=None)
     ap.add_argument("--sh-degree", type=int, default=3)
-    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--seed", type=int, default=None)
+    ap.add_argument("--slices", type=int, default=4,
+                    help="gradient bucket slices: slice c is all-reduced while slice c+1 is computed (N > 1)")
+    ap.add_argument("--no-trim", action="store_true", help="all-reduce all 16 SH bands even when the degree is below 3")
+    ap.add_argument("--forward-only", action="store_true", help="forward only (C5 sets it)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-views", type=int, default=4, help="views timed for the CPU baseline sample")
-    ap.add_argument("--eager-allreduce", action="store_true",
-                    help="start a step's gradient all-reduce right after its backward instead of after the next "
-                         "step's preprocess pass")
-    ap.add_argument("--per-view-backward", action="store_true",
-                    help="sum the views with the per-view accumulating backward instead of the fused multi-view pass")
-    ap.add_argument("--streams", type=int, default=3,
-                    help="CUDA streams the views of a step are spread over (the reference arm always uses 1: its "
-                         "kernels are hard-wired to the legacy default stream)")
     return ap.parse_args()
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 20 ms while the timed region runs."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -81,9 +88,13 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20", "-i",
                  str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
+            t0 = time.time()
+            while not self.lines and time.time() - t0 < 2.0:  # the first sample takes a while: have it before timing
+                time.sleep(0.01)
+            self.lines.clear()
         except Exception:
             self.proc = None
 
@@ -94,7 +105,7 @@ class ClockSampler:
     def stop(self) -> dict:
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
+        time.sleep(0.05)
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
         for ln in self.lines:
@@ -124,28 +135,36 @@ def hbm_peak() -> tuple[float, str]:
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def stage_bytes(P, R, N, T, s, fused_views=0):
-    """Algorithmic bytes per launch of each stage (SURVEY.md §8d / DESIGN.md §4): compulsory traffic, each array counted
-    once per pass that semantically needs it. s = 12*(D+1)^2 bytes of active SH per Gaussian. With the fused multi-view
-    backward one preprocess_bwd launch serves `fused_views` views: per view it must read radii 4, the accumulator row
-    48, mean 12, scale 12, rotation 16, clamp bits 1 (= 93 B per Gaussian); once per launch the SH rows (s) and the
-    gradient rows it writes (opacity 4, mean 12, scale 12, rotation 16, SH s)."""
-    if fused_views:
-        pre_bwd = P * (93 * fused_views + 2 * s + 44)
-    else:
-        pre_bwd = P * (199 + 2 * s)
-    return {
-        "preprocess_fwd": P * (119 + s),
-        "tile_scan": 8 * T,
-        "scatter": 20 * P + 12 * R,
+def stage_bytes(P, Rs, N, T, s, n, V_fe, fwd_only):
+    """Algorithmic bytes PER LAUNCH of each stage (SURVEY.md §8d / DESIGN.md §4): compulsory traffic, each array counted
+    once per pass that semantically needs it. Every stage is one launch for the step's n views. s = 12*(D+1)^2 bytes of
+    active SH per Gaussian, Rs = per-view num_rendered.
+      preprocess_fwd   the shared SH rows once + per view inputs/radii/saved geometry: P*(s + 127 n)
+      preprocess_bwd   per view radius 4 + accumulator row 48 + mean 12 + scale 12 + rotation 16 + clamp bits 1 = 93;
+                       once the SH rows (s) and the gradient rows written (opacity 4, scale 12, SH s) + per view the
+                       mean/rotation gradients (28): P*((93 + 28) n + 2 s + 16)
+      frontend_fwd/bwd the front-end's own arrays, SH copy limited to the active bands"""
+    R = sum(Rs)
+    out = {
+        "preprocess_fwd": P * (s + 127 * n),
+        "tile_scan": 8 * T * n,
+        "scatter": 20 * P * n + 12 * R,
         "tile_sort": 24 * R,
-        "blend_fwd": 48 * R + 20 * N,
-        "blend_bwd": 40 * R + 20 * N,
-        "preprocess_bwd": pre_bwd,
+        "blend_fwd": 48 * R + 20 * N * n,
+        "frontend_fwd": P * (56 + 2 * s + 28 * V_fe),
     }
+    if not fwd_only:
+        out.update({
+            "blend_bwd": 40 * R + 20 * N * n,
+            "preprocess_bwd": P * (121 * n + 2 * s + 16),
+            "frontend_bwd": P * (72 + 48 + 2 * s + 28 * V_fe),
+        })
+    return out
 
 
-def view_bytes(P, R, N, T, s):
+def view_bytes(P, R, N, T, s, fwd_only=False):
+    if fwd_only:
+        return P * (119 + s) + 84 * R + 20 * N + 8 * T
     return P * (318 + 3 * s) + 124 * R + 40 * N + 8 * T
 
 
@@ -163,6 +182,19 @@ def emit(obj):
         os.write(_JSON_FD, line)
 
 
+def resolve_config(args):
+    from das3r_b200.synth import CONFIGS
+    c = dict(CONFIGS[args.config])
+    for k, a in (("P", args.P), ("V", args.V), ("W", args.W), ("H", args.H), ("seed", args.seed)):
+        if a is not None:
+            c[k] = a
+    c["sh_degree"] = args.sh_degree
+    c.pop("n_poses", None)
+    if args.config == "C5":
+        args.forward_only = True
+    return c
+
+
 def main():
     global _JSON_FD
     args = parse_args()
@@ -176,6 +208,9 @@ def main():
 
     from das3r_b200.synth import synth_scene, view_inputs, grad_seed
     from das3r_b200 import sharding
+
+    cfg = resolve_config(args)
+    args.P, args.V, args.W, args.H, args.seed = cfg["P"], cfg["V"], cfg["W"], cfg["H"], cfg["seed"]
 
     if args.impl == "oracle-cpu":
         if rank != 0:
@@ -206,159 +241,125 @@ def main():
     # ---- the workload: one replicated scene, per-rank view pools ------------------------------------------------
     sc = synth_scene(P=args.P, V=args.V, W=args.W, H=args.H, seed=args.seed, sh_degree=args.sh_degree)
     P, W, H, D = args.P, args.W, args.H, args.sh_degree
+    K = (D + 1) ** 2
     N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    fwd_only = bool(args.forward_only)
     perm = torch.randperm(sc.V, generator=torch.Generator().manual_seed(1234)).tolist()
     my_views = sharding.shard_views(perm, 0, rank, world, vps)
     empty = torch.Tensor([])
-    shared = None
-    pool = []
-    for v in my_views:
-        vi = view_inputs(sc, v)
-        if shared is None:
-            shared = dict(shs=vi["shs"].to(dev), opac=vi["opacities"].to(dev), scales=vi["scales"].to(dev),
-                          bg=vi["bg"].to(dev), view=vi["viewmatrix"].to(dev).contiguous(),
-                          proj=vi["projmatrix"].to(dev).contiguous(), campos=vi["campos"].to(dev).contiguous(),
-                          tanx=vi["tanfovx"], tany=vi["tanfovy"])
-        pool.append(dict(means=vi["means3D"].contiguous().to(dev), rots=vi["rotations"].contiguous().to(dev)))
+    vi0 = view_inputs(sc, my_views[0])
+    S = dict(shs=vi0["shs"].to(dev), opac=vi0["opacities"].to(dev), scales=vi0["scales"].to(dev), bg=vi0["bg"].to(dev),
+             view=vi0["viewmatrix"].to(dev).contiguous(), proj=vi0["projmatrix"].to(dev).contiguous(),
+             campos=vi0["campos"].to(dev).contiguous(), tanx=float(vi0["tanfovx"]), tany=float(vi0["tanfovy"]))
     dL = grad_seed(sc).to(dev)
-    S = shared
-
-    shapes = sharding.gaussian_grad_shapes(P, 16)
-    # The views of a step are independent, so they are spread over S streams: the HBM-bound stages of one view
-    # (preprocess, binning, gather) overlap with the issue-bound blend kernels of another. Every stream sums into its
-    # own bucket (a shared one would be a read-modify-write race); the step ends by folding them into bucket 0.
-    S_ = 1 if args.impl != "ours" else max(1, min(args.streams, vps))
-    nbuf = 2 if world > 1 else 1
-    buckets = [[sharding.GradBucket(shapes, dev) for _ in range(S_)] for _ in range(nbuf)]
-    streams = [torch.cuda.Stream(device=dev) for _ in range(S_)] if S_ > 1 else [None]
-    handles = [None] * nbuf
     last_R = [0]
-    workers = ThreadPoolExecutor(max_workers=S_) if S_ > 1 else None
+    all_R = [[0] * vps]
 
-    def fwd(pv):
-        return C.rasterize_gaussians(S["bg"], pv["means"], empty, S["opac"], S["scales"], pv["rots"], 1.0, empty,
-                                     S["view"], S["proj"], S["tanx"], S["tany"], H, W, S["shs"], D, S["campos"], False,
-                                     False)
+    if args.impl == "ours":
+        # raw model parameters (what GaussianModel holds) + this rank's poses: the front-end poses the Gaussians
+        raw = dict(xyz=sc.xyz.to(dev).contiguous(), rotation=sc.rot.to(dev).contiguous(),
+                   opacity=torch.logit(sc.opacity.clamp(1e-6, 1 - 1e-6)).to(dev).contiguous(),
+                   scaling=torch.log(sc.scales).to(dev).contiguous(),
+                   features_dc=sc.shs[:, :1].to(dev).contiguous(), features_rest=sc.shs[:, 1:].to(dev).contiguous(),
+                   conf_static=torch.ones(P, device=dev))
+        poses = sc.poses[my_views].to(dev).contiguous()
+        ci = torch.empty(0, dtype=torch.int64)
+        fi = torch.empty(0, dtype=torch.int64)
+        Kb = K if not args.no_trim else 16
+        widths = sharding.raw_param_widths(D, trim_sh=not args.no_trim)
+        n_slices = args.slices if (world > 1 and not fwd_only) else 1
+        bucket = sharding.SlicedGradBucket(P, widths, dev, n_slices, tail={"poses": (vps, 7)})
+        o = dict(device=dev, dtype=torch.float32)
+        # intermediates of the backward, allocated once: the rasterizer's gradients w.r.t. its own inputs
+        g_opac, g_scales, g_shs = torch.empty(P, 1, **o), torch.empty(P, 3, **o), torch.empty(P, Kb, 3, **o)
+        g_msum, g_rsum = torch.empty(P, 3, **o), torch.empty(P, 4, **o)  # unused (every view has its own)
+        g_means = [torch.empty(P, 3, **o) for _ in range(vps)]
+        g_rots = [torch.empty(P, 4, **o) for _ in range(vps)]
+        fe_scratch = torch.empty(((P + 255) // 256) * vps * 16 * 4 + 256, dtype=torch.uint8, device=dev)
+        rest_w = widths.get("features_rest", 0) // 3
 
-    def one_view(pv, bk):
-        """fwd + bwd of one view with the per-view API (reference arm; ours with --per-view-backward)."""
-        g = bk.views()
-        R, color, radii, geom, binning, img = fwd(pv)
-        last_R[0] = R
-        bargs = (S["bg"], pv["means"], radii, empty, S["scales"], pv["rots"], 1.0, empty, S["view"], S["proj"],
-                 S["tanx"], S["tany"], dL, S["shs"], D, S["campos"], geom, R, binning, img, False)
-        if args.impl == "ours":
-            outs = [empty, empty, g["opacities"], g["means3D"], empty, g["shs"], g["scales"], g["rotations"]]
-            C.rasterize_gaussians_backward_into(*bargs, outs, True)
-        else:
-            (_m2d, _dc, d_op, d_m3, _dcov, d_sh, d_sc, d_rot) = C.rasterize_gaussians_backward(*bargs)
-            g["opacities"].add_(d_op)
-            g["means3D"].add_(d_m3)
-            g["shs"].add_(d_sh)
-            g["scales"].add_(d_sc)
-            g["rotations"].add_(d_rot)
+        def step(_i):
+            opac, scales, shs, means, rots = C.frontend_forward_ex(
+                raw["xyz"], raw["rotation"], raw["opacity"], raw["scaling"], raw["features_dc"], raw["features_rest"],
+                raw["conf_static"], ci, poses, D, fi)
+            pre = C.rasterize_gaussians_forward_preprocess(
+                [(S["bg"], means[v], rots[v], S["view"], S["proj"], S["tanx"], S["tany"], H, W, S["campos"])
+                 for v in range(vps)], opac, scales, shs, D, 1.0, False, False)
+            res = C.rasterize_gaussians_forward_render_batch(
+                [(S["bg"], pre[v][0], pre[v][1], pre[v][2], pre[v][3]) for v in range(vps)], False)
+            all_R[0] = [r[0] for r in res]
+            last_R[0] = res[-1][0]
+            if fwd_only:
+                return [p[0] for p in pre]
+            accs = C.rasterize_gaussians_backward_blend_batch(
+                [(S["bg"], dL, pre[v][2], res[v][0], res[v][1], pre[v][3]) for v in range(vps)], P, False)
+            fviews = [(means[v], pre[v][1], scales, rots[v], S["view"], S["proj"], S["tanx"], S["tany"], S["campos"],
+                       pre[v][2], accs[v], H, W, g_means[v], g_rots[v]) for v in range(vps)]
+            handles = []
+            last = len(bucket.slices) - 1
+            for c, (first, count) in enumerate(bucket.slices):
+                C.rasterize_gaussians_backward_finish_ex(fviews, shs, D, 1.0, [g_opac, g_msum, g_shs, g_scales, g_rsum],
+                                                         False, False, Kb, first, count)
+                w = bucket.windows(c)
+                rest = w["features_rest"].view(count, rest_w, 3) if rest_w else torch.empty(0, **o)
+                C.frontend_backward_ex(raw["xyz"], raw["rotation"], raw["opacity"], raw["scaling"], raw["conf_static"],
+                                       ci, poses, g_opac, g_scales, g_shs, g_means, g_rots, D, fi,
+                                       [w["xyz"], w["rotation"], w["opacity"], w["scaling"],
+                                        w["features_dc"].view(count, 1, 3), rest, w["conf"].view(count),
+                                        bucket.tail("poses")], fe_scratch, first, count, c == last)
+                if world > 1:
+                    handles.append(bucket.all_reduce_slice(c, async_op=True))
+            for h in handles:  # the step is over when its gradients are reduced: nothing is carried into the next step
+                h.wait()
+            return None
 
-    def preprocess_all():
-        """first half of the forward for all views of the step in one call (one kernel reads the shared SH rows once)"""
-        return C.rasterize_gaussians_forward_preprocess(
-            [(S["bg"], pv["means"], pv["rots"], S["view"], S["proj"], float(S["tanx"]), float(S["tany"]), H, W,
-              S["campos"]) for pv in pool], S["opac"], S["scales"], S["shs"], D, 1.0, False, False)
+        bucket_bytes = bucket.nbytes()
+        impl_detail = {
+            "what": "fused front-end -> rasterizer (every stage one launch for all views of the step) -> front-end "
+                    "backward into a slice-major fp32 bucket of raw-parameter gradients",
+            "bucket_slices": len(bucket.slices), "bucket_bytes": bucket_bytes,
+            "sh_bands_in_bucket": Kb, "streams": 1, "host_threads": 1,
+            "allreduce": "one NCCL all-reduce per bucket slice, started when the slice is complete, all waited on "
+                         "before the step ends" if world > 1 else "none (1 rank)",
+        }
+    else:
+        pool = []
+        for v in my_views:
+            vi = view_inputs(sc, v)
+            pool.append(dict(means=vi["means3D"].contiguous().to(dev), rots=vi["rotations"].contiguous().to(dev)))
+        shapes = sharding.gaussian_grad_shapes(P, 16)
+        bucket = sharding.GradBucket(shapes, dev)
 
-    def view_blend(pv, pre_v, lane_stream=None):
-        """second half of the forward + first half of the backward (backward blend) of one view; returns what the fused
-        second half of the backward needs."""
-        color, radii, geom, img = pre_v
-        if lane_stream is not None:
-            for t in (color, radii, geom, img):
-                t.record_stream(lane_stream)
-        R, binning = C.rasterize_gaussians_forward_render(S["bg"], color, radii, geom, img, False)
-        last_R[0] = R
-        acc = C.rasterize_gaussians_backward_blend(S["bg"], dL, P, geom, R, binning, img, False)
-        return (pv["means"], radii, S["scales"], pv["rots"], S["view"], S["proj"], float(S["tanx"]), float(S["tany"]),
-                S["campos"], geom, acc, H, W, empty, empty)
+        def step(_i):
+            g = bucket.views()
+            if not fwd_only:
+                bucket.zero_()
+            for pv in pool:
+                R, color, radii, geom, binning, img = C.rasterize_gaussians(
+                    S["bg"], pv["means"], empty, S["opac"], S["scales"], pv["rots"], 1.0, empty, S["view"], S["proj"],
+                    S["tanx"], S["tany"], H, W, S["shs"], D, S["campos"], False, False)
+                last_R[0] = R
+                if fwd_only:
+                    continue
+                (_m2d, _dc, d_op, d_m3, _dcov, d_sh, d_sc, d_rot) = C.rasterize_gaussians_backward(
+                    S["bg"], pv["means"], radii, empty, S["scales"], pv["rots"], 1.0, empty, S["view"], S["proj"],
+                    S["tanx"], S["tany"], dL, S["shs"], D, S["campos"], geom, R, binning, img, False)
+                g["opacities"].add_(d_op)
+                g["means3D"].add_(d_m3)
+                g["shs"].add_(d_sh)
+                g["scales"].add_(d_sc)
+                g["rotations"].add_(d_rot)
+            if world > 1 and not fwd_only:
+                bucket.all_reduce(async_op=False)
+            return None
 
-    def finish(fviews, bk):
-        """second half of the backward for all views of the step: one pass, gradients summed over the views."""
-        g = bk.views()
-        C.rasterize_gaussians_backward_finish(fviews, S["shs"], D, 1.0,
-                                              [g["opacities"], g["means3D"], g["shs"], g["scales"], g["rotations"]],
-                                              False, False)
-
-    fused_bwd = args.impl == "ours" and not args.per_view_backward
-    single_stream = [False]  # the per-stage profiling pass runs the views back to back on one stream
-
-    def step(i):
-        b = i % nbuf
-        if handles[b] is not None:
-            handles[b].wait()
-            handles[b] = None
-        if S_ == 1 or single_stream[0]:
-            if fused_bwd:
-                pre = preprocess_all()
-                finish([view_blend(pv, pre[j]) for j, pv in enumerate(pool)], buckets[b][0])
-            else:
-                buckets[b][0].zero_()
-                for pv in pool:
-                    one_view(pv, buckets[b][0])
-        else:
-            # one host thread per stream: the forward blocks its thread on the 16-byte read-back of num_rendered, the
-            # other threads keep their streams fed meanwhile
-            main = torch.cuda.current_stream()
-            pre = preprocess_all() if fused_bwd else None
-            launch_pending_reduce()  # ordered after this step's preprocess pass: it then runs under the blend kernels
-            ev = torch.cuda.Event()
-            ev.record(main)
-            fviews = [None] * len(pool)
-
-            def work(si):
-                torch.cuda.set_device(dev)
-                st = streams[si]
-                with torch.cuda.stream(st):
-                    st.wait_event(ev)
-                    if not fused_bwd:
-                        buckets[b][si].zero_()
-                    for j in range(si, len(pool), S_):
-                        if fused_bwd:
-                            fviews[j] = view_blend(pool[j], pre[j], st)
-                        else:
-                            one_view(pool[j], buckets[b][si])
-
-            for f in [workers.submit(work, si) for si in range(S_)]:
-                f.result()
-            for si, st in enumerate(streams):
-                main.wait_stream(st)
-            if fused_bwd:
-                finish(fviews, buckets[b][0])
-                for fv in fviews:  # the per-view tensors were allocated on side streams and are last read on `main`
-                    for t in fv:
-                        if isinstance(t, torch.Tensor) and t.is_cuda:
-                            t.record_stream(main)
-            else:
-                for si in range(1, S_):
-                    buckets[b][0].flat.add_(buckets[b][si].flat)
-        if world > 1:
-            # The all-reduce of this step's bucket is not started here but after the NEXT step's preprocess pass (or in
-            # drain()): started right away it shares HBM with that bandwidth-bound pass; a little later it overlaps
-            # the issue-bound blend kernels, which leave the memory system idle.
-            launch_pending_reduce()
-            pending[0] = b
-            if args.eager_allreduce:
-                launch_pending_reduce()
-
-    pending = [None]
-
-    def launch_pending_reduce():
-        if world > 1 and pending[0] is not None:
-            pb = pending[0]
-            pending[0] = None
-            handles[pb] = buckets[pb][0].all_reduce(async_op=True)
-
-    def drain():
-        launch_pending_reduce()
-        for b in range(len(handles)):
-            if handles[b] is not None:
-                handles[b].wait()
-                handles[b] = None
+        bucket_bytes = bucket.nbytes()
+        impl_detail = {
+            "what": "reference CUDA rasterizer (oracle/_ref) forward + backward per view on pre-posed inputs, its fresh "
+                    "gradient tensors added into one fp32 bucket with torch ops; no front-end",
+            "bucket_bytes": bucket_bytes, "streams": 1,
+            "allreduce": "one blocking NCCL all-reduce of the bucket per step" if world > 1 else "none (1 rank)",
+        }
 
     def barrier():
         if world > 1:
@@ -366,27 +367,22 @@ def main():
         torch.cuda.synchronize()
 
     # ---- warm-up, then the timed region -------------------------------------------------------------------------
-    if world > 1:  # NCCL sets up its channels and buffers lazily: not inside the W warm-up steps, let alone the timed ones
-        for _ in range(3):
-            for bb in range(nbuf):
-                buckets[bb][0].all_reduce(async_op=True).wait()
-        torch.cuda.synchronize()
-    for i in range(args.warmup):
+    for i in range(max(args.warmup, 3)):  # the warm-up steps ARE the timed step: NCCL, allocator and caches settle here
         step(i)
-    drain()
     barrier()
     launches0 = C.launch_count() if args.impl == "ours" else 0
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
+    barrier()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    evs[0].record()
     for i in range(args.steps):
         step(args.warmup + i)
-    drain()
-    ev1.record()
+        evs[i + 1].record()
     torch.cuda.synchronize()
-    elapsed_ms = ev0.elapsed_time(ev1)
+    elapsed_ms = evs[0].elapsed_time(evs[-1])
+    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     launches = (C.launch_count() - launches0) if args.impl == "ours" else None
@@ -394,32 +390,56 @@ def main():
     views_total = world * vps * args.steps
     value = views_total / (elapsed_ms / 1e3)
     R = int(last_R[0])
-    s_bytes = 12 * (D + 1) ** 2
+    s_bytes = 12 * K
+    ss = sorted(step_ms)
 
+    unit = "views/s"
     out = {
-        "metric": METRIC, "value": round(value, 2), "unit": "views/s", "n_gpus": world, "steps": args.steps,
+        "metric": METRIC if (args.config == "C2" and not fwd_only) else
+                  f"raster {'forward' if fwd_only else 'fwd+bwd'} views/s @{P} Gaussians {W}x{H} ({args.config})",
+        "value": round(value, 2), "unit": unit, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(elapsed_ms / args.steps, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {
-            "workload": f"C2-shaped synthetic scene: {P} Gaussians from {args.V} pointmap views, {W}x{H}, SH degree {D}, "
-                        f"shs+scales/rotations inputs; step = {vps} views/rank (fwd+bwd, dense dL), gradients summed "
-                        f"{'by the fused multi-view backward pass' if fused_bwd else 'in place (per-view accumulate)'} into a "
-                        f"{buckets[0][0].nbytes() // (1 << 20)} MiB fp32 bucket, views spread over {S_} CUDA stream(s)"
-                        + (", one NCCL all-reduce of the bucket per step (overlapped)" if world > 1 else ""),
-            "views_per_step_per_rank": vps, "streams": S_, "P": P, "W": W, "H": H, "sh_degree": D, "num_rendered": R,
-            "l2_policy": "inputs larger than L2 (per step each rank streams ~%d MB of distinct inputs; L2 is 126 MB)" %
-                         ((P * (28 * vps + 208)) // 1_000_000),
+            "workload": f"{args.config}-shaped synthetic scene: {P} Gaussians from {args.V} pointmap views, {W}x{H}, SH degree "
+                        f"{D}, shs+scales/rotations inputs; step = {vps} views/rank, "
+                        + ("forward only" if fwd_only else "fwd+bwd with a dense dL/dcolour, Gaussian-parameter gradients "
+                           "summed over the rank's views into one fp32 bucket, summed across ranks once per step (N > 1)"),
+            "views_per_step_per_rank": vps, "P": P, "W": W, "H": H, "sh_degree": D, "forward_only": fwd_only,
+            "l2_policy": "inputs larger than L2 (per step each rank streams > %d MB of distinct per-Gaussian inputs; "
+                         "L2 is 126 MB)" % ((P * (28 * vps + 44 + s_bytes)) // 1_000_000),
             "parallelism": f"views sharded over {world} rank(s), Gaussians replicated",
         },
+        "impl_detail": impl_detail,
+        "num_rendered": R,  # (Gaussian, tile) instances of the step's last view
+        "step_ms": {"min": round(ss[0], 4), "median": round(ss[len(ss) // 2], 4), "max": round(ss[-1], 4),
+                    "first5": [round(x, 3) for x in step_ms[:5]],
+                    "all": [round(x, 3) for x in step_ms] if args.steps <= 64 else None},
     }
+    if world > 1 and not fwd_only:
+        # the collective alone, on an idle GPU: what the step has to hide
+        flat = bucket.flat
+        for _ in range(3):
+            dist.all_reduce(flat)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(10):
+            dist.all_reduce(flat)
+        a1.record()
+        torch.cuda.synchronize()
+        ar_ms = sharding.all_reduce_max(a0.elapsed_time(a1) / 10, dev)
+        out["allreduce"] = {"bytes": bucket_bytes, "alone_ms": round(ar_ms, 4),
+                            "algbw_gbs": round(bucket_bytes / (ar_ms * 1e-3) / 1e9, 1),
+                            "kernel": "ncclDevKernel_AllReduce_Sum_f32_*"}
     if args.impl != "ours":
         out["impl"] = "reference"
-        out["cpu_baseline"] = {"value": out["value"], "unit": "views/s", "cores": 0, "kind": "reference",
+        out["cpu_baseline"] = {"value": out["value"], "unit": unit, "cores": 0, "kind": "reference",
                                "sample": "reference CUDA rasterizer (oracle/_ref, sm_100 build of the vendored "
                                          "diff-gaussian-rasterization with DAS3R's 0.001 near plane) on the GPU: the "
                                          "reference has no CPU implementation of this path; the CPU port is timed by "
                                          "`--impl oracle-cpu` and in the `ours` line's cpu_baseline"}
-        out["e2e"] = {"value": out["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+        out["e2e"] = {"value": out["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
         out["clocks"] = clocks
         if rank == 0:
             emit((out))
@@ -430,49 +450,62 @@ def main():
     # ---- per-stage device times (CUDA events on the launching stream), profiled pass right after the timed region ---
     C.prof_collect(True)
     C.prof_enable(True)
-    single_stream[0] = True
     prof_steps = max(2, min(args.steps, 10))
     for i in range(prof_steps):
         step(i)
-    drain()
     torch.cuda.synchronize()
-    single_stream[0] = False
     collected = [(name, ms, calls) for name, ms, calls in C.prof_collect(True) if calls > 0]
     stages = {name: (ms / calls) for name, ms, calls in collected}
     stage_total = {name: ms for name, ms, calls in collected}
     C.prof_enable(False)
     peak, peak_src = hbm_peak()
-    sb = stage_bytes(P, R, N, T, s_bytes, fused_views=vps if fused_bwd else 0)
+    Rs = [int(r) for r in all_R[0]]
+    sb = stage_bytes(P, Rs, N, T, s_bytes, vps, vps, fwd_only)
+    n_sl = len(bucket.slices)
+    for k in ("preprocess_bwd", "frontend_bwd"):  # one launch per bucket slice
+        if k in sb:
+            sb[k] = sb[k] // n_sl
     kern = {k: v for k, v in stages.items() if k in sb}
     dom = max(kern, key=lambda k: stage_total[k])  # the kernel with the largest share of the step
     achieved = sb[dom] / (kern[dom] * 1e-3) / 1e9
-    vb = view_bytes(P, R, N, T, s_bytes)
+    vb = view_bytes(P, sum(Rs) / len(Rs), N, T, s_bytes, fwd_only)
     per_view_ms = elapsed_ms / (vps * args.steps)
-    traffic = None
-    try:  # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (not measured by this run)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(dom)
-    except Exception:
-        pass
+    step_must_move = sum(sb[k] * (n_sl if k in ("preprocess_bwd", "frontend_bwd") else 1) for k in sb)
+    traffic, traffic_src = None, None
+    for cand in ("r02_traffic.json", "r01_traffic.json"):
+        try:  # DRAM bytes per launch from a committed `ncu --set full` capture (not measured by this run)
+            t = json.load(open(os.path.join(ROOT, "profiles", cand)))
+            if dom in t:
+                traffic, traffic_src = t[dom], f"profiles/{cand} (ncu --set full capture; not re-measured by this run)"
+                break
+        except Exception:
+            pass
     out["roofline"] = {
         "bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-        "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+        "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": sb[dom], "avg_launch_ms": round(kern[dom], 5),
-        "timing": f"CUDA events around every stage on the launching stream, {prof_steps} single-stream steps right "
-                  "after the timed region",
+        "views_per_launch": vps,
+        "timing": f"CUDA events around every stage on the launching stream, {prof_steps} steps right after the timed "
+                  "region",
         "stage_ms": {k: round(v, 5) for k, v in stages.items()},
         "stage_share_of_step": {k: round(v / sum(stage_total.values()), 4) for k, v in stage_total.items()},
-        "sort_gkeys_per_s": round(R / (stages["tile_sort"] * 1e-3) / 1e9, 2) if "tile_sort" in stages else None,
+        "sort_gkeys_per_s": round(sum(Rs) / (stages["tile_sort"] * 1e-3) / 1e9, 2) if "tile_sort" in stages else None,
         "stage_frac_of_hbm_peak": {k: round(sb[k] / (v * 1e-3) / 1e9 / peak, 4) for k, v in kern.items()},
-        "view": {"algorithmic_bytes": vb, "achieved_gbs": round(vb / (per_view_ms * 1e-3) / 1e9, 1),
+        "view": {"algorithmic_bytes": int(vb), "achieved_gbs": round(vb / (per_view_ms * 1e-3) / 1e9, 1),
                  "frac": round(vb / (per_view_ms * 1e-3) / 1e9 / peak, 4),
-                 "roofline_views_per_s_per_gpu": round(peak * 1e9 / vb, 1)},
+                 "roofline_views_per_s_per_gpu": round(peak * 1e9 / vb, 1),
+                 "what": "SURVEY.md §8d per-view bytes (rasterizer only, each view on its own) x views/s"},
+        "step": {"must_move_bytes": int(step_must_move),
+                 "achieved_gbs": round(step_must_move / (elapsed_ms / args.steps * 1e-3) / 1e9, 1),
+                 "frac": round(step_must_move / (elapsed_ms / args.steps * 1e-3) / 1e9 / peak, 4),
+                 "what": "bytes the fused step (front-end included, shared arrays read once for all views) has to move"},
     }
     out["gpu_launches"] = int(launches)
     out["clocks"] = clocks
 
-    # ---- e2e: public API (GaussianRasterizer + autograd), per-view host inputs from pinned memory -------------------
+    # ---- e2e: public API (render_inputs + MultiViewRasterizer + autograd), host inputs from pinned memory -----------
     if not args.no_e2e:
-        out["e2e"] = run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views)
+        out["e2e"] = run_e2e(args, sc, dev, world, rank, S, dL, my_views, fwd_only)
     # ---- CPU baseline: the C port of the reference algorithm on the host cores (rank 0, N = 1 only) -----------------
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args, sc)
@@ -482,32 +515,29 @@ def main():
         dist.destroy_process_group()
 
 
-def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
-    """views/s through the public Python API with HOST inputs. Per view, inside the timed region: H2D (pinned) of the
-    camera bundle (viewmatrix 16 + projmatrix 16 + campos 3 + bg 3 floats) and of dL/d(colour) [3,H,W]; forward; loss;
-    autograd backward; D2H of the rendered image; D2H of the step's loss. The Gaussian parameters are the resident
-    model state (like weights). For N > 1 the leaf gradients are all-reduced once per step.
+def run_e2e(args, sc, dev, world, rank, S, dL, my_views, fwd_only):
+    """views/s through the public Python API with HOST inputs. Per step, inside the timed region: H2D (pinned) of the
+    step's poses, per view of the camera bundle (viewmatrix 16 + projmatrix 16 + campos 3 + bg 3 floats) and of
+    dL/d(colour) [3,H,W]; front-end; forward; loss; autograd backward down to the raw parameters and the poses; D2H of
+    every rendered image and of the step's loss. The raw Gaussian parameters are the resident model state (like
+    weights). For N > 1 the leaf gradients are all-reduced once per step (blocking).
 
-    Two surfaces are timed: `MultiViewRasterizer` (das3r_b200/multiview.py: all views of the step in one autograd node -
-    the headline `value`) and the drop-in per-view `GaussianRasterizer` (`per_view_api`)."""
+    Surfaces timed: `render_inputs` + `MultiViewRasterizer` (the headline), the same with pre-posed inputs
+    (`pre_posed`), and the drop-in per-view `GaussianRasterizer` (`per_view_api`)."""
     from das3r_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
     from das3r_b200.multiview import MultiViewRasterizer
+    from das3r_b200.frontend import render_inputs
+    from das3r_b200.synth import view_inputs
     from das3r_b200 import sharding
 
-    W, H, D, vps = args.W, args.H, args.sh_degree, args.views_per_step
+    W, H, D, vps, P = args.W, args.H, args.sh_degree, args.views_per_step, args.P
     cam_host = torch.cat([S["view"].flatten().cpu(), S["proj"].flatten().cpu(), S["campos"].cpu(), S["bg"].cpu()]).pin_memory()
     dL_host = dL.cpu().pin_memory()
     cam_dev = [torch.empty_like(cam_host, device=dev) for _ in range(vps)]
     dL_dev = [torch.empty_like(dL_host, device=dev) for _ in range(vps)]
     img_host = [torch.empty(3, H, W).pin_memory() for _ in range(vps)]
     loss_host = torch.empty(1).pin_memory()
-    leaves = dict(shs=S["shs"].clone().requires_grad_(True), opac=S["opac"].clone().requires_grad_(True),
-                  scales=S["scales"].clone().requires_grad_(True))
-    per_view = [dict(means=pv["means"].clone().requires_grad_(True), rots=pv["rots"].clone().requires_grad_(True))
-                for pv in pool]
-    means2D = torch.zeros(args.P, 3, device=dev, requires_grad=True)
-    all_leaves = list(leaves.values()) + [means2D] + [x for pv in per_view for x in pv.values()]
-    mv = MultiViewRasterizer(streams=max(1, min(args.streams, vps)))
+    mv = MultiViewRasterizer()
     copy_stream = torch.cuda.Stream(device=dev)
 
     def settings_for(v):
@@ -517,23 +547,20 @@ def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
             viewmatrix=c[0:16].view(4, 4), projmatrix=c[16:32].view(4, 4), sh_degree=D, campos=c[32:35],
             prefiltered=False, debug=False)
 
-    def reduce_grads():
-        if world > 1:
-            for t in (leaves["shs"], leaves["opac"], leaves["scales"], per_view[0]["means"], per_view[0]["rots"]):
-                dist.all_reduce(t.grad)
+    raw = dict(xyz=sc.xyz.to(dev), rotation=sc.rot.to(dev), opacity=torch.logit(sc.opacity.clamp(1e-6, 1 - 1e-6)).to(dev),
+               scaling=torch.log(sc.scales).to(dev), features_dc=sc.shs[:, :1].contiguous().to(dev),
+               features_rest=sc.shs[:, 1:].contiguous().to(dev), conf_static=torch.ones(P, device=dev))
+    raw = {k: v.contiguous().requires_grad_(True) for k, v in raw.items()}
+    poses_host = sc.poses[my_views].contiguous().pin_memory()
+    poses_dev = torch.empty(vps, 7, device=dev, requires_grad=True)
 
-    def step_multi():
+    def finish_step(colors, leaves):
         main = torch.cuda.current_stream()
-        for t in all_leaves:
-            t.grad = None  # optimizer.zero_grad(set_to_none=True)
-        for v in range(vps):
-            cam_dev[v].copy_(cam_host, non_blocking=True)
-        copy_stream.wait_stream(main)  # the previous step is done with dL_dev
-        with torch.cuda.stream(copy_stream):
-            for v in range(vps):
-                dL_dev[v].copy_(dL_host, non_blocking=True)  # only needed by the loss: overlaps the forwards
-        colors, _radii = mv([settings_for(v) for v in range(vps)], [pv["means"] for pv in per_view],
-                            [pv["rots"] for pv in per_view], leaves["opac"], leaves["shs"], leaves["scales"])
+        if fwd_only:
+            for v, c in enumerate(colors):
+                img_host[v].copy_(c.detach(), non_blocking=True)
+            main.synchronize()
+            return
         main.wait_stream(copy_stream)
         loss = sum((c * dL_dev[v]).sum() for v, c in enumerate(colors))
         copy_stream.wait_stream(main)
@@ -543,31 +570,86 @@ def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
                 c.record_stream(copy_stream)
         loss.backward()
         loss_host.copy_(loss.detach().view(1), non_blocking=True)
-        reduce_grads()
+        if world > 1:
+            for t in leaves:
+                if t.grad is not None:
+                    dist.all_reduce(t.grad)
         main.wait_stream(copy_stream)
         main.synchronize()  # the step's images and loss are on the host now
 
-    def step_per_view():
-        for t in all_leaves:
-            if t.grad is not None:
-                t.grad.zero_()
-        total = None
-        for v, pv in enumerate(per_view):
+    def host_inputs():
+        main = torch.cuda.current_stream()
+        for v in range(vps):
             cam_dev[v].copy_(cam_host, non_blocking=True)
-            dL_dev[v].copy_(dL_host, non_blocking=True)
-            color, _radii = GaussianRasterizer(settings_for(v))(
-                means3D=pv["means"], means2D=means2D, opacities=leaves["opac"], shs=leaves["shs"],
-                scales=leaves["scales"], rotations=pv["rots"])
-            loss = (color * dL_dev[v]).sum()
-            loss.backward()
-            img_host[v].copy_(color.detach(), non_blocking=True)
-            total = loss.detach() if total is None else total + loss.detach()
-        loss_host.copy_(total.view(1), non_blocking=True)
-        reduce_grads()
+        if not fwd_only:
+            copy_stream.wait_stream(main)  # the previous step is done with dL_dev
+            with torch.cuda.stream(copy_stream):
+                for v in range(vps):
+                    dL_dev[v].copy_(dL_host, non_blocking=True)  # only needed by the loss: overlaps the forwards
+
+    def step_frontend():
+        leaves = list(raw.values()) + [poses_dev]
+        for t in leaves:
+            t.grad = None
+        with torch.no_grad():
+            poses_dev.copy_(poses_host, non_blocking=True)
+        host_inputs()
+        ctx = torch.no_grad() if fwd_only else torch.enable_grad()
+        with ctx:
+            fe = render_inputs(raw["xyz"], raw["rotation"], raw["opacity"], raw["scaling"], raw["features_dc"],
+                               raw["features_rest"], raw["conf_static"], None, poses_dev, sh_degree=D)
+            colors, _radii = mv([settings_for(v) for v in range(vps)], fe.means3D, fe.rotations, fe.opacity, fe.shs,
+                                fe.scales)
+            finish_step(colors, leaves)
+
+    # pre-posed inputs (the rasterizer alone, like the reference arm)
+    pool = []
+    for v in my_views:
+        vi = view_inputs(sc, v)
+        pool.append(dict(means=vi["means3D"].contiguous().to(dev).requires_grad_(True),
+                         rots=vi["rotations"].contiguous().to(dev).requires_grad_(True)))
+    shared = dict(shs=S["shs"].clone().requires_grad_(True), opac=S["opac"].clone().requires_grad_(True),
+                  scales=S["scales"].clone().requires_grad_(True))
+    means2D = torch.zeros(P, 3, device=dev, requires_grad=True)
+    pp_leaves = list(shared.values()) + [means2D] + [x for pv in pool for x in pv.values()]
+
+    def step_pre_posed():
+        for t in pp_leaves:
+            t.grad = None
+        host_inputs()
+        ctx = torch.no_grad() if fwd_only else torch.enable_grad()
+        with ctx:
+            colors, _radii = mv([settings_for(v) for v in range(vps)], [pv["means"] for pv in pool],
+                                [pv["rots"] for pv in pool], shared["opac"], shared["shs"], shared["scales"])
+            finish_step(colors, list(shared.values()) + [pool[0]["means"], pool[0]["rots"]])
+
+    def step_per_view():
+        for t in pp_leaves:
+            t.grad = None
+        total = None
+        ctx = torch.no_grad() if fwd_only else torch.enable_grad()
+        with ctx:
+            for v, pv in enumerate(pool):
+                cam_dev[v].copy_(cam_host, non_blocking=True)
+                if not fwd_only:
+                    dL_dev[v].copy_(dL_host, non_blocking=True)
+                color, _radii = GaussianRasterizer(settings_for(v))(
+                    means3D=pv["means"], means2D=means2D, opacities=shared["opac"], shs=shared["shs"],
+                    scales=shared["scales"], rotations=pv["rots"])
+                if not fwd_only:
+                    loss = (color * dL_dev[v]).sum()
+                    loss.backward()
+                    total = loss.detach() if total is None else total + loss.detach()
+                img_host[v].copy_(color.detach(), non_blocking=True)
+        if total is not None:
+            loss_host.copy_(total.view(1), non_blocking=True)
+            if world > 1:
+                for t in list(shared.values()) + [pool[0]["means"], pool[0]["rots"]]:
+                    dist.all_reduce(t.grad)
         torch.cuda.current_stream().synchronize()
 
     def timed(step, steps):
-        for _ in range(2):
+        for _ in range(3):
             step()
         if world > 1:
             dist.barrier()
@@ -583,66 +665,25 @@ def run_e2e(args, sc, dev, world, rank, pool, S, dL, my_views):
             dist.barrier()
         return round(world * vps * steps / (ms / 1e3), 2)
 
-    # The same step started one stage earlier: raw model parameters + camera poses -> fused front-end
-    # (das3r_b200/frontend.py: what gaussian_renderer/__init__.py:83-126 does with ~10 torch kernels per view) ->
-    # MultiViewRasterizer; the backward reaches the raw parameters and the poses.
-    from das3r_b200.frontend import render_inputs
-    raw = dict(xyz=per_view[0]["means"].detach().clone(), rotation=per_view[0]["rots"].detach().clone(),
-               opacity=torch.logit(S["opac"].clamp(1e-6, 1 - 1e-6)), scaling=torch.log(S["scales"]),
-               features_dc=S["shs"][:, :1].contiguous(), features_rest=S["shs"][:, 1:].contiguous(),
-               conf_static=torch.ones(args.P, device=dev))
-    raw = {k: v.requires_grad_(True) for k, v in raw.items()}
-    poses_host = torch.tensor([[1.0, 0, 0, 0, 0, 0, 0]] * vps).pin_memory()  # identity: the scene stays in view
-    poses_dev = torch.empty(vps, 7, device=dev, requires_grad=True)
-
-    def step_frontend():
-        main = torch.cuda.current_stream()
-        for t in list(raw.values()) + [poses_dev]:
-            t.grad = None
-        with torch.no_grad():
-            poses_dev.copy_(poses_host, non_blocking=True)
-        for v in range(vps):
-            cam_dev[v].copy_(cam_host, non_blocking=True)
-        copy_stream.wait_stream(main)
-        with torch.cuda.stream(copy_stream):
-            for v in range(vps):
-                dL_dev[v].copy_(dL_host, non_blocking=True)
-        fe = render_inputs(raw["xyz"], raw["rotation"], raw["opacity"], raw["scaling"], raw["features_dc"],
-                           raw["features_rest"], raw["conf_static"], None, poses_dev)
-        colors, _radii = mv([settings_for(v) for v in range(vps)], fe.means3D, fe.rotations, fe.opacity, fe.shs, fe.scales)
-        main.wait_stream(copy_stream)
-        loss = sum((c * dL_dev[v]).sum() for v, c in enumerate(colors))
-        copy_stream.wait_stream(main)
-        with torch.cuda.stream(copy_stream):
-            for v, c in enumerate(colors):
-                img_host[v].copy_(c.detach(), non_blocking=True)
-                c.record_stream(copy_stream)
-        loss.backward()
-        loss_host.copy_(loss.detach().view(1), non_blocking=True)
-        if world > 1:
-            for t in raw.values():
-                dist.all_reduce(t.grad)
-        main.wait_stream(copy_stream)
-        main.synchronize()
-
     steps = max(3, min(args.steps // 3, 40))
-    v_multi = timed(step_multi, steps)
-    v_single = timed(step_per_view, steps)
     v_front = timed(step_frontend, steps)
-    return {"value": v_multi, "unit": "views/s",
-            "h2d_bytes_per_step": vps * (38 * 4 + 3 * H * W * 4), "d2h_bytes_per_step": vps * (3 * H * W * 4) + 4,
+    v_multi = timed(step_pre_posed, steps)
+    v_single = timed(step_per_view, steps)
+    img_b = 3 * H * W * 4
+    return {"value": v_front, "unit": "views/s",
+            "h2d_bytes_per_step": vps * (38 * 4 + (0 if fwd_only else img_b)) + vps * 7 * 4,
+            "d2h_bytes_per_step": vps * img_b + (0 if fwd_only else 4),
             "steps": steps,
-            "what": "das3r_b200.multiview.MultiViewRasterizer (all views of the step in one autograd node: forwards and "
-                    "backward blends on CUDA streams, one fused gradient pass) + autograd; per view H2D (pinned) of the "
-                    "camera bundle and dL/dcolour and D2H of the rendered image, per step D2H of the loss; Gaussian "
-                    "parameters resident (model state)",
-            "from_raw_parameters": {"value": v_front, "unit": "views/s",
-                                    "what": "same step started from the raw model parameters and camera poses: fused "
-                                            "front-end (das3r_b200.frontend.render_inputs) + MultiViewRasterizer; "
-                                            "gradients reach the raw parameters and the poses"},
+            "what": "das3r_b200.frontend.render_inputs + das3r_b200.multiview.MultiViewRasterizer + autograd: raw model "
+                    "parameters and the step's poses -> images -> gradients of the raw parameters and the poses; per step "
+                    "H2D (pinned) of the poses, per view of the camera bundle and dL/dcolour, D2H of every rendered image "
+                    "and of the loss; Gaussian parameters resident (model state)",
+            "pre_posed": {"value": v_multi, "unit": "views/s",
+                          "what": "MultiViewRasterizer alone on pre-posed means/rotations (what the reference arm times), "
+                                  "same copies"},
             "per_view_api": {"value": v_single, "unit": "views/s",
                              "what": "the drop-in GaussianRasterizer.forward + autograd backward called once per view, "
-                                     "single stream, same copies"}}
+                                     "same copies"}}
 
 
 def cpu_baseline(args, sc):
@@ -661,11 +702,13 @@ def cpu_baseline(args, sc):
         vi = view_inputs(sc, v % sc.V, sh_degree=args.sh_degree)
         a = time.perf_counter()
         fw = oracle.forward(**vi)
-        oracle.backward(fw, dL, **vi)
+        if not args.forward_only:
+            oracle.backward(fw, dL, **vi)
         t += time.perf_counter() - a
     return {"value": round(n / t, 4), "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": f"{n} views (fwd+bwd) of the same {args.P}-Gaussian {args.W}x{args.H} scene through the C port of "
-                      f"the reference algorithm (oracle/raster_oracle.c, OpenMP on all {os.cpu_count()} host cores)"}
+            "sample": f"{n} views ({'forward' if args.forward_only else 'fwd+bwd'}) of the same {args.P}-Gaussian "
+                      f"{args.W}x{args.H} scene through the C port of the reference algorithm (oracle/raster_oracle.c, "
+                      f"OpenMP on all {os.cpu_count()} host cores)"}
 
 
 def run_cpu_arm(args):

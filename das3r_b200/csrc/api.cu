@@ -93,10 +93,11 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
 // ---- optional per-stage CUDA-event timing + kernel launch counter (bench.py's roofline leg) ------------------------
 enum Stage {
     ST_PREPROCESS_FWD = 0, ST_TILE_SCAN, ST_SCATTER, ST_TILE_SORT, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
-    ST_MEMSET, ST_RECT_LISTS, ST_COUNT
+    ST_MEMSET, ST_RECT_LISTS, ST_FRONTEND_FWD, ST_FRONTEND_BWD, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "blend_fwd",
-                                           "blend_bwd", "preprocess_bwd", "memset", "rect_lists"};
+                                           "blend_bwd", "preprocess_bwd", "memset", "rect_lists", "frontend_fwd",
+                                           "frontend_bwd"};
 struct Pending {
     int stage;
     cudaEvent_t a, b;
@@ -949,8 +950,11 @@ int das3r_frontend_forward_ex(const das3r_frontend_model* model, int32_t n_views
         a.means3D[v] = out->means3D[v];
         a.rotations[v] = out->rotations[v];
     }
-    cudaError_t e = launch_frontend_fwd(a, stream);
-    g_launches += 1;
+    cudaError_t e;
+    {
+        StageScope scope_(ST_FRONTEND_FWD, stream, 1);
+        e = launch_frontend_fwd(a, stream);
+    }
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_fwd", e);
     return DAS3R_OK;
 }
@@ -1016,8 +1020,11 @@ int das3r_frontend_backward_ex(const das3r_frontend_model* model, int32_t n_view
     a.dL_dscaling_raw = gout->dL_dscaling; a.dL_dfeatures_dc = gout->dL_dfeatures_dc;
     a.dL_dfeatures_rest = gout->dL_dfeatures_rest; a.dL_dconf = gout->dL_dconf;
     a.partials = gout->scratch;
-    cudaError_t e = launch_frontend_bwd(a, finish ? gout->dL_dposes : nullptr, stream);
-    g_launches += (count > 0 ? 1 : 0) + (finish ? 1 : 0);
+    cudaError_t e;
+    {
+        StageScope scope_(ST_FRONTEND_BWD, stream, (count > 0 ? 1 : 0) + (finish ? 1 : 0));
+        e = launch_frontend_bwd(a, finish ? gout->dL_dposes : nullptr, stream);
+    }
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "frontend_bwd", e);
     return DAS3R_OK;
 }

