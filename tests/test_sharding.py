@@ -75,8 +75,22 @@ def _worker(rank, world, port, out):
     h = bucket.all_reduce(async_op=True)
     h.wait()
     mx = sharding.all_reduce_max(float(rank + 1), "cpu")
+    # the slice-major bucket: every slice reduced by its own asynchronous collective, all waited on at the end
+    sb = sharding.SlicedGradBucket(700, sharding.raw_param_widths(0), "cpu", n_slices=3, tail={"poses": (2, 7)})
+    handles = []
+    for c in range(len(sb.slices)):
+        for w in sb.windows(c).values():
+            w.fill_(float(rank + 1 + c))
+        if c == len(sb.slices) - 1:
+            sb.tail("poses").fill_(float(rank + 1))
+        handles.append(sb.all_reduce_slice(c, async_op=True))
+    for h in handles:
+        h.wait()
     if rank == 0:
-        torch.save({"flat": bucket.flat.clone(), "max": mx}, out)
+        torch.save({"views": {k: v.clone() for k, v in bucket.views().items()}, "max": mx,
+                    "sliced": [float(sb.window(c, "xyz").min()) for c in range(len(sb.slices))] +
+                              [float(sb.window(c, "xyz").max()) for c in range(len(sb.slices))],
+                    "poses": sb.tail("poses").clone()}, out)
     dist.destroy_process_group()
 
 
@@ -86,8 +100,12 @@ def test_allreduce_over_gloo_world2(tmp_path):
     mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
     res = torch.load(out)
     # steps 0,1 x ranks 0,1 consume views 0,1,2,3 -> values 1+2+3+4 = 10 everywhere
-    assert torch.all(res["flat"] == 10.0)
+    for k, v in res["views"].items():
+        assert torch.all(v == 10.0), k
     assert res["max"] == 2.0
+    n = len(res["sliced"]) // 2
+    assert res["sliced"] == [3.0 + 2 * c for c in range(n)] * 2  # (1 + c) + (2 + c) in every element of slice c
+    assert torch.all(res["poses"] == 3.0)
 
 
 def test_sliced_bucket_layout():
