@@ -141,7 +141,10 @@ def knn_dist2_cpu(xyz: torch.Tensor) -> torch.Tensor:
 
 
 def synth_scene(P: int, V: int, W: int, H: int, seed: int, sh_degree: int = 3, n_poses: int | None = None,
-                focal_mul: float = 1.1, opacity_views: int | None = None, depth_noise: float = 7e-4) -> Scene:
+                focal_mul: float = 1.1, opacity_views: int | None = None, depth_noise: float = 7e-4,
+                dist2_fn=None) -> Scene:
+    """dist2_fn: optional replacement for the CPU k-d tree that gives the 3-NN mean squared distances (e.g. distCUDA2
+    on the GPU for the multi-million-point configs, where the tree takes minutes); xyz [P,3] float32 CPU -> [P] CPU."""
     g = torch.Generator().manual_seed(seed)
     focal = focal_mul * W
     poses = _camera_arc(V)
@@ -181,7 +184,7 @@ def synth_scene(P: int, V: int, W: int, H: int, seed: int, sh_degree: int = 3, n
         world = (dirs * zc[:, None] - t) @ R
         chunks.append(world.float())
     xyz = torch.cat(chunks, dim=0).contiguous().float()
-    dist2 = knn_dist2_cpu(xyz).clamp_min(1e-7)
+    dist2 = (dist2_fn(xyz) if dist2_fn is not None else knn_dist2_cpu(xyz)).clamp_min(1e-7)
     scales = torch.sqrt(dist2)[:, None].repeat(1, 3).contiguous()
     rot = torch.zeros(P, 4)
     rot[:, 0] = 1.0

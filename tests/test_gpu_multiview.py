@@ -83,7 +83,7 @@ def _check(outs, want, what):
         assert err <= Hn.GRAD_RTOL, f"{what}: {n} differs from the sum of per-view backwards by {err}"
 
 
-@pytest.mark.parametrize("D,V", [(3, 4), (1, 3), (3, 1), (3, 18)])
+@pytest.mark.parametrize("D,V", [(3, 4), (1, 3), (3, 1), (3, 18), (0, 3), (2, 5), (0, 18)])
 def test_sum_over_views_matches_the_per_view_backward(D, V):
     dev = torch.device("cuda:0")
     C = load_native()
@@ -101,8 +101,8 @@ def test_sum_over_views_matches_the_per_view_backward(D, V):
     _check(outs, [2 * w for w in want], f"D={D} V={V} accumulate")
 
 
-@pytest.mark.parametrize("D", [3, 1])
-def test_per_view_mean_and_rotation_gradients(D):
+@pytest.mark.parametrize("D,M4", [(3, False), (1, False), (0, False), (1, True)])
+def test_per_view_mean_and_rotation_gradients(D, M4):
     """Views 0 and 2 ask for their own dL_dmeans3D / dL_drotations (what DAS3R needs to go back through each view's
     pose); view 1 joins the summed outputs. D=1 exercises the per-view fallback, which supports this only when
     accumulating."""
@@ -110,6 +110,10 @@ def test_per_view_mean_and_rotation_gradients(D):
     C = load_native()
     V, P, W, H = 3, 8_000, 128, 80
     views, dLs = _scene_views(P, V, W, H, D, seed=21, dev=dev)
+    if M4:  # 4-coefficient rows (max_sh_degree 1): not the fused kernel but one accumulating one-view pass per view
+        sh4 = views[0]["shs"][:, :4].contiguous()
+        for vi in views:
+            vi["shs"] = sh4
     M = views[0]["shs"].shape[1]
     e = torch.Tensor([])
     singles, states = [], []
@@ -120,8 +124,8 @@ def test_per_view_mean_and_rotation_gradients(D):
                                              vi["viewmatrix"], vi["projmatrix"], vi["tanfovx"], vi["tanfovy"], dL,
                                              vi["shs"], D, vi["campos"], geom, R, binning, img, False)
         singles.append([out[i].double() for i in IDX])
-    accumulate = D != 3
-    fill = 0.0 if accumulate else float("nan")
+    accumulate = False  # every path overwrites: fused kernel, or the per-view fallback clearing a view's own outputs
+    fill = float("nan")
     outs = _fresh(P, M, dev, fill=fill)
     per_view = [(torch.full((P, 3), fill, device=dev), torch.full((P, 4), fill, device=dev)), None,
                 (torch.full((P, 3), fill, device=dev), torch.full((P, 4), fill, device=dev))]
@@ -206,7 +210,7 @@ def test_multiview_rasterizer_matches_the_per_view_module(D):
         assert Hn.rel_err(rb.grad, ra.grad) <= Hn.GRAD_RTOL, f"rotations of view {v}"
 
 
-@pytest.mark.parametrize("D,V", [(3, 5), (1, 2), (3, 18)])
+@pytest.mark.parametrize("D,V", [(3, 5), (1, 2), (3, 18), (0, 3), (2, 4), (0, 17)])
 def test_forward_split_is_bit_identical_to_the_one_call_forward(D, V):
     """das3r_raster_forward_preprocess (all views in one call: one kernel when they share degree-3 SH rows, the one-view
     kernel otherwise, chunks of 16) + das3r_raster_forward_render per view against das3r_raster_forward: image, radii,
@@ -233,3 +237,113 @@ def test_forward_split_is_bit_identical_to_the_one_call_forward(D, V):
         assert torch.equal(tiles(geom), tiles(w[3]))
         clamp = lambda g: g[L.g_clamped:L.g_clamped + P][vis]
         assert torch.equal(clamp(geom), clamp(w[3]))
+
+
+@pytest.mark.parametrize("D", [3, 0])
+def test_more_views_than_one_launch_with_per_view_outputs(D):
+    """18 views (one launch takes 16), every view with its own dL_dmeans3D / dL_drotations, overwrite mode: the second
+    launch must overwrite ITS views' buffers (NaN-poisoned here) while it adds to the summed outputs."""
+    dev = torch.device("cuda:0")
+    C = load_native()
+    V, P, W, H = 18, 6_000, 112, 80
+    views, dLs = _scene_views(P, V, W, H, D, seed=23, dev=dev)
+    e = torch.Tensor([])
+    singles, states = [], []
+    for vi, dL in zip(views, dLs):
+        R, color, radii, geom, binning, img = _forward(C, vi, D)
+        states.append((R, radii, geom, binning, img))
+        out = C.rasterize_gaussians_backward(vi["bg"], vi["means3D"], radii, e, vi["scales"], vi["rotations"], 1.0, e,
+                                             vi["viewmatrix"], vi["projmatrix"], vi["tanfovx"], vi["tanfovy"], dL,
+                                             vi["shs"], D, vi["campos"], geom, R, binning, img, False)
+        singles.append([out[i].double() for i in IDX])
+    nan = float("nan")
+    outs = _fresh(P, 16, dev)
+    per_view = [(torch.full((P, 3), nan, device=dev), torch.full((P, 4), nan, device=dev)) for _ in range(V)]
+    _fused(C, views, dLs, states, D, outs, accumulate=False, per_view=per_view)
+    for k in (0, 2, 3):  # opacity, sh, scales are summed over all 18 views
+        want = sum(s[k] for s in singles)
+        assert Hn.rel_err(outs[k].double().cpu().numpy(), want.cpu().numpy()) <= Hn.GRAD_RTOL, NAMES[k]
+    for v in range(V):
+        for got, w, n in ((per_view[v][0], singles[v][1], "dL_dmeans3D"), (per_view[v][1], singles[v][4], "dL_drotations")):
+            assert bool(torch.isfinite(got).all()), f"view {v} {n}: not every element was written"
+            assert Hn.rel_err(got.double().cpu().numpy(), w.cpu().numpy()) <= Hn.GRAD_RTOL, f"view {v} {n}"
+
+
+@pytest.mark.parametrize("D", [0, 1, 2, 3])
+def test_trimmed_rows_and_gaussian_ranges(D):
+    """das3r_raster_backward_finish_ex: dL_dsh rows trimmed to the (D+1)^2 active coefficients, computed range by range
+    (absolute-indexed buffers and slice-local windows), equal the full-row one-call result."""
+    dev = torch.device("cuda:0")
+    C = load_native()
+    V, P, W, H = 3, 5_003, 128, 80
+    K = (D + 1) ** 2
+    views, dLs = _scene_views(P, V, W, H, D, seed=61 + D, dev=dev)
+    want, states = _regular_sum(C, views, dLs, D)
+    e = torch.Tensor([])
+    fv = []
+    for vi, dL, (R, radii, geom, binning, img) in zip(views, dLs, states):
+        acc = C.rasterize_gaussians_backward_blend(vi["bg"], dL, P, geom, R, binning, img, False)
+        fv.append((vi["means3D"], radii, vi["scales"], vi["rotations"], vi["viewmatrix"], vi["projmatrix"],
+                   float(vi["tanfovx"]), float(vi["tanfovy"]), vi["campos"], geom, acc, H, W, e, e))
+    nan = float("nan")
+    shapes = ((P, 1), (P, 3), (P, K, 3), (P, 3), (P, 4))
+    outs = [torch.full(s, nan, device=dev) for s in shapes]
+    ranges = [(0, 2048), (2048, 1024), (3072, P - 3072)]
+    for first, count in ranges:
+        C.rasterize_gaussians_backward_finish_ex(fv, views[0]["shs"], D, 1.0, outs, False, False, K, first, count)
+    torch.cuda.synchronize()
+    want_t = list(want)
+    want_t[2] = want[2][:, :K]
+    assert float(want[2][:, K:].abs().max()) == 0.0 if K < 16 else True
+    _check(outs, want_t, f"D={D} trimmed, absolute ranges")
+    # slice-local windows (what a slice-major gradient bucket hands over)
+    for first, count in ranges:
+        loc = [torch.full((count,) + s[1:], nan, device=dev) for s in shapes]
+        C.rasterize_gaussians_backward_finish_ex(fv, views[0]["shs"], D, 1.0, loc, False, False, K, first, count)
+        torch.cuda.synchronize()
+        _check(loc, [w[first:first + count] for w in want_t], f"D={D} trimmed, local window at {first}")
+    # accumulate on top
+    for first, count in ranges:
+        C.rasterize_gaussians_backward_finish_ex(fv, views[0]["shs"], D, 1.0, outs, True, False, K, first, count)
+    torch.cuda.synchronize()
+    _check(outs, [2 * w for w in want_t], f"D={D} trimmed, accumulate")
+
+
+@pytest.mark.parametrize("D,V", [(3, 5), (0, 3), (1, 18)])
+def test_batched_render_and_blend_match_the_per_view_calls(D, V):
+    """das3r_raster_forward_render_batch / das3r_raster_backward_blend_batch (one launch per stage for all views)
+    against the per-view entry points: images, radii, point lists, n_contrib, final_T bit-identical; the accumulators
+    equal up to the order of the atomic additions."""
+    dev = torch.device("cuda:0")
+    C = load_native()
+    P, W, H = 25_000, 176, 112
+    views, dLs = _scene_views(P, V, W, H, D, seed=70 + D, dev=dev)
+
+    def pre():
+        return C.rasterize_gaussians_forward_preprocess(
+            [(vi["bg"], vi["means3D"], vi["rotations"], vi["viewmatrix"], vi["projmatrix"], float(vi["tanfovx"]),
+              float(vi["tanfovy"]), H, W, vi["campos"]) for vi in views], views[0]["opacities"], views[0]["scales"],
+            views[0]["shs"], D, 1.0, False, True)
+
+    pa = pre()
+    single = [C.rasterize_gaussians_forward_render(vi["bg"], p[0], p[1], p[2], p[3], True) for vi, p in zip(views, pa)]
+    pb = pre()
+    batch = C.rasterize_gaussians_forward_render_batch([(vi["bg"], p[0], p[1], p[2], p[3]) for vi, p in zip(views, pb)], True)
+    torch.cuda.synchronize()
+    for v in range(V):
+        Ra, bina = single[v]
+        Rb, binb = batch[v]
+        assert Ra == Rb
+        assert torch.equal(pa[v][0], pb[v][0]) and torch.equal(pa[v][1], pb[v][1])
+        L = Hn.layout(P, W, H, Ra)
+        for off, cnt in ((L.b_point_list, 4 * Ra), (L.b_keys_sorted, 8 * Ra)):
+            assert torch.equal(bina[off:off + cnt], binb[off:off + cnt])
+        for off, cnt in ((L.i_final_T, 4 * W * H), (L.i_n_contrib, 4 * W * H)):
+            assert torch.equal(pa[v][3][off:off + cnt], pb[v][3][off:off + cnt])
+    acc_single = [C.rasterize_gaussians_backward_blend(vi["bg"], dL, P, pa[v][2], single[v][0], single[v][1], pa[v][3], True)
+                  for v, (vi, dL) in enumerate(zip(views, dLs))]
+    acc_batch = C.rasterize_gaussians_backward_blend_batch(
+        [(vi["bg"], dL, pb[v][2], batch[v][0], batch[v][1], pb[v][3]) for v, (vi, dL) in enumerate(zip(views, dLs))], P, True)
+    torch.cuda.synchronize()
+    for a, b in zip(acc_single, acc_batch):
+        assert Hn.rel_err(b[:, :9], a[:, :9]) <= 1e-4
