@@ -74,6 +74,16 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* f, float3 pos,
     return make_float3(res[0] < 0.0f ? 0.0f : res[0], res[1] < 0.0f ? 0.0f : res[1], res[2] < 0.0f ? 0.0f : res[2]);
 }
 
+// SH degrees 0..2 go through ONE out-of-line copy of the evaluation: inlined, the compiler contracts products like
+// xx - yy into different FMAs in the one-view and the multi-view kernel (seen at degree 2: a 1-ulp colour difference),
+// and the two must agree bit for bit. Degree 3 stays inline (its rows are staged and both kernels were verified equal).
+__device__ __noinline__ float3 sh_to_rgb_low(int deg, const float* f, float3 pos, float3 campos, uint8_t* clamped) {
+    uint8_t cl = 0;
+    const float3 rgb = sh_to_rgb(deg, f, pos, campos, cl);
+    *clamped = cl;
+    return rgb;
+}
+
 constexpr int PRE_THREADS = 256;
 constexpr int SH_ROW_F4 = 12;      // 48 floats = 12 float4 per degree-3 row
 constexpr int SH_ROW_PAD_F4 = 13;  // padded row pitch in shared memory: 13 float4 (odd) -> conflict-free LDS.128
@@ -187,20 +197,28 @@ __device__ __forceinline__ void pre_finish(const PreFwdArgs& a, const int idx, c
         float3 rgb;
         uint8_t cl = 0;
         if (a.colors_precomp == nullptr) {
-            float f[48];
-            if (STAGE_SH) {
-#pragma unroll
-                for (int j = 0; j < SH_ROW_F4; j++) {
-                    float4 v = sh_row[j];
-                    f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
-                }
-            } else {
+            const float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
+            if (!STAGE_SH && a.D < 3) {
+                float fl[27];
                 const float* row = a.shs + (size_t)idx * 3 * a.M;
-                bool aligned = ((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
-                load_sh_row(row, a.D, aligned, f);
+                const bool aligned = ((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+                load_sh_row(row, a.D, aligned, fl);
+                rgb = sh_to_rgb_low(a.D, fl, g.p_orig, cam, &cl);
+            } else {
+                float f[48];
+                if (STAGE_SH) {
+#pragma unroll
+                    for (int j = 0; j < SH_ROW_F4; j++) {
+                        float4 v = sh_row[j];
+                        f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
+                    }
+                } else {
+                    const float* row = a.shs + (size_t)idx * 3 * a.M;
+                    bool aligned = ((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+                    load_sh_row(row, a.D, aligned, f);
+                }
+                rgb = sh_to_rgb(a.D, f, g.p_orig, cam, cl);
             }
-            float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
-            rgb = sh_to_rgb(a.D, f, g.p_orig, cam, cl);
         } else {
             rgb = {a.colors_precomp[3 * idx], a.colors_precomp[3 * idx + 1], a.colors_precomp[3 * idx + 2]};
         }
