@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=None)
     ap.add_argument("--slices", type=int, default=4,
                     help="gradient bucket slices: slice c is all-reduced while slice c+1 is computed (N > 1)")
+    ap.add_argument("--nccl-normal-priority", action="store_true",
+                    help="NCCL's stream at normal priority (default: high, so that a slice's all-reduce is not queued "
+                         "behind the blocks of the next slice's gradient kernels)")
     ap.add_argument("--no-trim", action="store_true", help="all-reduce all 16 SH bands even when the degree is below 3")
     ap.add_argument("--forward-only", action="store_true", help="forward only (C5 sets it)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -224,7 +227,16 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout for the one JSON line
-        dist.init_process_group("nccl", device_id=dev)
+        opts = None
+        if not args.nccl_normal_priority:
+            try:
+                opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+            except Exception:
+                opts = None
+        if opts is not None:
+            dist.init_process_group("nccl", device_id=dev, pg_options=opts)
+        else:
+            dist.init_process_group("nccl", device_id=dev)
 
     if args.impl == "ours":
         from das3r_b200 import load_native
