@@ -68,6 +68,11 @@ def parse_args():
     ap.add_argument("--nccl-normal-priority", action="store_true",
                     help="NCCL's stream at normal priority (default: high, so that a slice's all-reduce is not queued "
                          "behind the blocks of the next slice's gradient kernels)")
+    ap.add_argument("--unbalanced", action="store_true",
+                    help="shard the step's views by position in the permutation instead of by cost (num_rendered)")
+    ap.add_argument("--sweep-slices", default="",
+                    help="developer option: comma-separated slice counts timed one after the other in this process "
+                         "(extra lines on stderr); the JSON line reports --slices")
     ap.add_argument("--no-trim", action="store_true", help="all-reduce all 16 SH bands even when the degree is below 3")
     ap.add_argument("--forward-only", action="store_true", help="forward only (C5 sets it)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -257,15 +262,30 @@ def main():
     N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     fwd_only = bool(args.forward_only)
     perm = torch.randperm(sc.V, generator=torch.Generator().manual_seed(1234)).tolist()
-    my_views = sharding.shard_views(perm, 0, rank, world, vps)
     empty = torch.Tensor([])
-    vi0 = view_inputs(sc, my_views[0])
+    vi0 = view_inputs(sc, 0)
     S = dict(shs=vi0["shs"].to(dev), opac=vi0["opacities"].to(dev), scales=vi0["scales"].to(dev), bg=vi0["bg"].to(dev),
              view=vi0["viewmatrix"].to(dev).contiguous(), proj=vi0["projmatrix"].to(dev).contiguous(),
              campos=vi0["campos"].to(dev).contiguous(), tanx=float(vi0["tanfovx"]), tany=float(vi0["tanfovy"]))
     dL = grad_seed(sc).to(dev)
     last_R = [0]
     all_R = [[0] * vps]
+
+    # ---- which views this rank takes: the step's world*vps views dealt by cost (num_rendered of every view, computed
+    # once here by each arm with its own forward - the counts are bit-identical, so both arms get the same assignment)
+    step_views = sorted(set(perm[j % sc.V] for j in range(world * vps)))
+    costs = [0.0] * sc.V
+    if world > 1 and not args.unbalanced:
+        for v in step_views:
+            vi = view_inputs(sc, v)
+            a_ = (S["bg"], vi["means3D"].contiguous().to(dev), empty, S["opac"], S["scales"],
+                  vi["rotations"].contiguous().to(dev), 1.0, empty, S["view"], S["proj"], S["tanx"], S["tany"], H, W,
+                  S["shs"], D, S["campos"], False, False)
+            costs[v] = float(C.rasterize_gaussians(*a_)[0])
+        my_views = sharding.shard_views_balanced(perm, costs, 0, rank, world, vps)
+    else:
+        my_views = sharding.shard_views(perm, 0, rank, world, vps)
+    torch.cuda.empty_cache()
 
     if args.impl == "ours":
         # raw model parameters (what GaussianModel holds) + this rank's poses: the front-end poses the Gaussians
@@ -280,7 +300,8 @@ def main():
         Kb = K if not args.no_trim else 16
         widths = sharding.raw_param_widths(D, trim_sh=not args.no_trim)
         n_slices = args.slices if (world > 1 and not fwd_only) else 1
-        bucket = sharding.SlicedGradBucket(P, widths, dev, n_slices, tail={"poses": (vps, 7)})
+        holder = {"bucket": sharding.SlicedGradBucket(P, widths, dev, n_slices, tail={"poses": (vps, 7)})}
+        bucket = holder["bucket"]
         o = dict(device=dev, dtype=torch.float32)
         # intermediates of the backward, allocated once: the rasterizer's gradients w.r.t. its own inputs
         g_opac, g_scales, g_shs = torch.empty(P, 1, **o), torch.empty(P, 3, **o), torch.empty(P, Kb, 3, **o)
@@ -308,6 +329,7 @@ def main():
             fviews = [(means[v], pre[v][1], scales, rots[v], S["view"], S["proj"], S["tanx"], S["tany"], S["campos"],
                        pre[v][2], accs[v], H, W, g_means[v], g_rots[v]) for v in range(vps)]
             handles = []
+            bucket = holder["bucket"]
             last = len(bucket.slices) - 1
             for c, (first, count) in enumerate(bucket.slices):
                 C.rasterize_gaussians_backward_finish_ex(fviews, shs, D, 1.0, [g_opac, g_msum, g_shs, g_scales, g_rsum],
@@ -398,6 +420,7 @@ def main():
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     launches = (C.launch_count() - launches0) if args.impl == "ours" else None
+    my_ms = elapsed_ms
     elapsed_ms = sharding.all_reduce_max(elapsed_ms, dev)
     views_total = world * vps * args.steps
     value = views_total / (elapsed_ms / 1e3)
@@ -428,6 +451,30 @@ def main():
                     "first5": [round(x, 3) for x in step_ms[:5]],
                     "all": [round(x, 3) for x in step_ms] if args.steps <= 64 else None},
     }
+    if world > 1:
+        stat = torch.tensor([my_ms / args.steps, float(sum(costs[v] for v in my_views))], dtype=torch.float64, device=dev)
+        stats = [torch.zeros_like(stat) for _ in range(world)]
+        dist.all_gather(stats, stat)
+        out["per_rank"] = {"ms_per_step": [round(float(t[0]), 4) for t in stats],
+                           "sum_num_rendered": [int(t[1]) for t in stats],
+                           "views": "dealt by cost (num_rendered)" if not args.unbalanced else "by position"}
+    if world > 1 and not fwd_only and args.impl == "ours" and args.sweep_slices:
+        for ns in [int(x) for x in args.sweep_slices.split(",") if x]:
+            holder["bucket"] = sharding.SlicedGradBucket(P, widths, dev, ns, tail={"poses": (vps, 7)})
+            for i in range(5):
+                step(i)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(args.steps):
+                step(i)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = sharding.all_reduce_max(e0.elapsed_time(e1), dev) / args.steps
+            if rank == 0:
+                sys.stderr.write(f"[sweep] slices={len(holder['bucket'].slices)} ms_per_step={ms:.4f} "
+                                 f"views/s={world * vps / (ms * 1e-3):.1f}\n")
+        holder["bucket"] = bucket
     if world > 1 and not fwd_only:
         # the collective alone, on an idle GPU: what the step has to hide
         flat = bucket.flat

@@ -22,6 +22,26 @@ def shard_views(perm: Sequence[int], step: int, rank: int, world: int, views_per
     return [perm[(base + rank * views_per_rank + j) % n] for j in range(views_per_rank)]
 
 
+def shard_views_balanced(perm: Sequence[int], costs: Sequence[float], step: int, rank: int, world: int,
+                         views_per_rank: int = 1) -> list[int]:
+    """Like shard_views, but the step's world*views_per_rank views are dealt to the ranks by cost instead of by position:
+    longest-processing-time-first onto the least loaded rank that still has a free slot. A synchronous data-parallel
+    step lasts as long as its slowest rank, and the cost of a view (its number of (Gaussian, tile) instances,
+    `num_rendered`) varies by +-10 % between the views of a scene; with 8 ranks the slowest one decides. Every rank
+    computes the same assignment from the same costs (costs[v] for view index v); ties are broken by view order."""
+    n = len(perm)
+    base = step * world * views_per_rank
+    step_views = [perm[(base + j) % n] for j in range(world * views_per_rank)]
+    order = sorted(range(len(step_views)), key=lambda j: (-float(costs[step_views[j]]), j))
+    load = [0.0] * world
+    slots = [[] for _ in range(world)]
+    for j in order:
+        r = min((q for q in range(world) if len(slots[q]) < views_per_rank), key=lambda q: (load[q], q))
+        slots[r].append(step_views[j])
+        load[r] += float(costs[step_views[j]])
+    return slots[rank]
+
+
 def shard_frames(n_frames: int, rank: int, world: int) -> list[int]:
     """Frames rendered by `rank` in the forward-only all-frames render: i % world == rank, no communication."""
     return list(range(rank, n_frames, world))
