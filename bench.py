@@ -341,7 +341,7 @@ def main():
                                        [w["xyz"], w["rotation"], w["opacity"], w["scaling"],
                                         w["features_dc"].view(count, 1, 3), rest, w["conf"].view(count),
                                         bucket.tail("poses")], fe_scratch, first, count, c == last)
-                if world > 1:
+                if world > 1 and not holder.get("no_allreduce"):
                     handles.append(bucket.all_reduce_slice(c, async_op=True))
             for h in handles:  # the step is over when its gradients are reduced: nothing is carried into the next step
                 h.wait()
@@ -460,7 +460,8 @@ def main():
                            "views": "dealt by cost (num_rendered)" if not args.unbalanced else "by position"}
     if world > 1 and not fwd_only and args.impl == "ours" and args.sweep_slices:
         for ns in [int(x) for x in args.sweep_slices.split(",") if x]:
-            holder["bucket"] = sharding.SlicedGradBucket(P, widths, dev, ns, tail={"poses": (vps, 7)})
+            holder["no_allreduce"] = ns == 0  # 0: the step without its collective (per-rank compute time, stragglers)
+            holder["bucket"] = sharding.SlicedGradBucket(P, widths, dev, max(ns, 1), tail={"poses": (vps, 7)})
             for i in range(5):
                 step(i)
             barrier()
@@ -470,10 +471,14 @@ def main():
                 step(i)
             e1.record()
             torch.cuda.synchronize()
-            ms = sharding.all_reduce_max(e0.elapsed_time(e1), dev) / args.steps
+            mine = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
+            every = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(every, mine)
+            ms = max(float(t) for t in every)
             if rank == 0:
-                sys.stderr.write(f"[sweep] slices={len(holder['bucket'].slices)} ms_per_step={ms:.4f} "
-                                 f"views/s={world * vps / (ms * 1e-3):.1f}\n")
+                sys.stderr.write(f"[sweep] slices={ns} ms_per_step={ms:.4f} views/s={world * vps / (ms * 1e-3):.1f} "
+                                 f"per_rank_ms={[round(float(t), 3) for t in every]}\n")
+        holder["no_allreduce"] = False
         holder["bucket"] = bucket
     if world > 1 and not fwd_only:
         # the collective alone, on an idle GPU: what the step has to hide
