@@ -68,6 +68,9 @@ def parse_args():
     ap.add_argument("--nccl-normal-priority", action="store_true",
                     help="NCCL's stream at normal priority (default: high, so that a slice's all-reduce is not queued "
                          "behind the blocks of the next slice's gradient kernels)")
+    ap.add_argument("--allreduce", default="auto", choices=["auto", "nccl", "nvls"],
+                    help="how the bucket is summed across ranks: this library's in-switch kernel (multimem.ld_reduce / "
+                         "multimem.st on torch symmetric memory) or NCCL; auto = nvls when the box supports multicast")
     ap.add_argument("--unbalanced", action="store_true",
                     help="shard the step's views by position in the permutation instead of by cost (num_rendered)")
     ap.add_argument("--sweep-slices", default="",
@@ -300,7 +303,27 @@ def main():
         Kb = K if not args.no_trim else 16
         widths = sharding.raw_param_widths(D, trim_sh=not args.no_trim)
         n_slices = args.slices if (world > 1 and not fwd_only) else 1
-        holder = {"bucket": sharding.SlicedGradBucket(P, widths, dev, n_slices, tail={"poses": (vps, 7)})}
+        reducer = None
+        if world > 1 and not fwd_only and args.allreduce != "nccl":
+            try:
+                reducer = sharding.NvlsReducer(dev)
+            except Exception as ex:  # symmetric memory unavailable in this build
+                if args.allreduce == "nvls":
+                    raise
+                sys.stderr.write(f"[bench] symmetric memory unavailable ({ex}); using NCCL\n")
+                reducer = None
+
+        def make_bucket(ns):
+            nonlocal reducer
+            b_ = sharding.SlicedGradBucket(P, widths, dev, ns, tail={"poses": (vps, 7)},
+                                           allocate=reducer.allocate if reducer is not None else None)
+            if reducer is not None and not reducer.available:
+                if args.allreduce == "nvls":
+                    raise RuntimeError("no NVSwitch multicast support on this box")
+                reducer = None
+            return b_
+
+        holder = {"bucket": make_bucket(n_slices)}
         bucket = holder["bucket"]
         o = dict(device=dev, dtype=torch.float32)
         # intermediates of the backward, allocated once: the rasterizer's gradients w.r.t. its own inputs
@@ -342,8 +365,14 @@ def main():
                                         w["features_dc"].view(count, 1, 3), rest, w["conf"].view(count),
                                         bucket.tail("poses")], fe_scratch, first, count, c == last)
                 if world > 1 and not holder.get("no_allreduce"):
-                    handles.append(bucket.all_reduce_slice(c, async_op=True))
-            for h in handles:  # the step is over when its gradients are reduced: nothing is carried into the next step
+                    if reducer is not None:
+                        reducer.all_reduce(*bucket.slice_bounds(c))
+                    else:
+                        handles.append(bucket.all_reduce_slice(c, async_op=True))
+            # the step is over when its gradients are reduced: nothing is carried into the next step
+            if reducer is not None:
+                reducer.wait()
+            for h in handles:
                 h.wait()
             return None
 
@@ -353,8 +382,9 @@ def main():
                     "backward into a slice-major fp32 bucket of raw-parameter gradients",
             "bucket_slices": len(bucket.slices), "bucket_bytes": bucket_bytes,
             "sh_bands_in_bucket": Kb, "streams": 1, "host_threads": 1,
-            "allreduce": "one NCCL all-reduce per bucket slice, started when the slice is complete, all waited on "
-                         "before the step ends" if world > 1 else "none (1 rank)",
+            "allreduce": ("one all-reduce per bucket slice, started when the slice is complete, all waited on before the "
+                          "step ends; " + ("das3r_nvls_allreduce_sum (multimem.ld_reduce + multimem.st on torch symmetric "
+                                           "memory)" if reducer is not None else "NCCL")) if world > 1 else "none (1 rank)",
         }
     else:
         pool = []
@@ -461,7 +491,7 @@ def main():
     if world > 1 and not fwd_only and args.impl == "ours" and args.sweep_slices:
         for ns in [int(x) for x in args.sweep_slices.split(",") if x]:
             holder["no_allreduce"] = ns == 0  # 0: the step without its collective (per-rank compute time, stragglers)
-            holder["bucket"] = sharding.SlicedGradBucket(P, widths, dev, max(ns, 1), tail={"poses": (vps, 7)})
+            holder["bucket"] = make_bucket(max(ns, 1))
             for i in range(5):
                 step(i)
             barrier()
@@ -493,9 +523,34 @@ def main():
         a1.record()
         torch.cuda.synchronize()
         ar_ms = sharding.all_reduce_max(a0.elapsed_time(a1) / 10, dev)
-        out["allreduce"] = {"bytes": bucket_bytes, "alone_ms": round(ar_ms, 4),
-                            "algbw_gbs": round(bucket_bytes / (ar_ms * 1e-3) / 1e9, 1),
-                            "kernel": "ncclDevKernel_AllReduce_Sum_f32_*"}
+        out["allreduce"] = {"bytes": bucket_bytes, "nccl_alone_ms": round(ar_ms, 4),
+                            "nccl_algbw_gbs": round(bucket_bytes / (ar_ms * 1e-3) / 1e9, 1),
+                            "nccl_kernel": "ncclDevKernel_AllReduce_Sum_f32_*"}
+        if args.impl == "ours" and reducer is not None:
+            # this library's in-switch kernel alone, and its result against NCCL's on the same data
+            g_ = torch.Generator(device=dev).manual_seed(100 + rank)
+            flat.copy_(torch.randn(flat.numel(), device=dev, generator=g_))
+            want = flat.clone()
+            dist.all_reduce(want)
+            reducer.all_reduce(0, flat.numel())
+            reducer.wait()
+            torch.cuda.synchronize()
+            err = float((flat - want).abs().max() / want.abs().max())
+            for _ in range(3):
+                reducer.all_reduce(0, flat.numel())
+            reducer.wait()
+            barrier()
+            a0.record()
+            for _ in range(10):
+                reducer.all_reduce(0, flat.numel())
+            reducer.wait()
+            a1.record()
+            torch.cuda.synchronize()
+            nv_ms = sharding.all_reduce_max(a0.elapsed_time(a1) / 10, dev)
+            out["allreduce"].update({"nvls_alone_ms": round(nv_ms, 4),
+                                     "nvls_algbw_gbs": round(bucket_bytes / (nv_ms * 1e-3) / 1e9, 1),
+                                     "nvls_kernel": "das3r::nvls_allreduce_kernel (between two symmetric-memory barriers)",
+                                     "nvls_vs_nccl_max_rel_diff": err})
     if args.impl != "ours":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": out["value"], "unit": unit, "cores": 0, "kind": "reference",

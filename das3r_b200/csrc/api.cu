@@ -5,6 +5,7 @@
 #include "../../include/das3r_frontend.h"
 #include "../../include/das3r_loss.h"
 #include "../../include/das3r_adam.h"
+#include "../../include/das3r_comm.h"
 #include <math.h>
 #include "kernels.cuh"
 #include <stdio.h>
@@ -1087,6 +1088,23 @@ int das3r_loss_backward(const das3r_loss_inputs* in, const void* state, const fl
     return DAS3R_OK;
 }
 
+
+// ---- in-switch all-reduce of a bucket slice (include/das3r_comm.h) ------------------------------------------------
+int das3r_nvls_allreduce_sum(void* multicast_base, size_t offset_floats, size_t n_floats, int32_t rank, int32_t world,
+                             int32_t n_ctas, void* stream_v) {
+    g_err.clear();
+    if (!multicast_base || world < 1 || rank < 0 || rank >= world)
+        return fail_msg(DAS3R_EINVAL, "nvls_allreduce: null multicast pointer or bad rank / world");
+    if ((offset_floats & 3) || (n_floats & 3) || (reinterpret_cast<uintptr_t>(multicast_base) & 15))
+        return fail_msg(DAS3R_EINVAL, "nvls_allreduce: base, offset and length must be multiples of 16 bytes");
+    if (n_floats == 0) return DAS3R_OK;
+    if (n_ctas <= 0) n_ctas = 24;
+    cudaError_t e = launch_nvls_allreduce(static_cast<float*>(multicast_base) + offset_floats, n_floats / 4, rank, world,
+                                          n_ctas, static_cast<cudaStream_t>(stream_v));
+    g_launches += 1;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "nvls_allreduce", e);
+    return DAS3R_OK;
+}
 
 // ---- fused Adam step (include/das3r_adam.h) -----------------------------------------------------------------------
 int das3r_adam_step(int32_t n_tensors, const das3r_adam_tensor* tensors, double beta1, double beta2, double eps,

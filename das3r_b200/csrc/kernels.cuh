@@ -216,6 +216,9 @@ cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s);
 // request so that at most ceil(grid / #SMs) blocks fit on an SM; 0 when the grid spans several waves anyway.
 size_t spread_pad_smem(const void* kernel, int grid, int block_threads, size_t static_smem);
 
+// comm.cu
+cudaError_t launch_nvls_allreduce(float* mc, size_t n_f4, int rank, int world, int n_ctas, cudaStream_t s);
+
 // knn.cu
 size_t knn_scratch_bytes(int P);
 cudaError_t knn_dist2(int P, const float* points, float* out, void* scratch, size_t scratch_bytes, cudaStream_t s);

@@ -12,6 +12,7 @@
 #include "../../include/das3r_frontend.h"
 #include "../../include/das3r_loss.h"
 #include "../../include/das3r_adam.h"
+#include "../../include/das3r_comm.h"
 
 namespace {
 
@@ -1029,6 +1030,14 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("loss_forward", &LossForwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("loss_backward", &LossBackwardCUDA, py::call_guard<py::gil_scoped_release>());
     m.def("adam_step", &AdamStepCUDA);
+    m.def("nvls_allreduce_sum", [](int64_t multicast_ptr, int64_t offset_floats, int64_t n_floats, int rank, int world,
+                                   int n_ctas, int device_index) {
+        c10::cuda::CUDAGuard guard((c10::DeviceIndex)device_index);
+        cudaStream_t stream = c10::cuda::getCurrentCUDAStream(device_index).stream();
+        check(das3r_nvls_allreduce_sum(reinterpret_cast<void*>(multicast_ptr), (size_t)offset_floats, (size_t)n_floats,
+                                       rank, world, n_ctas, stream),
+              "nvls_allreduce_sum");
+    });
     m.def("prof_enable", [](bool on) { das3r_prof_enable(on ? 1 : 0); });
     m.def("prof_collect", [](bool reset) {
         int n = das3r_prof_num_stages();

@@ -108,7 +108,7 @@ class SlicedGradBucket:
     gradients (poses, ...) and travels with the last slice. Slice boundaries are multiples of 256 rows."""
 
     def __init__(self, P: int, widths: dict[str, int], device, n_slices: int = 1, tail: dict[str, Sequence[int]] | None = None,
-                 dtype=torch.float32):
+                 dtype=torch.float32, allocate=None):
         self.P = int(P)
         self.widths = {k: int(w) for k, w in widths.items() if int(w) > 0}
         n_slices = max(1, min(int(n_slices), max(1, (self.P + 255) // 256)))
@@ -137,7 +137,14 @@ class SlicedGradBucket:
             self._tail[k] = (total, n)
             total += _pad(n)
         self._bounds[-1][1] = total  # the tail rides with the last slice
-        self.flat = torch.zeros(total, device=device, dtype=dtype)
+        # allocate(numel) -> flat fp32 tensor: lets the caller place the bucket in symmetric memory (NvlsReducer)
+        self.flat = allocate(total) if allocate is not None else torch.zeros(total, device=device, dtype=dtype)
+        assert self.flat.numel() >= total and self.flat.dtype == dtype
+
+    def slice_bounds(self, c: int) -> tuple[int, int]:
+        """(offset, length) of slice c in the flat buffer, in elements; both are multiples of 16."""
+        a, b = self._bounds[c]
+        return a, b - a
 
     def window(self, c: int, name: str) -> torch.Tensor:
         off, n = self._win[c][name]
@@ -179,3 +186,64 @@ def all_reduce_max(value: float, device) -> float:
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+class NvlsReducer:
+    """Sum of a symmetric fp32 buffer over the ranks of one NVSwitch box with this library's own kernel
+    (das3r_nvls_allreduce_sum: multimem.ld_reduce + multimem.st, include/das3r_comm.h) instead of NCCL. The buffer lives
+    in torch's symmetric memory, which also provides the multicast mapping and the cross-rank barrier; the reductions run
+    on a high-priority side stream so that a finished slice of the gradient bucket is summed while the next slice is
+    still being computed.
+
+        red = NvlsReducer(device, group)            # after init_process_group
+        bucket = SlicedGradBucket(..., allocate=red.allocate)
+        ... compute slice c on the current stream ...
+        red.all_reduce(*bucket.slice_bounds(c))      # asynchronous
+        red.wait()                                   # current stream waits for every reduction issued so far
+
+    `available` is False when the box has no multicast support (then use NCCL: SlicedGradBucket.all_reduce_slice)."""
+
+    def __init__(self, device, group=None, n_ctas: int = 0):
+        import torch.distributed._symmetric_memory as symm
+        from . import load_native
+
+        self._symm = symm
+        self._C = load_native()
+        self.device = torch.device(device)
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        self.n_ctas = int(n_ctas)
+        self.flat = None
+        self.handle = None
+        self.available = False
+        self.stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self._pending = []
+
+    def allocate(self, numel: int) -> torch.Tensor:
+        self.flat = self._symm.empty(numel, dtype=torch.float32, device=self.device)
+        self.flat.zero_()
+        self.handle = self._symm.rendezvous(self.flat, self.group)
+        self.available = bool(getattr(self.handle, "has_multicast_support", False)) and int(self.handle.multicast_ptr) != 0
+        return self.flat
+
+    def all_reduce(self, offset: int, length: int) -> None:
+        assert self.available, "no NVSwitch multicast mapping: use NCCL"
+        main = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ready)
+            self.handle.barrier(channel=0)  # every rank has finished writing its copy of the slice
+            self._C.nvls_allreduce_sum(int(self.handle.multicast_ptr), int(offset), int(length), self.rank, self.world,
+                                       self.n_ctas, self.device.index)
+            self.handle.barrier(channel=0)  # every rank's share of the sums has landed in every copy
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        self._pending.append(done)
+
+    def wait(self) -> None:
+        main = torch.cuda.current_stream(self.device)
+        for ev in self._pending:
+            main.wait_event(ev)
+        self._pending.clear()
