@@ -366,7 +366,7 @@ def main():
                                         bucket.tail("poses")], fe_scratch, first, count, c == last)
                 if world > 1 and not holder.get("no_allreduce"):
                     if reducer is not None:
-                        reducer.all_reduce(*bucket.slice_bounds(c))
+                        reducer.all_reduce(bucket.flat, *bucket.slice_bounds(c))
                     else:
                         handles.append(bucket.all_reduce_slice(c, async_op=True))
             # the step is over when its gradients are reduced: nothing is carried into the next step
@@ -532,17 +532,17 @@ def main():
             flat.copy_(torch.randn(flat.numel(), device=dev, generator=g_))
             want = flat.clone()
             dist.all_reduce(want)
-            reducer.all_reduce(0, flat.numel())
+            reducer.all_reduce(flat, 0, flat.numel())
             reducer.wait()
             torch.cuda.synchronize()
             err = float((flat - want).abs().max() / want.abs().max())
             for _ in range(3):
-                reducer.all_reduce(0, flat.numel())
+                reducer.all_reduce(flat, 0, flat.numel())
             reducer.wait()
             barrier()
             a0.record()
             for _ in range(10):
-                reducer.all_reduce(0, flat.numel())
+                reducer.all_reduce(flat, 0, flat.numel())
             reducer.wait()
             a1.record()
             torch.cuda.synchronize()

@@ -198,7 +198,7 @@ class NvlsReducer:
         red = NvlsReducer(device, group)            # after init_process_group
         bucket = SlicedGradBucket(..., allocate=red.allocate)
         ... compute slice c on the current stream ...
-        red.all_reduce(*bucket.slice_bounds(c))      # asynchronous
+        red.all_reduce(bucket.flat, *bucket.slice_bounds(c))   # asynchronous
         red.wait()                                   # current stream waits for every reduction issued so far
 
     `available` is False when the box has no multicast support (then use NCCL: SlicedGradBucket.all_reduce_slice)."""
@@ -214,30 +214,33 @@ class NvlsReducer:
         self.rank = dist.get_rank(self.group)
         self.world = dist.get_world_size(self.group)
         self.n_ctas = int(n_ctas)
-        self.flat = None
-        self.handle = None
+        self._handles = {}  # data_ptr of an allocation -> (flat tensor, symmetric-memory handle)
         self.available = False
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._pending = []
 
     def allocate(self, numel: int) -> torch.Tensor:
-        self.flat = self._symm.empty(numel, dtype=torch.float32, device=self.device)
-        self.flat.zero_()
-        self.handle = self._symm.rendezvous(self.flat, self.group)
-        self.available = bool(getattr(self.handle, "has_multicast_support", False)) and int(self.handle.multicast_ptr) != 0
-        return self.flat
+        flat = self._symm.empty(numel, dtype=torch.float32, device=self.device)
+        flat.zero_()
+        handle = self._symm.rendezvous(flat, self.group)
+        self.available = int(handle.multicast_ptr) != 0
+        self._handles[flat.data_ptr()] = (flat, handle)
+        return flat
 
-    def all_reduce(self, offset: int, length: int) -> None:
+    def all_reduce(self, flat: torch.Tensor, offset: int, length: int) -> None:
+        """Sum flat[offset:offset+length] (a buffer from `allocate`, offset and length multiples of 4) over the ranks,
+        asynchronously on the reducer's stream, ordered after everything queued on the current stream so far."""
         assert self.available, "no NVSwitch multicast mapping: use NCCL"
+        handle = self._handles[flat.data_ptr()][1]
         main = torch.cuda.current_stream(self.device)
         ready = torch.cuda.Event()
         ready.record(main)
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ready)
-            self.handle.barrier(channel=0)  # every rank has finished writing its copy of the slice
-            self._C.nvls_allreduce_sum(int(self.handle.multicast_ptr), int(offset), int(length), self.rank, self.world,
-                                       self.n_ctas, self.device.index)
-            self.handle.barrier(channel=0)  # every rank's share of the sums has landed in every copy
+            handle.barrier(channel=0)  # every rank has finished writing its copy of the slice
+            self._C.nvls_allreduce_sum(int(handle.multicast_ptr) + int(handle.offset), int(offset), int(length), self.rank,
+                                       self.world, self.n_ctas, self.device.index)
+            handle.barrier(channel=0)  # every rank's share of the sums has landed in every copy
             done = torch.cuda.Event()
             done.record(self.stream)
         self._pending.append(done)
