@@ -304,7 +304,9 @@ def main():
         widths = sharding.raw_param_widths(D, trim_sh=not args.no_trim)
         n_slices = args.slices if (world > 1 and not fwd_only) else 1
         reducer = None
-        if world > 1 and not fwd_only and args.allreduce != "nccl":
+        # auto: the in-switch kernel from 4 ranks on (measured on B200 HGX, 240 MB: 0.55 ms vs NCCL 0.65 ms at 8 ranks, and
+        # it needs 16 CTAs; with 2 ranks a multicast reduction moves more bytes per link than NCCL's ring: 0.61 vs 0.48 ms)
+        if world > 1 and not fwd_only and (args.allreduce == "nvls" or (args.allreduce == "auto" and world >= 4)):
             try:
                 reducer = sharding.NvlsReducer(dev)
             except Exception as ex:  # symmetric memory unavailable in this build

@@ -1098,7 +1098,7 @@ int das3r_nvls_allreduce_sum(void* multicast_base, size_t offset_floats, size_t 
     if ((offset_floats & 3) || (n_floats & 3) || (reinterpret_cast<uintptr_t>(multicast_base) & 15))
         return fail_msg(DAS3R_EINVAL, "nvls_allreduce: base, offset and length must be multiples of 16 bytes");
     if (n_floats == 0) return DAS3R_OK;
-    if (n_ctas <= 0) n_ctas = 64;
+    if (n_ctas <= 0) n_ctas = 16;  // link-bound from 16 CTAs on (B200 HGX, 8 ranks); leaves the SMs to the gradient kernels
     cudaError_t e = launch_nvls_allreduce(static_cast<float*>(multicast_base) + offset_floats, n_floats / 4, rank, world,
                                           n_ctas, static_cast<cudaStream_t>(stream_v));
     g_launches += 1;
