@@ -503,6 +503,19 @@ def main():
                 step(i)
             e1.record()
             torch.cuda.synchronize()
+            if reducer is not None and not holder["no_allreduce"]:  # timeline of one more step
+                t0 = torch.cuda.Event(enable_timing=True)
+                t1 = torch.cuda.Event(enable_timing=True)
+                reducer.trace = []
+                t0.record()
+                step(0)
+                t1.record()
+                torch.cuda.synchronize()
+                tl = [(round(t0.elapsed_time(a), 3), round(t0.elapsed_time(b), 3)) for a, b in reducer.trace]
+                reducer.trace = None
+                if rank == 0:
+                    sys.stderr.write(f"[sweep] slices={ns} timeline ms from step start (slice ready, reduced): {tl} "
+                                     f"step end {t0.elapsed_time(t1):.3f}\n")
             mine = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
             every = [torch.zeros_like(mine) for _ in range(world)]
             dist.all_gather(every, mine)

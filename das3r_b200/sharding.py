@@ -218,6 +218,7 @@ class NvlsReducer:
         self.available = False
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._pending = []
+        self.trace = None  # developer aid: a list collects (slice ready on the main stream, reduction done) event pairs
 
     def allocate(self, numel: int) -> torch.Tensor:
         flat = self._symm.empty(numel, dtype=torch.float32, device=self.device)
@@ -241,8 +242,12 @@ class NvlsReducer:
             self._C.nvls_allreduce_sum(int(handle.multicast_ptr) + int(handle.offset), int(offset), int(length), self.rank,
                                        self.world, self.n_ctas, self.device.index)
             handle.barrier(channel=0)  # every rank's share of the sums has landed in every copy
-            done = torch.cuda.Event()
+            done = torch.cuda.Event(enable_timing=self.trace is not None)
             done.record(self.stream)
+        if self.trace is not None:
+            ready_t = torch.cuda.Event(enable_timing=True)
+            ready_t.record(main)
+            self.trace.append((ready_t, done))
         self._pending.append(done)
 
     def wait(self) -> None:
