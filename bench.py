@@ -71,6 +71,7 @@ def parse_args():
     ap.add_argument("--allreduce", default="auto", choices=["auto", "nccl", "nvls"],
                     help="how the bucket is summed across ranks: this library's in-switch kernel (multimem.ld_reduce / "
                          "multimem.st on torch symmetric memory) or NCCL; auto = nvls when the box supports multicast")
+    ap.add_argument("--nvls-ctas", type=int, default=0, help="thread blocks of the in-switch all-reduce kernel (0: default)")
     ap.add_argument("--unbalanced", action="store_true",
                     help="shard the step's views by position in the permutation instead of by cost (num_rendered)")
     ap.add_argument("--sweep-slices", default="",
@@ -308,7 +309,7 @@ def main():
         # it needs 16 CTAs; with 2 ranks a multicast reduction moves more bytes per link than NCCL's ring: 0.61 vs 0.48 ms)
         if world > 1 and not fwd_only and (args.allreduce == "nvls" or (args.allreduce == "auto" and world >= 4)):
             try:
-                reducer = sharding.NvlsReducer(dev)
+                reducer = sharding.NvlsReducer(dev, n_ctas=args.nvls_ctas)
             except Exception as ex:  # symmetric memory unavailable in this build
                 if args.allreduce == "nvls":
                     raise

@@ -43,6 +43,18 @@ def timeit(fn, it=10):
 for ctas in (16, 32, 48, 64, 96, 148):
     t = timeit(lambda: ours(ctas))
     if rank == 0: print("ours ctas", ctas, round(t, 4), "ms", round(n * 4 / t / 1e6, 1), "GB/s")
+t = timeit(lambda: (h.barrier(channel=0), h.barrier(channel=0)))
+if rank == 0: print("two barriers alone", round(t, 4), "ms")
+for frac in (2, 4, 8):
+    m = (n // frac) // 16 * 16
+    def part():
+        h.barrier(channel=0); C.nvls_allreduce_sum(mc, 0, m, rank, world, 16, lr); h.barrier(channel=0)
+    t = timeit(part)
+    if rank == 0: print(f"ours 1/{frac} of the buffer, 16 ctas", round(t, 4), "ms")
+    def part32():
+        h.barrier(channel=0); C.nvls_allreduce_sum(mc, 0, m, rank, world, 48, lr); h.barrier(channel=0)
+    t = timeit(part32)
+    if rank == 0: print(f"ours 1/{frac} of the buffer, 48 ctas", round(t, 4), "ms")
 t = timeit(lambda: torch.ops.symm_mem.multimem_all_reduce_(flat, "sum", dist.group.WORLD.group_name))
 if rank == 0: print("torch multimem_all_reduce_", round(t, 4), "ms", round(n * 4 / t / 1e6, 1), "GB/s")
 t = timeit(lambda: torch.ops.symm_mem.two_shot_all_reduce_(flat, "sum", dist.group.WORLD.group_name))
