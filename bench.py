@@ -63,15 +63,16 @@ def parse_args():
     ap.add_argument("--H", type=int, default=None)
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--seed", type=int, default=None)
-    ap.add_argument("--slices", type=int, default=4,
-                    help="gradient bucket slices: slice c is all-reduced while slice c+1 is computed (N > 1)")
+    ap.add_argument("--slices", type=int, default=0,
+                    help="gradient bucket slices: slice c is all-reduced while slice c+1 is computed (N > 1); 0 = the "
+                         "measured best: 4 with NCCL (2 and 4 ranks), 2 with the in-switch kernel (8 ranks)")
     ap.add_argument("--nccl-normal-priority", action="store_true",
                     help="NCCL's stream at normal priority (default: high, so that a slice's all-reduce is not queued "
                          "behind the blocks of the next slice's gradient kernels)")
     ap.add_argument("--allreduce", default="auto", choices=["auto", "nccl", "nvls"],
                     help="how the bucket is summed across ranks: this library's in-switch kernel (multimem.ld_reduce / "
                          "multimem.st on torch symmetric memory) or NCCL; auto = nvls when the box supports multicast")
-    ap.add_argument("--nvls-ctas", type=int, default=0, help="thread blocks of the in-switch all-reduce kernel (0: default)")
+    ap.add_argument("--nvls-ctas", type=int, default=32, help="thread blocks of the in-switch all-reduce kernel")
     ap.add_argument("--unbalanced", action="store_true",
                     help="shard the step's views by position in the permutation instead of by cost (num_rendered)")
     ap.add_argument("--sweep-slices", default="",
@@ -303,11 +304,13 @@ def main():
         fi = torch.empty(0, dtype=torch.int64)
         Kb = K if not args.no_trim else 16
         widths = sharding.raw_param_widths(D, trim_sh=not args.no_trim)
-        n_slices = args.slices if (world > 1 and not fwd_only) else 1
+        want_nvls = args.allreduce == "nvls" or (args.allreduce == "auto" and world >= 8)
+        n_slices = (args.slices if args.slices > 0 else (2 if want_nvls else 4)) if (world > 1 and not fwd_only) else 1
         reducer = None
-        # auto: the in-switch kernel from 4 ranks on (measured on B200 HGX, 240 MB: 0.55 ms vs NCCL 0.65 ms at 8 ranks, and
-        # it needs 16 CTAs; with 2 ranks a multicast reduction moves more bytes per link than NCCL's ring: 0.61 vs 0.48 ms)
-        if world > 1 and not fwd_only and (args.allreduce == "nvls" or (args.allreduce == "auto" and world >= 4)):
+        # auto: the in-switch kernel from 8 ranks on (measured on B200 HGX, 240 MB alone: 0.55 ms vs NCCL 0.65 ms at 8
+        # ranks; 0.57 vs 0.62 at 4, where the step as a whole is faster with NCCL; with 2 ranks a multicast reduction moves
+        # more bytes per link than NCCL's ring: 0.61 vs 0.48 ms)
+        if world > 1 and not fwd_only and (args.allreduce == "nvls" or (args.allreduce == "auto" and world >= 8)):
             try:
                 reducer = sharding.NvlsReducer(dev, n_ctas=args.nvls_ctas)
             except Exception as ex:  # symmetric memory unavailable in this build
