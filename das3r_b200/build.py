@@ -24,10 +24,10 @@ BUILD_DIR = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libdas3r_raster.so")
 EXT = os.path.join(HERE, "_C" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
 
-CU_SOURCES = ["forward.cu", "backward.cu", "knn.cu", "frontend.cu", "loss.cu", "adam.cu", "comm.cu", "api.cu"]
+CU_SOURCES = ["forward.cu", "backward.cu", "knn.cu", "frontend.cu", "loss.cu", "adam.cu", "comm.cu", "init.cu", "api.cu"]
 HEADERS = ["common.cuh", "kernels.cuh", os.path.join(ROOT, "include", "das3r_raster.h"), "blend_common.cuh",
            os.path.join(ROOT, "include", "das3r_frontend.h"), os.path.join(ROOT, "include", "das3r_loss.h"), os.path.join(ROOT, "include", "das3r_adam.h"),
-           os.path.join(ROOT, "include", "das3r_comm.h")]
+           os.path.join(ROOT, "include", "das3r_comm.h"), os.path.join(ROOT, "include", "das3r_init.h")]
 
 
 def _mtime(p: str) -> float:

@@ -6,6 +6,7 @@
 #include "../../include/das3r_loss.h"
 #include "../../include/das3r_adam.h"
 #include "../../include/das3r_comm.h"
+#include "../../include/das3r_init.h"
 #include <math.h>
 #include "kernels.cuh"
 #include <stdio.h>
@@ -1088,6 +1089,79 @@ int das3r_loss_backward(const das3r_loss_inputs* in, const void* state, const fl
     return DAS3R_OK;
 }
 
+
+// ---- pointmap initialisation (include/das3r_init.h) ---------------------------------------------------------------
+static bool pointmaps_ok(const das3r_pointmaps* in) {
+    return in && in->V > 0 && in->H > 0 && in->W > 0 && in->K && in->poses && in->depth && in->confidence &&
+           in->dyna_avg && in->rgb;
+}
+
+size_t das3r_pointmap_scratch_bytes(int64_t n_pixels) { return pointmap_scratch_bytes(n_pixels > 0 ? n_pixels : 0); }
+
+int64_t das3r_pointmap_select(const das3r_pointmaps* in, uint8_t* aggregated_mask, float* conf_static, void* scratch,
+                              size_t scratch_bytes, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!pointmaps_ok(in) || !aggregated_mask || !conf_static || !scratch)
+        return fail_msg(DAS3R_EINVAL, "pointmap_select: null or invalid argument");
+    const int64_t n = (int64_t)in->V * in->H * in->W;
+    if (scratch_bytes < pointmap_scratch_bytes(n)) return fail_msg(DAS3R_EINVAL, "pointmap_select: scratch too small");
+    cudaError_t e = launch_pointmap_select(in->confidence, in->dyna_avg, in->log_conf_thre, n, aggregated_mask, conf_static,
+                                           scratch, stream);
+    g_launches += 2;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_select", e);
+    unsigned long long total = 0;
+    e = cudaMemcpyAsync(&total, scratch, sizeof(total), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_select read-back", e);
+    if (total > 0x7fffffffull) return fail_msg(DAS3R_ELIMIT, "pointmap_select: more than 2^31-1 selected pixels");
+    return (int64_t)total;
+}
+
+int das3r_pointmap_init(const das3r_pointmaps* in, const uint8_t* aggregated_mask, int64_t P, const das3r_init_outputs* out,
+                        void* scratch, size_t scratch_bytes, void* knn_scratch, size_t knn_bytes, void* stream_v) {
+    g_err.clear();
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (!pointmaps_ok(in) || !aggregated_mask || !out || !scratch || P < 0 || P > 0x7fffffffLL)
+        return fail_msg(DAS3R_EINVAL, "pointmap_init: null or invalid argument");
+    if (P == 0) return DAS3R_OK;
+    if (!out->xyz || !out->features_dc || !out->scaling || !out->rotation || !out->opacity ||
+        (reinterpret_cast<uintptr_t>(out->rotation) & 15))
+        return fail_msg(DAS3R_EINVAL, "pointmap_init: null output (or rotation not 16-byte aligned)");
+    const int64_t n = (int64_t)in->V * in->H * in->W;
+    if (scratch_bytes < pointmap_scratch_bytes(n)) return fail_msg(DAS3R_EINVAL, "pointmap_init: scratch too small");
+    if (!knn_scratch || knn_bytes < knn_scratch_bytes((int)P))
+        return fail_msg(DAS3R_EINVAL, "pointmap_init: knn scratch too small (das3r_knn_scratch_bytes(P))");
+    // inverse_sigmoid(1/V) as torch forms it in fp32: log(x / (1 - x)) with x = (float)(1/V)  (gaussian_model.py:646-647)
+    const float x = (float)(1.0 / (double)in->V);
+    const float opacity_raw = logf(x / (1.0f - x));
+    cudaError_t e = cudaSuccess;
+    if (out->features_rest) {  // features[:, 3:, 1:] = 0 (gaussian_model.py:637)
+        e = cudaMemsetAsync(out->features_rest, 0, (size_t)P * 45 * sizeof(float), stream);
+        if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_init memset", e);
+    }
+    e = launch_pointmap_emit(in->V, in->H, in->W, in->K, in->poses, in->depth, in->rgb, aggregated_mask,
+                                         scratch, out->xyz, out->features_dc, out->features_rest, out->rotation,
+                                         out->opacity, out->conf_index, opacity_raw, stream);
+    g_launches += 1;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_emit", e);
+    // the 3-NN distances go through out->dist2 when given, else through the scaling buffer's first P floats
+    float* d2 = out->dist2 ? out->dist2 : out->scaling;
+    g_launches += 7;
+    e = knn_dist2((int)P, out->xyz, d2, knn_scratch, knn_bytes, stream);
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_init knn", e);
+    if (!out->dist2) {
+        // in place: scaling[3i..3i+2] are written from dist2 = scaling[i]; walk from the back would be needed - use the
+        // knn scratch's head (free again after the search) as the staging copy instead
+        e = cudaMemcpyAsync(knn_scratch, d2, (size_t)P * sizeof(float), cudaMemcpyDeviceToDevice, stream);
+        if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_init copy", e);
+        d2 = static_cast<float*>(knn_scratch);
+    }
+    e = launch_pointmap_scales(P, d2, out->scaling, stream);
+    g_launches += 1;
+    if (e != cudaSuccess) return fail(DAS3R_ECUDA, "pointmap_scales", e);
+    return DAS3R_OK;
+}
 
 // ---- in-switch all-reduce of a bucket slice (include/das3r_comm.h) ------------------------------------------------
 int das3r_nvls_allreduce_sum(void* multicast_base, size_t offset_floats, size_t n_floats, int32_t rank, int32_t world,

@@ -216,6 +216,16 @@ cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s);
 // request so that at most ceil(grid / #SMs) blocks fit on an SM; 0 when the grid spans several waves anyway.
 size_t spread_pad_smem(const void* kernel, int grid, int block_threads, size_t static_smem);
 
+// init.cu (include/das3r_init.h)
+size_t pointmap_scratch_bytes(int64_t n_pixels);
+cudaError_t launch_pointmap_select(const float* conf, const float* dyna, float log_thre, int64_t n, uint8_t* mask,
+                                   float* conf_static, void* scratch, cudaStream_t s);
+cudaError_t launch_pointmap_emit(int V, int H, int W, const float* K, const float* poses, const float* depth,
+                                 const float* rgb, const uint8_t* mask, void* scratch, float* xyz, float* features_dc,
+                                 float* features_rest, float* rotation, float* opacity, int64_t* conf_index,
+                                 float opacity_raw, cudaStream_t s);
+cudaError_t launch_pointmap_scales(int64_t P, const float* dist2, float* scaling, cudaStream_t s);
+
 // comm.cu
 cudaError_t launch_nvls_allreduce(float* mc, size_t n_f4, int rank, int world, int n_ctas, cudaStream_t s);
 

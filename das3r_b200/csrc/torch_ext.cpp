@@ -13,6 +13,7 @@
 #include "../../include/das3r_loss.h"
 #include "../../include/das3r_adam.h"
 #include "../../include/das3r_comm.h"
+#include "../../include/das3r_init.h"
 
 namespace {
 
@@ -1009,7 +1010,63 @@ static void AdamStepCUDA(const std::vector<torch::Tensor>& params, const std::ve
     }
 }
 
+// ---- pointmap initialisation (include/das3r_init.h) ---------------------------------------------------------------
+// K [V,3,3], poses [V,4,4] (camera-to-world), depth / confidence / dyna_avg [V,H,W], rgb [V,3,H,W], log_conf_thre
+// -> (xyz, features_dc, features_rest, scaling, rotation, opacity, conf_static [V,H,W], aggregated_mask [V*H*W] bool,
+//     conf_index [P] int64, dist2 [P])
+static std::vector<torch::Tensor> PointmapInitCUDA(const torch::Tensor& K_, const torch::Tensor& poses_,
+                                                   const torch::Tensor& depth_, const torch::Tensor& conf_,
+                                                   const torch::Tensor& dyna_, const torch::Tensor& rgb_,
+                                                   const double log_conf_thre) {
+    TORCH_CHECK(depth_.is_cuda(), "depth must be a CUDA tensor: the initialisation has no CPU path");
+    const auto dev = depth_.device();
+    c10::cuda::CUDAGuard guard(dev);
+    TORCH_CHECK(depth_.dim() == 3, "depth must be [V,H,W]");
+    const int64_t V = depth_.size(0), H = depth_.size(1), W = depth_.size(2);
+    auto K = prep(K_, "K", dev), poses = prep(poses_, "poses", dev), depth = prep(depth_, "depth", dev);
+    auto conf = prep(conf_, "confidence", dev), dyna = prep(dyna_, "dyna_avg", dev), rgb = prep(rgb_, "rgb", dev);
+    TORCH_CHECK(K.numel() == 9 * V && poses.numel() == 16 * V && conf.numel() == V * H * W && dyna.numel() == V * H * W &&
+                    rgb.numel() == 3 * V * H * W,
+                "K [V,3,3], poses [V,4,4], confidence / dyna_avg [V,H,W], rgb [V,3,H,W]");
+    das3r_pointmaps in;
+    memset(&in, 0, sizeof(in));
+    in.V = (int32_t)V; in.H = (int32_t)H; in.W = (int32_t)W;
+    in.K = fptr(K); in.poses = fptr(poses); in.depth = fptr(depth); in.confidence = fptr(conf); in.dyna_avg = fptr(dyna);
+    in.rgb = fptr(rgb);
+    in.log_conf_thre = (float)log_conf_thre;
+    const int64_t n = V * H * W;
+    auto bo = torch::TensorOptions().dtype(torch::kByte).device(dev);
+    auto fo = depth.options();
+    auto mask = torch::empty({n}, torch::TensorOptions().dtype(torch::kBool).device(dev));
+    auto conf_static = torch::empty({V, H, W}, fo);
+    const size_t sbytes = das3r_pointmap_scratch_bytes(n);
+    auto scratch = torch::empty({(long long)sbytes}, bo);
+    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+    const int64_t P = das3r_pointmap_select(&in, reinterpret_cast<uint8_t*>(mask.data_ptr<bool>()),
+                                            conf_static.data_ptr<float>(), scratch.data_ptr(), sbytes, stream);
+    if (P < 0) throw std::runtime_error(std::string("pointmap_select: ") + das3r_last_error());
+    auto xyz = torch::empty({P, 3}, fo), fdc = torch::empty({P, 1, 3}, fo), frest = torch::empty({P, 15, 3}, fo);
+    auto scaling = torch::empty({P, 3}, fo), rotation = torch::empty({P, 4}, fo), opacity = torch::empty({P, 1}, fo);
+    auto conf_index = torch::empty({P}, torch::TensorOptions().dtype(torch::kInt64).device(dev));
+    auto dist2 = torch::empty({P}, fo);
+    if (P > 0) {
+        const size_t kbytes = das3r_knn_scratch_bytes((int32_t)P);
+        auto kscratch = torch::empty({(long long)kbytes}, bo);
+        das3r_init_outputs out;
+        memset(&out, 0, sizeof(out));
+        out.xyz = xyz.data_ptr<float>(); out.features_dc = fdc.data_ptr<float>(); out.features_rest = frest.data_ptr<float>();
+        out.scaling = scaling.data_ptr<float>(); out.rotation = rotation.data_ptr<float>();
+        out.opacity = opacity.data_ptr<float>(); out.conf_index = conf_index.data_ptr<int64_t>();
+        out.dist2 = dist2.data_ptr<float>();
+        check(das3r_pointmap_init(&in, reinterpret_cast<const uint8_t*>(mask.data_ptr<bool>()), P, &out, scratch.data_ptr(),
+                                  sbytes, kscratch.data_ptr(), kbytes, stream),
+              "pointmap_init");
+    }
+    return {xyz, fdc, frest, scaling, rotation, opacity, conf_static, mask, conf_index, dist2};
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    m.def("pointmap_init", &PointmapInitCUDA, py::call_guard<py::gil_scoped_release>());
     // The GIL is released around every call into the library: a host that drives several CUDA streams from several
     // threads (bench.py) must not serialise on the forward's read-back of num_rendered.
     m.def("rasterize_gaussians", &RasterizeGaussiansCUDA, py::call_guard<py::gil_scoped_release>());
