@@ -397,7 +397,7 @@ static int forward_finish(int n, const das3r_raster_fwd_view* const* views, int*
     if (R_total > 0) {
         STAGE(launch_scatter(b, stream), "scatter", ST_SCATTER, 1);
         STAGE(launch_tile_sort(b, max_count, R, view_max, temp, temp_bytes, stream), "tile_sort", ST_TILE_SORT,
-              2 + (max_count > 4096 ? 1 : 0) + (max_count > 8192 ? 1 : 0) + (any_fallback ? 3 : 0));
+              1 + (max_count > 4096 ? 1 : 0) + (max_count > 8192 ? 1 : 0) + (any_fallback ? 3 : 0));
         STAGE(launch_rect_lists(b, stream), "rect_lists", ST_RECT_LISTS, 1);
     }
     STAGE(launch_blend_fwd(b, stream), "blend_fwd", ST_BLEND_FWD, 1);

@@ -10,6 +10,7 @@
 #include "kernels.cuh"
 #include "blend_common.cuh"
 #include <stdlib.h>
+#include <algorithm>
 
 namespace das3r {
 
@@ -563,13 +564,17 @@ __global__ void __launch_bounds__(PB_THREADS, 3) preprocess_bwd_kernel(const Pre
 constexpr int MV_THREADS = 128;
 constexpr int MV_OUT_PITCH = MV_THREADS + 1;  // [coefficient][thread] accumulators, odd pitch: conflict-free both ways
 
+#ifndef DAS3R_MV_MIN_BLOCKS
+#define DAS3R_MV_MIN_BLOCKS 4
+#endif
 template <int DEG>
-__global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(const __grid_constant__ MultiBwdArgs a) {
+__global__ void __launch_bounds__(MV_THREADS, DAS3R_MV_MIN_BLOCKS) preprocess_bwd_multi_kernel(const __grid_constant__ MultiBwdArgs a) {
     constexpr int NW = 3 * (DEG + 1) * (DEG + 1);  // active floats of an SH row
     constexpr bool STAGE = DEG == 3;
     extern __shared__ __align__(16) unsigned char mv_smem[];
+    // the staged input rows are consumed into registers before the accumulators are first touched: one buffer serves both
     float4* in_rows = reinterpret_cast<float4*>(mv_smem);  // [MV_THREADS][13] (STAGE only)
-    float* out_acc = reinterpret_cast<float*>(mv_smem + (STAGE ? (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 : 0));  // [NW][pitch]
+    float* out_acc = reinterpret_cast<float*>(mv_smem);    // [NW][pitch]
     __shared__ uint8_t row_vis[MV_THREADS];
     const int tid = threadIdx.x;
     const int base = blockIdx.x * MV_THREADS;
@@ -591,8 +596,6 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
         }
         cp_async_commit();
     }
-#pragma unroll
-    for (int k = 0; k < NW; k++) out_acc[k * MV_OUT_PITCH + tid] = 0.f;
 
     float3 s_mean = {0.f, 0.f, 0.f}, s_scale = {0.f, 0.f, 0.f};
     float4 s_rot = {0.f, 0.f, 0.f, 0.f};
@@ -609,9 +612,12 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
             const float4 v = myrow[j];
             f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w;
         }
+        __syncthreads();  // every row has been read: the buffer becomes the accumulator array
     } else if (in_range) {
         load_sh_row(a.shs + (size_t)idx * 48, DEG, true, f);
     }
+#pragma unroll
+    for (int k = 0; k < NW; k++) out_acc[k * MV_OUT_PITCH + tid] = 0.f;
 
 #pragma unroll 1
     for (int v = 0; v < a.n_views; v++) {
@@ -727,7 +733,7 @@ __global__ void __launch_bounds__(MV_THREADS, 4) preprocess_bwd_multi_kernel(con
 cudaError_t launch_preprocess_bwd_multi(const MultiBwdArgs& a, cudaStream_t s) {
     const int blocks = (a.P + MV_THREADS - 1) / MV_THREADS;
     const int nw = 3 * (a.D + 1) * (a.D + 1);
-    const size_t smem = (a.D == 3 ? (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 : 0) + (size_t)nw * MV_OUT_PITCH * sizeof(float);
+    const size_t smem = std::max((a.D == 3 ? (size_t)MV_THREADS * PB_ROW_PAD_F4 * 16 : 0), (size_t)nw * MV_OUT_PITCH * sizeof(float));
     const void* fn = a.D == 0   ? (const void*)preprocess_bwd_multi_kernel<0>
                      : a.D == 1 ? (const void*)preprocess_bwd_multi_kernel<1>
                      : a.D == 2 ? (const void*)preprocess_bwd_multi_kernel<2>

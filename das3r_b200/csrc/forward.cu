@@ -7,9 +7,9 @@
 //                      duplicateWithKeys, rasterizer_impl.cu:70-111)
 //   tile_sort       -> per-tile most-significant-digit bucket sort in shared memory, three size classes, bitonic
 //                      network for skewed depths, library segmented sort only for tiles above 16384 entries (replaces
-//                      the global 64-bit cub::DeviceRadixSort, rasterizer_impl.cu:303-308) + gather_records: the
-//                      tile-ordered record streams
-//   rect_lists      -> per 8x4-pixel rectangle the list of {tile-list position, pixel mask} of the Gaussians that can
+//                      the global 64-bit cub::DeviceRadixSort, rasterizer_impl.cu:303-308)
+//   rect_lists      -> gathers the tile-ordered record streams through the sorted point list and builds, per 8x4-pixel
+//                      rectangle, the list of {tile-list position, pixel mask} of the Gaussians that can
 //                      reach alpha >= 1/255 there (no reference counterpart: there every thread of the tile looks at
 //                      every Gaussian of the tile)
 //   blend_fwd       -> front-to-back alpha blend, one warp per rectangle walking its list (replaces renderCUDA,
@@ -818,19 +818,6 @@ __global__ void __launch_bounds__(SORT_THREADS, (MAXE <= 8 ? 2 : 1))
     }
 }
 
-// gather_records: entry i of the sorted list -> sA[i] = {x, y, h, -tau'}, sBC[i] = {conic, opacity}, {rgb, index}.
-// grid.y = view; the view's entry count is read from its totals (the grid is sized for the largest view).
-__global__ void __launch_bounds__(256) gather_records_kernel(const __grid_constant__ BatchArgs b) {
-    const ViewBin& V = b.v[blockIdx.y];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if ((uint32_t)i >= V.totals[0]) return;
-    const uint32_t g = V.point_list[i];
-    const GaussRec r = V.rec[g];
-    V.sA[i] = r.A;
-    V.sBC[2 * (size_t)i] = r.B;
-    V.sBC[2 * (size_t)i + 1] = make_float4(r.C.x, r.C.y, r.C.z, __uint_as_float(g));
-}
-
 int tile_sort_capacity() { return SORT_THREADS * SORT_MAX_E; }
 
 template <int MAXE, int MIN_N, int LOG_NB>
@@ -925,10 +912,7 @@ cudaError_t launch_tile_sort(const BatchArgs& b, uint32_t max_count, const int* 
         }
     if (fork) cudaEventDestroy(fork);
     if (e != cudaSuccess) return e;
-    int Rmax = 0;
-    for (int v = 0; v < b.n; v++) Rmax = R[v] > Rmax ? R[v] : Rmax;
-    if (Rmax > 0) gather_records_kernel<<<dim3((Rmax + 255) / 256, b.n), 256, 0, s>>>(b);
-    return cudaGetLastError();
+    return cudaGetLastError();  // the tile-ordered record streams are written by rect_lists_kernel
 }
 
 // Tiles beyond the shared-memory capacity: library segmented radix sort of their (depth|index) entries (segment =
@@ -1047,12 +1031,23 @@ static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint6
 #ifndef DAS3R_RECT_MIN_BLOCKS
 #define DAS3R_RECT_MIN_BLOCKS 4
 #endif
+constexpr int RECT_CHUNK = 1024;  // tile-list entries staged in shared memory at a time (4 per thread)
+
+// The block first GATHERS a chunk of the tile's records through the sorted point list (48-byte reads scattered over the
+// per-Gaussian array) into the tile-ordered streams the blends read (sA / sBC, coalesced writes) and, on the way, into
+// shared memory; its eight warps then scan the chunk from shared memory. The gather is pure memory latency, the scan
+// pure arithmetic: inside one kernel the two overlap across the blocks of an SM (a separate gather kernel ran at 5 %
+// issue utilisation and took as long as the sort), and the lists never re-read the streams from L2.
 __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(const __grid_constant__ BatchArgs b) {
-    __shared__ uint32_t cand_s[8][256];  // per warp: circular buffer of tile-list positions that reach the rectangle
+    __shared__ uint32_t cand_s[8][256];  // per warp: circular buffer of chunk positions that reach the rectangle
+    __shared__ float4 sA_s[RECT_CHUNK];  // {x, y, h, -tau'} of the chunk's entries
+    __shared__ float4 sB_s[RECT_CHUNK];  // {conic, opacity}
     const ViewBin& V = b.v[blockIdx.y];
     const uint2* __restrict__ ranges = V.ranges;
-    const float4* __restrict__ sA = V.sA;
-    const float4* __restrict__ sBC = V.sBC;
+    const uint32_t* __restrict__ point_list = V.point_list;
+    const GaussRec* __restrict__ rec = V.rec;
+    float4* __restrict__ sA = V.sA;
+    float4* __restrict__ sBC = V.sBC;
     uint32_t* __restrict__ rect_off = V.rect_off;
     uint32_t* __restrict__ rect_cnt = V.rect_cnt;
     uint2* __restrict__ rect_list = V.rect_list;
@@ -1062,8 +1057,9 @@ __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
     const int tx = tile % gx, ty = tile / gx;
-    const float4* gA = sA + range.x;
-    const float4* gBC = sBC + 2 * (size_t)range.x;
+    float4* gA = sA + range.x;
+    float4* gBC = sBC + 2 * (size_t)range.x;
+    const uint32_t* gL = point_list + range.x;
     uint32_t* cand = cand_s[w];
     const uint32_t off = 8u * range.x + (uint32_t)w * (uint32_t)n;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -1075,13 +1071,15 @@ __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(
             if (rx0 + j < W && ry0 + r < H) pix_valid |= 1u << (r * 8 + j);
 
     uint32_t head = 0, tail = 0, run = 0;
-    // Pixel masks of `k` (<= 32) buffered candidates, one per lane; entries with a non-empty mask are appended.
+    int chunk0 = 0;
+    // Pixel masks of `k` (<= 32) buffered candidates of the current chunk, one per lane; entries with a non-empty mask
+    // are appended to the rectangle's list with their position in the tile list.
     auto emit = [&](int k) {
         uint32_t pos = 0, mask = 0;
         if (lane < k) {
             pos = cand[(head + lane) & 255u];
-            const float4 A = gA[pos];
-            const float4 con_o = gBC[2 * (size_t)pos];
+            const float4 A = sA_s[pos];
+            const float4 con_o = sB_s[pos];
             // splat_power() for the 32 pixels with the column / row factors hoisted (same operations, same rounding)
             float dx[8], ax[8], bx[8];
 #pragma unroll
@@ -1104,31 +1102,71 @@ __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(
             }
             mask &= pix_valid;
         }
-        const unsigned b = __ballot_sync(0xffffffffu, mask != 0u);
-        if (mask) rect_list[off + run + __popc(b & lt_mask)] = make_uint2(pos, mask);
-        run += __popc(b);
+        const unsigned bal = __ballot_sync(0xffffffffu, mask != 0u);
+        if (mask) rect_list[off + run + __popc(bal & lt_mask)] = make_uint2((uint32_t)chunk0 + pos, mask);
+        run += __popc(bal);
         head += (uint32_t)k;
     };
 
-    for (int c0 = 0; c0 < n; c0 += 128) {
-        float4 a[4];
+    for (chunk0 = 0; chunk0 < n; chunk0 += RECT_CHUNK) {
+        const int cn = min(RECT_CHUNK, n - chunk0);
+        // ---- gather: 2 x 2 entries per thread, a round's loads all in flight before its first store ----
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const int g = c0 + 32 * u + lane;
-            a[u] = (g < n) ? gA[g] : make_float4(0.f, 0.f, -1.f, 0.f);
-        }
+        for (int half = 0; half < 2; half++) {
+            constexpr int PER = RECT_CHUNK / 256 / 2;
+            uint32_t g[PER];
+            float4 rA[PER], rB[PER], rC[PER];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const bool ov = reaches_rect(a[u], tx, ty, w);
-            const unsigned m = __ballot_sync(0xffffffffu, ov);
-            if (ov) cand[(tail + __popc(m & lt_mask)) & 255u] = (uint32_t)(c0 + 32 * u + lane);
-            tail += __popc(m);
+            for (int u = 0; u < PER; u++) {
+                const int i = threadIdx.x + (half * PER + u) * 256;
+                g[u] = (i < cn) ? gL[chunk0 + i] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < PER; u++) {
+                const int i = threadIdx.x + (half * PER + u) * 256;
+                if (i < cn) {
+                    const float4* src = reinterpret_cast<const float4*>(rec + g[u]);
+                    rA[u] = __ldg(src);
+                    rB[u] = __ldg(src + 1);
+                    rC[u] = __ldg(src + 2);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < PER; u++) {
+                const int i = threadIdx.x + (half * PER + u) * 256;
+                if (i < cn) {
+                    sA_s[i] = rA[u];
+                    sB_s[i] = rB[u];
+                    gA[chunk0 + i] = rA[u];
+                    gBC[2 * (size_t)(chunk0 + i)] = rB[u];
+                    gBC[2 * (size_t)(chunk0 + i) + 1] = make_float4(rC[u].x, rC[u].y, rC[u].z, __uint_as_float(g[u]));
+                }
+            }
         }
-        __syncwarp();
-        while (tail - head >= 32u) emit(32);
-        __syncwarp();
+        __syncthreads();
+        // ---- scan: every warp compacts the entries that reach its rectangle and evaluates their pixel masks ----
+        for (int c0 = 0; c0 < cn; c0 += 128) {
+            float4 a[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int e = c0 + 32 * u + lane;
+                a[u] = (e < cn) ? sA_s[e] : make_float4(0.f, 0.f, -1.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool ov = reaches_rect(a[u], tx, ty, w);
+                const unsigned m = __ballot_sync(0xffffffffu, ov);
+                if (ov) cand[(tail + __popc(m & lt_mask)) & 255u] = (uint32_t)(c0 + 32 * u + lane);
+                tail += __popc(m);
+            }
+            __syncwarp();
+            while (tail - head >= 32u) emit(32);
+            __syncwarp();
+        }
+        // candidates index the CURRENT chunk's shared-memory copy: drain them before it is replaced
+        while (tail != head) emit((int)min(32u, tail - head));
+        __syncthreads();
     }
-    if (tail != head) emit((int)(tail - head));
     if (lane == 0) {
         rect_off[tile * 8 + w] = off;
         rect_cnt[tile * 8 + w] = run;

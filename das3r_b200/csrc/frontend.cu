@@ -269,14 +269,35 @@ __global__ void __launch_bounds__(FE_THREADS) frontend_bwd_kernel(const __grid_c
 __global__ void __launch_bounds__(FE_THREADS) frontend_pose_kernel(const float* __restrict__ partials, int n_blocks,
                                                                   int n_views, const float* __restrict__ poses,
                                                                   float* __restrict__ dL_dposes) {
-    __shared__ float red[FE_THREADS / 32];
+    __shared__ float red[FE_THREADS / 32][FE_PART_F];
     __shared__ float s_sum[FE_PART_F];
     const int v = blockIdx.x;
+    // every thread sums its blocks' 16 partials (fixed assignment and order: run-to-run identical), then one shuffle
+    // tree per value and a fixed-order sum over the warps
+    float acc[FE_PART_F];
+#pragma unroll
+    for (int k = 0; k < FE_PART_F; k++) acc[k] = 0.f;
+    for (int b = threadIdx.x; b < n_blocks; b += FE_THREADS) {
+        const float4* p4 = reinterpret_cast<const float4*>(partials + ((size_t)b * n_views + v) * FE_PART_F);
+#pragma unroll
+        for (int q = 0; q < FE_PART_F / 4; q++) {
+            const float4 t = p4[q];
+            acc[4 * q] += t.x; acc[4 * q + 1] += t.y; acc[4 * q + 2] += t.z; acc[4 * q + 3] += t.w;
+        }
+    }
+#pragma unroll
     for (int k = 0; k < FE_PART_F; k++) {
-        float s = 0.f;
-        for (int b = threadIdx.x; b < n_blocks; b += FE_THREADS) s += partials[((size_t)b * n_views + v) * FE_PART_F + k];
-        const float t = block_sum(s, red);
-        if (threadIdx.x == 0) s_sum[k] = t;
+        float t = acc[k];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][k] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x < FE_PART_F) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < FE_THREADS / 32; w++) t += red[w][threadIdx.x];
+        s_sum[threadIdx.x] = t;
     }
     __syncthreads();
     if (threadIdx.x != 0) return;
