@@ -80,12 +80,10 @@ void binning_layout(int R, int T, bool with_keys, bool with_fallback, das3r_rast
     const size_t n = (size_t)R;
     L->b_unsorted = c.take(n * 8);
     L->b_point_list = c.take(n * 4);
-    L->b_sA = c.take(n * 16);  // float4[R]  {x, y, h, -tau'}
-    L->b_sB = c.take(n * 32);  // float4[R][2] {conic, opacity} {rgb, gaussian index}
-    L->b_sC = L->b_sB + 16;
     L->b_rect_off = c.take((size_t)T * 8 * 4);   // uint32[T*8] start of each rectangle's list
     L->b_rect_cnt = c.take((size_t)T * 8 * 4);   // uint32[T*8] its length
     L->b_rect_list = c.take(n * 8 * 8);          // uint2 {position, pixel mask}, capacity 8 per instance (<= 8 rectangles)
+    L->b_rect_gid = c.take(n * 8 * 4);           // uint32 Gaussian index of the same entry
     L->b_keys_sorted = with_keys ? c.take(n * 8) : (size_t)0;
     X->fallback_bytes = with_fallback ? tile_sort_fallback_bytes(R, T) : 0;
     X->b_fallback = with_fallback ? c.take(X->fallback_bytes) : 0;
@@ -312,11 +310,10 @@ static void bin_fill_state(ViewBin& vb, int P, int W, int H, char* geom, char* i
 static void bin_fill_binning(ViewBin& vb, const das3r_raster_state_layout& L, char* bin, bool debug) {
     vb.unsorted = reinterpret_cast<uint64_t*>(bin + L.b_unsorted);
     vb.point_list = reinterpret_cast<uint32_t*>(bin + L.b_point_list);
-    vb.sA = reinterpret_cast<float4*>(bin + L.b_sA);
-    vb.sBC = reinterpret_cast<float4*>(bin + L.b_sB);
     vb.rect_off = reinterpret_cast<uint32_t*>(bin + L.b_rect_off);
     vb.rect_cnt = reinterpret_cast<uint32_t*>(bin + L.b_rect_cnt);
     vb.rect_list = reinterpret_cast<uint2*>(bin + L.b_rect_list);
+    vb.rect_gid = reinterpret_cast<uint32_t*>(bin + L.b_rect_gid);
     vb.keys_sorted = debug ? reinterpret_cast<uint64_t*>(bin + L.b_keys_sorted) : nullptr;
 }
 

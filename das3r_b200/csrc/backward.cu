@@ -34,8 +34,8 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, DAS3R_BWD_MIN_BLOCKS) blend_
     const uint32_t* __restrict__ rect_off = V.rect_off;
     const uint32_t* __restrict__ rect_cnt = V.rect_cnt;
     const uint2* __restrict__ rect_list = V.rect_list;
-    const float4* __restrict__ sA = V.sA;
-    const float4* __restrict__ sBC = V.sBC;
+    const uint32_t* __restrict__ rect_gid = V.rect_gid;
+    const GaussRec* __restrict__ rec_by_id = V.rec;
     const float* __restrict__ bg = V.bg;
     const float* __restrict__ final_Ts = V.final_T;
     const uint32_t* __restrict__ n_contrib = V.n_contrib;
@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS, DAS3R_BWD_MIN_BLOCKS) blend_
     if (wmax == 0) return;
 
     walk_rect_list<true, BWD_K, BWD_NPAIR>(
-        sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, wmax,
+        sm.ring[warp], sm.qmask[warp], rect_list + off, rect_gid + off, cnt, rec_by_id, wmax,
         [&]() { return last_contributor != 0u; },
         [&](const RingRec& r) {
             // backward.cu:490-500: everything that does not depend on the pixel's running state

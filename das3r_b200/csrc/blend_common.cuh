@@ -150,35 +150,39 @@ __device__ unsigned long long g_walk_prof[8 * 65536];
 
 template <bool REVERSE, int K, int NPAIR, typename Keep, typename Prep, typename Apply>
 __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint32_t* __restrict__ qmask,
-                                               const uint2* __restrict__ list, int cnt,
-                                               const float4* __restrict__ gA, const float4* __restrict__ gBC,
-                                               const uint32_t pos_limit, Keep keep, Prep prep, Apply apply) {
+                                               const uint2* __restrict__ list, const uint32_t* __restrict__ gid_list,
+                                               int cnt, const GaussRec* __restrict__ rec, const uint32_t pos_limit,
+                                               Keep keep, Prep prep, Apply apply) {
     static_assert((K & (K - 1)) == 0, "K must be a power of two");
     const int lane = threadIdx.x & 31;
     const int nchunks = (cnt + CHUNK - 1) / CHUNK;
     if (nchunks == 0) return;
     constexpr int step = REVERSE ? -1 : 1;
-    // this lane's entry of list chunk c, in walk order; {~0, 0} where there is none
-    auto load_entry = [&](int c) -> uint2 {
-        if (c < 0 || c >= nchunks) return make_uint2(0xffffffffu, 0u);
+    // this lane's entry of list chunk c, in walk order: {position, mask, Gaussian index}; {~0, 0, 0} where there is none
+    auto load_entry = [&](int c) -> uint3 {
+        if (c < 0 || c >= nchunks) return make_uint3(0xffffffffu, 0u, 0u);
         const int ns = min(CHUNK, cnt - c * CHUNK);
-        return (lane < ns) ? list[c * CHUNK + (REVERSE ? ns - 1 - lane : lane)] : make_uint2(0xffffffffu, 0u);
+        if (lane >= ns) return make_uint3(0xffffffffu, 0u, 0u);
+        const int i = c * CHUNK + (REVERSE ? ns - 1 - lane : lane);
+        const uint2 e = list[i];
+        return make_uint3(e.x, e.y, gid_list[i]);
     };
     int lc = REVERSE ? nchunks - 1 : 0;  // list chunk to start next
     int left = nchunks;                  // list chunks not started yet
     // list entries are fetched LIST_AHEAD chunks before they are needed: a chunk start must never wait for them
-    uint2 e_q[LIST_AHEAD + 1];
+    uint3 e_q[LIST_AHEAD + 1];
 #pragma unroll
     for (int j = 0; j <= LIST_AHEAD; j++) e_q[j] = load_entry(lc + j * step);
 
     uint32_t m = 0;
     int nx = 0, vis = 0, iss = 0;
     // chunks in flight, oldest first: their transposed masks and this lane's entry position wait in registers
-    uint32_t pend_mask[BLEND_INFLIGHT], pend_pos[BLEND_INFLIGHT];
+    uint32_t pend_mask[BLEND_INFLIGHT], pend_pos[BLEND_INFLIGHT], pend_gid[BLEND_INFLIGHT];
 #pragma unroll
     for (int f = 0; f < BLEND_INFLIGHT; f++) {
         pend_mask[f] = 0;
         pend_pos[f] = 0xffffffffu;
+        pend_gid[f] = 0;
     }
 
     WALK_PROF_DECL
@@ -199,14 +203,15 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
         WALK_PROF(0)
         // start list chunks while the window and the pipeline have room (chunks nobody needs are skipped)
         while (left > 0 && nfly < BLEND_INFLIGHT && iss - oldest < K) {
-            const uint2 e_cur = e_q[0];
+            const uint3 e_cur = e_q[0];
             const bool valid = e_cur.x < pos_limit;
             if (__any_sync(0xffffffffu, valid)) {
                 RingRec& r = ring[(iss & (K - 1)) * 32 + lane];
-                if (valid) {
-                    cp_async_16(&r.A, gA + e_cur.x);
-                    cp_async_16(&r.B, gBC + 2 * (size_t)e_cur.x);
-                    cp_async_16(&r.C, gBC + 2 * (size_t)e_cur.x + 1);
+                if (valid) {  // the entry's 48-byte record, straight from the per-Gaussian array
+                    const float4* src = reinterpret_cast<const float4*>(rec + e_cur.z);
+                    cp_async_16(&r.A, src);
+                    cp_async_16(&r.B, src + 1);
+                    cp_async_16(&r.C, src + 2);
                 }
                 cp_async_commit();
                 const uint32_t tm = transpose_bits(valid ? e_cur.y : 0u, lane);
@@ -215,6 +220,7 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
                     if (f == nfly) {
                         pend_mask[f] = tm;
                         pend_pos[f] = valid ? e_cur.x : 0xffffffffu;
+                        pend_gid[f] = e_cur.z;
                     }
                 iss++;
                 nfly++;
@@ -234,12 +240,16 @@ __device__ __forceinline__ void walk_rect_list(RingRec* __restrict__ ring, uint3
             else if (nfly == 2) cp_async_wait_group<1>();
             else cp_async_wait_group<2>();
             const int slot = (vis & (K - 1)) * 32 + lane;
-            if (pend_pos[0] != 0xffffffffu) ring[slot].A.z = __uint_as_float(pend_pos[0]);
+            if (pend_pos[0] != 0xffffffffu) {  // the blends want the list position and the Gaussian index with the record
+                ring[slot].A.z = __uint_as_float(pend_pos[0]);
+                ring[slot].C.w = __uint_as_float(pend_gid[0]);
+            }
             qmask[slot] = pend_mask[0];
 #pragma unroll
             for (int f = 0; f + 1 < BLEND_INFLIGHT; f++) {
                 pend_mask[f] = pend_mask[f + 1];
                 pend_pos[f] = pend_pos[f + 1];
+                pend_gid[f] = pend_gid[f + 1];
             }
             __syncwarp();
             vis++;

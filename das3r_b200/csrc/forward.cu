@@ -1031,41 +1031,31 @@ static cudaError_t sort_oversized_tiles(int R, int T, const uint2* ranges, uint6
 #ifndef DAS3R_RECT_MIN_BLOCKS
 #define DAS3R_RECT_MIN_BLOCKS 4
 #endif
-constexpr int RECT_CHUNK = 256;  // tile-list entries per staging buffer (one per thread); three buffers in rotation
+constexpr int RECT_CHUNK = 1024;  // tile-list entries staged in shared memory at a time (4 per thread)
 
-struct RectStage {
-    float4 A[RECT_CHUNK];  // {x, y, h, -tau'}
-    float4 B[RECT_CHUNK];  // {conic, opacity}
-    float4 C[RECT_CHUNK];  // {r, g, b, depth}
-    uint32_t g[RECT_CHUNK];  // Gaussian index
-};
-
-// The block GATHERS its tile's records through the sorted point list (48-byte reads scattered over the per-Gaussian
-// array) into the tile-ordered streams the blends read (sA / sBC, coalesced writes) and scans them for its eight
-// rectangles, chunk by chunk: while the eight warps scan chunk k from shared memory, the records of chunk k+1 are already
-// on their way into the next buffer (cp.async, no register round trip), and chunk k-1 stays readable so that a warp's
-// not yet evaluated candidates (fewer than 32) can wait for company instead of being evaluated with idle lanes. The gather is pure memory latency, the scan pure
-// arithmetic; a separate gather kernel ran at 5 % issue utilisation and took as long as the whole sort.
+// The block stages a chunk of its tile's list in shared memory - Gaussian index and the 16-byte record head
+// {x, y, h, -tau'}, fetched through the sorted point list - and its eight warps scan the chunk for their rectangles. No
+// tile-ordered copy of the records is written any more: the lists carry the Gaussian index and the blends fetch the
+// 48-byte records from the per-Gaussian array themselves (a gather either way, but 52 bytes per instance less to write
+// and to read back; the separate gather kernel took as long as the whole sort).
 __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(const __grid_constant__ BatchArgs b) {
-    __shared__ uint32_t cand_s[8][256];  // per warp: circular buffer of chunk positions that reach the rectangle
-    __shared__ __align__(16) RectStage stage[3];
+    __shared__ uint32_t cand_s[8][256];   // per warp: circular buffer of chunk positions that reach the rectangle
+    __shared__ float4 sA_s[RECT_CHUNK];   // {x, y, h, -tau'} of the chunk's entries
+    __shared__ uint32_t sG_s[RECT_CHUNK];  // their Gaussian indices
     const ViewBin& V = b.v[blockIdx.y];
     const uint2* __restrict__ ranges = V.ranges;
     const uint32_t* __restrict__ point_list = V.point_list;
     const GaussRec* __restrict__ rec = V.rec;
-    float4* __restrict__ sA = V.sA;
-    float4* __restrict__ sBC = V.sBC;
     uint32_t* __restrict__ rect_off = V.rect_off;
     uint32_t* __restrict__ rect_cnt = V.rect_cnt;
     uint2* __restrict__ rect_list = V.rect_list;
+    uint32_t* __restrict__ rect_gid = V.rect_gid;
     const unsigned gx = b.gx;
     const int W = b.W, H = b.H;
     const int tile = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
     const int tx = tile % gx, ty = tile / gx;
-    float4* gA = sA + range.x;
-    float4* gBC = sBC + 2 * (size_t)range.x;
     const uint32_t* gL = point_list + range.x;
     uint32_t* cand = cand_s[w];
     const uint32_t off = 8u * range.x + (uint32_t)w * (uint32_t)n;
@@ -1079,15 +1069,15 @@ __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(
 
     uint32_t head = 0, tail = 0, run = 0;
     int chunk0 = 0;
-    // Pixel masks of `k` (<= 32) buffered candidates (tile-list positions of the current or the previous chunk), one per
-    // lane; entries with a non-empty mask are appended to the rectangle's list.
+    // Pixel masks of `k` (<= 32) buffered candidates of the current chunk, one per lane; entries with a non-empty mask
+    // are appended to the rectangle's list with their position in the tile list and their Gaussian index.
     auto emit = [&](int k) {
-        uint32_t pos = 0, mask = 0;
+        uint32_t pos = 0, mask = 0, gid = 0;
         if (lane < k) {
             pos = cand[(head + lane) & 255u];
-            const RectStage& st = stage[(pos / RECT_CHUNK) % 3u];
-            const float4 A = st.A[pos % RECT_CHUNK];
-            const float4 con_o = st.B[pos % RECT_CHUNK];
+            gid = sG_s[pos];
+            const float4 A = sA_s[pos];
+            const float4 con_o = __ldg(reinterpret_cast<const float4*>(rec + gid) + 1);
             // splat_power() for the 32 pixels with the column / row factors hoisted (same operations, same rounding)
             float dx[8], ax[8], bx[8];
 #pragma unroll
@@ -1111,66 +1101,65 @@ __global__ void __launch_bounds__(256, DAS3R_RECT_MIN_BLOCKS) rect_lists_kernel(
             mask &= pix_valid;
         }
         const unsigned bal = __ballot_sync(0xffffffffu, mask != 0u);
-        if (mask) rect_list[off + run + __popc(bal & lt_mask)] = make_uint2(pos, mask);
+        if (mask) {
+            const uint32_t slot = off + run + __popc(bal & lt_mask);
+            rect_list[slot] = make_uint2((uint32_t)chunk0 + pos, mask);
+            rect_gid[slot] = gid;
+        }
         run += __popc(bal);
         head += (uint32_t)k;
     };
-    // starts the copy of the chunk at c0 into stage[buf]: one entry per thread
-    auto prefetch = [&](int c0, int buf) {
-        const int i = threadIdx.x;
-        if (c0 + i < n) {
-            const uint32_t g = gL[c0 + i];
-            const float4* src = reinterpret_cast<const float4*>(rec + g);
-            stage[buf].g[i] = g;
-            cp_async_16(&stage[buf].A[i], src);
-            cp_async_16(&stage[buf].B[i], src + 1);
-            cp_async_16(&stage[buf].C[i], src + 2);
-        }
-        cp_async_commit();
-    };
 
-    if (n > 0) prefetch(0, 0);
-    int buf = 0;
-    for (chunk0 = 0; chunk0 < n; chunk0 += RECT_CHUNK, buf = (buf + 1) % 3) {
+    for (chunk0 = 0; chunk0 < n; chunk0 += RECT_CHUNK) {
         const int cn = min(RECT_CHUNK, n - chunk0);
-        cp_async_wait_all();
-        __syncthreads();  // this chunk is complete in stage[buf]; nobody holds candidates of the chunk before the last one
-        if (chunk0 + RECT_CHUNK < n) prefetch(chunk0 + RECT_CHUNK, (buf + 1) % 3);
-        const RectStage* cur = &stage[buf];
-        // the tile-ordered streams of this chunk (coalesced)
+        // ---- stage: 4 entries per thread, all loads in flight before the first store ----
         {
-            const int i = threadIdx.x;
-            if (i < cn) {
-                const float4 c = cur->C[i];
-                gA[chunk0 + i] = cur->A[i];
-                gBC[2 * (size_t)(chunk0 + i)] = cur->B[i];
-                gBC[2 * (size_t)(chunk0 + i) + 1] = make_float4(c.x, c.y, c.z, __uint_as_float(cur->g[i]));
+            constexpr int PER = RECT_CHUNK / 256;
+            uint32_t g[PER];
+            float4 rA[PER];
+#pragma unroll
+            for (int u = 0; u < PER; u++) {
+                const int i = threadIdx.x + u * 256;
+                g[u] = (i < cn) ? gL[chunk0 + i] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < PER; u++) {
+                const int i = threadIdx.x + u * 256;
+                if (i < cn) rA[u] = __ldg(reinterpret_cast<const float4*>(rec + g[u]));
+            }
+#pragma unroll
+            for (int u = 0; u < PER; u++) {
+                const int i = threadIdx.x + u * 256;
+                if (i < cn) {
+                    sA_s[i] = rA[u];
+                    sG_s[i] = g[u];
+                }
             }
         }
-        // every warp compacts the entries that reach its rectangle and evaluates their pixel masks
+        __syncthreads();
+        // ---- scan: every warp compacts the entries that reach its rectangle and evaluates their pixel masks ----
         for (int c0 = 0; c0 < cn; c0 += 128) {
             float4 a[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const int e = c0 + 32 * u + lane;
-                a[u] = (e < cn) ? cur->A[e] : make_float4(0.f, 0.f, -1.f, 0.f);
+                a[u] = (e < cn) ? sA_s[e] : make_float4(0.f, 0.f, -1.f, 0.f);
             }
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const bool ov = reaches_rect(a[u], tx, ty, w);
                 const unsigned m = __ballot_sync(0xffffffffu, ov);
-                if (ov) cand[(tail + __popc(m & lt_mask)) & 255u] = (uint32_t)(chunk0 + c0 + 32 * u + lane);
+                if (ov) cand[(tail + __popc(m & lt_mask)) & 255u] = (uint32_t)(c0 + 32 * u + lane);
                 tail += __popc(m);
             }
             __syncwarp();
             while (tail - head >= 32u) emit(32);
             __syncwarp();
         }
-        // the buffer of the PREVIOUS chunk is refilled after the next barrier: candidates from it must not wait longer
-        // (they sit at the head of the queue; rare - a rectangle that collected < 32 candidates over a whole chunk)
-        while (tail != head && cand[head & 255u] < (uint32_t)chunk0) emit((int)min(32u, tail - head));
+        // candidates index the CURRENT chunk's shared-memory copy: drain them before it is replaced
+        while (tail != head) emit((int)min(32u, tail - head));
+        __syncthreads();
     }
-    while (tail != head) emit((int)min(32u, tail - head));
     if (lane == 0) {
         rect_off[tile * 8 + w] = off;
         rect_cnt[tile * 8 + w] = run;
@@ -1217,8 +1206,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(const __gri
     const uint32_t* __restrict__ rect_off = V.rect_off;
     const uint32_t* __restrict__ rect_cnt = V.rect_cnt;
     const uint2* __restrict__ rect_list = V.rect_list;
-    const float4* __restrict__ sA = V.sA;
-    const float4* __restrict__ sBC = V.sBC;
+    const uint32_t* __restrict__ rect_gid = V.rect_gid;
     const GaussRec* __restrict__ rec_by_id = V.rec;
     const float* __restrict__ bg = V.bg;
     float* __restrict__ final_T = V.final_T;
@@ -1246,7 +1234,7 @@ __global__ void __launch_bounds__(32 * BLEND_WARPS) blend_fwd_kernel(const __gri
     float Dz = 0.f;
 
     walk_rect_list<false, FWD_K, FWD_NPAIR>(
-        sm.ring[warp], sm.qmask[warp], rect_list + off, cnt, sA + range.x, sBC + 2 * (size_t)range.x, 0xffffffffu,
+        sm.ring[warp], sm.qmask[warp], rect_list + off, rect_gid + off, cnt, rec_by_id, 0xffffffffu,
         [&]() { return !done; },
         [&](const RingRec& r) {
             FwdPair x;

@@ -10,14 +10,12 @@ constexpr int TILE_X = 16;  // reference config.h:16-17 (BLOCK_X, BLOCK_Y)
 constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
 
-// Per-Gaussian record, 48 bytes, written by the forward preprocess and gathered (in tile/depth order) by the tile
-// sort so that the blend kernels can stage contiguous batches with one TMA bulk copy.
+// Per-Gaussian record, 48 bytes, written by the forward preprocess; the blend kernels fetch the records of their list
+// entries straight from this array (cp.async, 48 contiguous bytes per entry).
 //   A = {x, y, h, -tau'}    pixel-space mean; h = conservative radius of the region where alpha >= 1/255 is possible
 //                           (< 0: never), tau' = ln(255*opacity) with a margin: a pixel can contribute iff power >= -tau'
 //   B = {conic a, b, c, opacity}   (reference: conic_opacity, forward.cu:253)
 //   C = {r, g, b, depth}
-// The tile-ordered copy is split into two streams: sA[R] = A (the 16 bytes every warp scans) and sBC[R][2] = {B, C'}
-// with C'.w = Gaussian index (as bits) instead of the depth.
 struct __align__(16) GaussRec {
     float4 A, B, C;
 };
@@ -99,11 +97,10 @@ struct ViewBin {
     // binning blob
     uint64_t* unsorted;
     uint32_t* point_list;
-    float4* sA;
-    float4* sBC;
     uint32_t* rect_off;
     uint32_t* rect_cnt;
-    uint2* rect_list;
+    uint2* rect_list;    // {tile-list position, pixel mask}
+    uint32_t* rect_gid;  // Gaussian index of the same entry (the blends fetch its 48-byte record directly)
     uint64_t* keys_sorted;  // debug only
     // per-view inputs / outputs of the blends
     const float* bg;

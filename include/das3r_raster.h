@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define DAS3R_ABI_VERSION 2
+#define DAS3R_ABI_VERSION 3
 
 #define DAS3R_OK 0
 #define DAS3R_EINVAL (-1)   /* bad argument (shape, null, size) */
@@ -287,10 +287,9 @@ typedef struct das3r_raster_state_layout {
     size_t b_unsorted;               /* uint64[R]: depth_bits<<32 | gaussian index, tile-bucketed */
     size_t b_point_list;             /* uint32[R] sorted */
     size_t b_keys_sorted;            /* uint64[R] tile<<32|depth_bits, written only when params.debug != 0 */
-    size_t b_sA;                     /* float4[R] tile-ordered {x, y, h, -tau'} */
-    size_t b_sB, b_sC;               /* float4[R][2] tile-ordered, interleaved {conic, opacity} {rgb, gaussian index} */
     size_t b_rect_off, b_rect_cnt;   /* uint32[T*8]: start / length of the list of each 8x4 pixel rectangle */
     size_t b_rect_list;              /* uint2[8*R] capacity: {tile-list position, pixel mask} per rectangle, in list order */
+    size_t b_rect_gid;               /* uint32[8*R] capacity: Gaussian index of the same list entry */
     size_t binning_bytes;
 } das3r_raster_state_layout;
 int das3r_raster_state_layout_query(int32_t P, int32_t width, int32_t height, int32_t num_rendered,

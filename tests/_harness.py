@@ -28,7 +28,7 @@ class _Layout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_size_t) for n in (
         "g_recA", "g_recB", "g_recC", "g_tiles_touched", "g_clamped", "geom_bytes",
         "i_final_T", "i_n_contrib", "i_ranges", "i_tile_counts", "i_cursors", "i_totals", "image_bytes",
-        "b_unsorted", "b_point_list", "b_keys_sorted", "b_sA", "b_sB", "b_sC", "b_rect_off", "b_rect_cnt", "b_rect_list",
+        "b_unsorted", "b_point_list", "b_keys_sorted", "b_rect_off", "b_rect_cnt", "b_rect_list", "b_rect_gid",
         "binning_bytes")]
 
 

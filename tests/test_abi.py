@@ -43,7 +43,7 @@ def test_every_entry_point_cites_the_reference():
 
 def test_version_and_error_string():
     lib = Hn.cabi()
-    assert lib.das3r_abi_version() == 2
+    assert lib.das3r_abi_version() == 3
     assert lib.das3r_last_error() in (b"",) or isinstance(lib.das3r_last_error(), bytes)
 
 
@@ -59,8 +59,8 @@ def test_layout_query_is_consistent():
     assert L.i_ranges >= L.i_n_contrib + 4 * W * H
     assert L.i_tile_counts >= L.i_ranges + 8 * T
     assert L.b_point_list >= L.b_unsorted + 8 * R
-    assert L.b_sA >= L.b_point_list + 4 * R
-    assert L.b_sB >= L.b_sA + 16 * R
+    assert L.b_rect_off >= L.b_point_list + 4 * R
+    assert L.b_rect_gid >= L.b_rect_list + 64 * R
     assert L.binning_bytes >= L.b_keys_sorted + 8 * R
     for f, _ in L._fields_:
         assert getattr(L, f) % 16 == 0, f
