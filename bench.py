@@ -261,7 +261,15 @@ def main():
         C, _ = oracle.load_reference()
 
     # ---- the workload: one replicated scene, per-rank view pools ------------------------------------------------
-    sc = synth_scene(P=args.P, V=args.V, W=args.W, H=args.H, seed=args.seed, sh_degree=args.sh_degree)
+    # multi-million-point scenes: the 3-NN distances that size the Gaussians come from the GPU (each arm uses its own
+    # distCUDA2 - the GPU tests pin ours to the reference's), the CPU k-d tree takes minutes there
+    dist2_fn = None
+    if args.P >= 3_000_000:
+        if args.impl == "ours":
+            dist2_fn = lambda xyz: C.distCUDA2(xyz.to(dev)).cpu()
+        else:
+            dist2_fn = lambda xyz: oracle.load_reference()[1].distCUDA2(xyz.to(dev)).cpu()
+    sc = synth_scene(P=args.P, V=args.V, W=args.W, H=args.H, seed=args.seed, sh_degree=args.sh_degree, dist2_fn=dist2_fn)
     P, W, H, D = args.P, args.W, args.H, args.sh_degree
     K = (D + 1) ** 2
     N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
