@@ -74,14 +74,39 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* f, float3 pos,
     return make_float3(res[0] < 0.0f ? 0.0f : res[0], res[1] < 0.0f ? 0.0f : res[1], res[2] < 0.0f ? 0.0f : res[2]);
 }
 
-// SH degrees 0..2 go through ONE out-of-line copy of the evaluation: inlined, the compiler contracts products like
-// xx - yy into different FMAs in the one-view and the multi-view kernel (seen at degree 2: a 1-ulp colour difference),
-// and the two must agree bit for bit. Degree 3 stays inline (its rows are staged and both kernels were verified equal).
-__device__ __noinline__ float3 sh_to_rgb_low(int deg, const float* f, float3 pos, float3 campos, uint8_t* clamped) {
-    uint8_t cl = 0;
-    const float3 rgb = sh_to_rgb(deg, f, pos, campos, cl);
-    *clamped = cl;
-    return rgb;
+// SH degrees 0..2 (the degrees DAS3R trains at) with every product and sum written as an explicit intrinsic: left to
+// the compiler, expressions like xx - yy are contracted into different FMAs in the one-view and the multi-view kernel
+// (seen at degree 2: a 1-ulp colour difference), and the two must agree bit for bit. Same formulas as sh_to_rgb
+// (forward.cu:20-71); the result is within an ulp or two of the reference's build, far inside the 1e-5 bar. Degree 3
+// keeps the plain expressions above (both kernels were verified equal there, and equal to the reference's build).
+__device__ __forceinline__ float3 sh_to_rgb_low(int deg, const float* f, float3 pos, float3 campos, uint8_t& clamped) {
+    float res[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) res[c] = __fmul_rn(kSH0, f[c]);
+    if (deg > 0) {
+        const float dx = __fsub_rn(pos.x, campos.x), dy = __fsub_rn(pos.y, campos.y), dz = __fsub_rn(pos.z, campos.z);
+        const float len = sqrtf(__fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx))));
+        const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
+        const float b1 = __fmul_rn(kSH1, y), b2 = __fmul_rn(kSH1, z), b3 = __fmul_rn(kSH1, x);
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+            res[c] = __fmaf_rn(-b3, f[9 + c], __fmaf_rn(b2, f[6 + c], __fmaf_rn(-b1, f[3 + c], res[c])));
+        if (deg > 1) {
+            const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+            const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
+            const float c0 = __fmul_rn(kSH2[0], xy), c1 = __fmul_rn(kSH2[1], yz);
+            const float c2 = __fmul_rn(kSH2[2], __fsub_rn(__fsub_rn(__fadd_rn(zz, zz), xx), yy));
+            const float c3 = __fmul_rn(kSH2[3], xz), c4 = __fmul_rn(kSH2[4], __fsub_rn(xx, yy));
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                res[c] = __fmaf_rn(c4, f[24 + c], __fmaf_rn(c3, f[21 + c], __fmaf_rn(c2, f[18 + c],
+                             __fmaf_rn(c1, f[15 + c], __fmaf_rn(c0, f[12 + c], res[c])))));
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; c++) res[c] = __fadd_rn(res[c], 0.5f);
+    clamped = (uint8_t)((res[0] < 0 ? 1 : 0) | (res[1] < 0 ? 2 : 0) | (res[2] < 0 ? 4 : 0));
+    return make_float3(res[0] < 0.0f ? 0.0f : res[0], res[1] < 0.0f ? 0.0f : res[1], res[2] < 0.0f ? 0.0f : res[2]);
 }
 
 constexpr int PRE_THREADS = 256;
@@ -186,9 +211,12 @@ __device__ __forceinline__ PreGeom pre_geometry(const PreFwdArgs& a, const int i
 
 // Colour / record half: radii and tile count, SH -> RGB (the row comes from shared memory when STAGE_SH), the 48-byte
 // record, clamp bits, tile histogram (forward.cu:239-255).
-template <bool STAGE_SH>
+// f_low: the first 27 floats of the Gaussian's SH row already in registers (degrees 0..2, multi-view kernel), or NULL.
+// KNOWN_DEG >= 0: the degree as a compile-time constant (multi-view kernel: f_low then holds exactly its active floats).
+template <bool STAGE_SH, int KNOWN_DEG = -1>
 __device__ __forceinline__ void pre_finish(const PreFwdArgs& a, const int idx, const PreGeom& g,
-                                           const float4* __restrict__ sh_row, uint32_t* __restrict__ hist) {
+                                           const float4* __restrict__ sh_row, uint32_t* __restrict__ hist,
+                                           const float* f_low = nullptr) {
     if (idx < a.P) {
         a.radii[idx] = g.vis ? (int)g.my_radius : 0;
         a.tiles_touched[idx] = g.vis ? (g.rmax.y - g.rmin.y) * (g.rmax.x - g.rmin.x) : 0u;
@@ -198,12 +226,14 @@ __device__ __forceinline__ void pre_finish(const PreFwdArgs& a, const int idx, c
         uint8_t cl = 0;
         if (a.colors_precomp == nullptr) {
             const float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
-            if (!STAGE_SH && a.D < 3) {
+            if constexpr (!STAGE_SH && KNOWN_DEG >= 0) {
+                rgb = sh_to_rgb_low(KNOWN_DEG, f_low, g.p_orig, cam, cl);
+            } else if (!STAGE_SH && a.D < 3) {
                 float fl[27];
                 const float* row = a.shs + (size_t)idx * 3 * a.M;
                 const bool aligned = ((a.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
                 load_sh_row(row, a.D, aligned, fl);
-                rgb = sh_to_rgb_low(a.D, fl, g.p_orig, cam, &cl);
+                rgb = sh_to_rgb_low(a.D, fl, g.p_orig, cam, cl);
             } else {
                 float f[48];
                 if (STAGE_SH) {
@@ -290,8 +320,9 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(const PreFw
 // its row per view (first view from HBM, the others from L1/L2); what the views share here is the launch, the tile
 // histograms and the Gaussian-major sweep. Same device functions as the one-view kernel, so every output is
 // bit-identical to it (tests/test_gpu_multiview.py).
-template <bool STAGE>
+template <int DEG>
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_multi_kernel(const __grid_constant__ MultiFwdArgs m) {
+    constexpr bool STAGE = DEG == 3;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* sh_stage = reinterpret_cast<float4*>(smem_raw);
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem_raw + (STAGE ? PRE_THREADS * SH_ROW_PAD_F4 * 16 : 0));
@@ -317,11 +348,18 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_multi_kernel(const
         cp_async_wait_all();
     }
     __syncthreads();
+    // degrees 0..2: the thread's active SH floats (3, 12 or 27) stay in registers for all views
+    float fl[STAGE ? 1 : 3 * (DEG + 1) * (DEG + 1)];
+    if (!STAGE && idx < P) {
+        const PreFwdArgs& a0 = m.v[0];
+        const bool aligned = ((a0.M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a0.shs) & 15) == 0);
+        load_sh_row(a0.shs + (size_t)idx * 3 * a0.M, DEG, aligned, fl);
+    }
 #pragma unroll 1
     for (int v = 0; v < m.n_views; v++) {
         const PreFwdArgs& a = m.v[v];
         const PreGeom g = pre_geometry(a, idx);
-        pre_finish<STAGE>(a, idx, g, sh_stage + tid * SH_ROW_PAD_F4, hist + (size_t)v * T);
+        pre_finish<STAGE, DEG>(a, idx, g, sh_stage + tid * SH_ROW_PAD_F4, hist + (size_t)v * T, STAGE ? nullptr : fl);
     }
     if (m.smem_hist) {
         __syncthreads();
@@ -340,14 +378,20 @@ cudaError_t launch_preprocess_fwd_multi(const MultiFwdArgs& m_in, cudaStream_t s
     m.smem_hist = hist_bytes <= 96 * 1024 ? 1 : 0;
     for (int v = 0; v < m.n_views; v++) m.v[v].smem_hist = m.smem_hist;
     const size_t smem = stage_bytes + (m.smem_hist ? hist_bytes : 0);
-    const void* fn = stage ? (const void*)preprocess_fwd_multi_kernel<true> : (const void*)preprocess_fwd_multi_kernel<false>;
+    const int deg = stage ? 3 : m.v[0].D;
+    const void* fn = deg == 0   ? (const void*)preprocess_fwd_multi_kernel<0>
+                     : deg == 1 ? (const void*)preprocess_fwd_multi_kernel<1>
+                     : deg == 2 ? (const void*)preprocess_fwd_multi_kernel<2>
+                                : (const void*)preprocess_fwd_multi_kernel<3>;
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int blocks = (m.v[0].P + PRE_THREADS - 1) / PRE_THREADS;
-    if (stage)
-        preprocess_fwd_multi_kernel<true><<<blocks, PRE_THREADS, smem, s>>>(m);
-    else
-        preprocess_fwd_multi_kernel<false><<<blocks, PRE_THREADS, smem, s>>>(m);
+    switch (deg) {
+        case 0: preprocess_fwd_multi_kernel<0><<<blocks, PRE_THREADS, smem, s>>>(m); break;
+        case 1: preprocess_fwd_multi_kernel<1><<<blocks, PRE_THREADS, smem, s>>>(m); break;
+        case 2: preprocess_fwd_multi_kernel<2><<<blocks, PRE_THREADS, smem, s>>>(m); break;
+        default: preprocess_fwd_multi_kernel<3><<<blocks, PRE_THREADS, smem, s>>>(m); break;
+    }
     return cudaGetLastError();
 }
 
