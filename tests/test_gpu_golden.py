@@ -12,7 +12,7 @@ import _harness as Hn
 pytestmark = pytest.mark.gpu
 
 GOLDEN_FILES = sorted(p for p in glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz"))
-                      if not os.path.basename(p).startswith(("frontend_", "loss_")))  # those have their own test files
+                      if not os.path.basename(p).startswith(("frontend_", "loss_", "init_")))  # those have their own test files
 
 
 @pytest.mark.skipif(not GOLDEN_FILES, reason="golden vectors not generated yet")
