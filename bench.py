@@ -716,10 +716,14 @@ def run_e2e(args, sc, dev, world, rank, S, dL, my_views, fwd_only):
                 c.record_stream(copy_stream)
         loss.backward()
         loss_host.copy_(loss.detach().view(1), non_blocking=True)
-        if world > 1:
-            for t in leaves:
-                if t.grad is not None:
-                    dist.all_reduce(t.grad)
+        if world > 1:  # one collective for all leaf gradients (flattened), not one per tensor
+            gs = [t.grad for t in leaves if t.grad is not None]
+            flat = torch.cat([g_.reshape(-1) for g_ in gs])
+            dist.all_reduce(flat)
+            o_ = 0
+            for g_ in gs:
+                g_.copy_(flat[o_:o_ + g_.numel()].view_as(g_))
+                o_ += g_.numel()
         main.wait_stream(copy_stream)
         main.synchronize()  # the step's images and loss are on the host now
 
