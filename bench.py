@@ -677,10 +677,11 @@ def run_e2e(args, sc, dev, world, rank, S, dL, my_views, fwd_only):
     from das3r_b200 import sharding
 
     W, H, D, vps, P = args.W, args.H, args.sh_degree, args.views_per_step, args.P
-    cam_host = torch.cat([S["view"].flatten().cpu(), S["proj"].flatten().cpu(), S["campos"].cpu(), S["bg"].cpu()]).pin_memory()
-    dL_host = dL.cpu().pin_memory()
-    cam_dev = [torch.empty_like(cam_host, device=dev) for _ in range(vps)]
-    dL_dev = [torch.empty_like(dL_host, device=dev) for _ in range(vps)]
+    cam_row = torch.cat([S["view"].flatten().cpu(), S["proj"].flatten().cpu(), S["campos"].cpu(), S["bg"].cpu()])
+    cam_host = cam_row[None].repeat(vps, 1).contiguous().pin_memory()        # one camera bundle per view, [vps,38]
+    dL_host = dL.cpu()[None].repeat(vps, 1, 1, 1).contiguous().pin_memory()  # one dL/dcolour per view, [vps,3,H,W]
+    cam_dev = torch.empty_like(cam_host, device=dev)   # the step's host inputs travel as one copy per kind
+    dL_dev = torch.empty_like(dL_host, device=dev)
     img_host = [torch.empty(3, H, W).pin_memory() for _ in range(vps)]
     loss_host = torch.empty(1).pin_memory()
     mv = MultiViewRasterizer()
@@ -729,13 +730,11 @@ def run_e2e(args, sc, dev, world, rank, S, dL, my_views, fwd_only):
 
     def host_inputs():
         main = torch.cuda.current_stream()
-        for v in range(vps):
-            cam_dev[v].copy_(cam_host, non_blocking=True)
+        cam_dev.copy_(cam_host, non_blocking=True)
         if not fwd_only:
             copy_stream.wait_stream(main)  # the previous step is done with dL_dev
             with torch.cuda.stream(copy_stream):
-                for v in range(vps):
-                    dL_dev[v].copy_(dL_host, non_blocking=True)  # only needed by the loss: overlaps the forwards
+                dL_dev.copy_(dL_host, non_blocking=True)  # only needed by the loss: overlaps the forwards
 
     def step_frontend():
         leaves = list(raw.values()) + [poses_dev]
@@ -780,9 +779,9 @@ def run_e2e(args, sc, dev, world, rank, S, dL, my_views, fwd_only):
         ctx = torch.no_grad() if fwd_only else torch.enable_grad()
         with ctx:
             for v, pv in enumerate(pool):
-                cam_dev[v].copy_(cam_host, non_blocking=True)
+                cam_dev[v].copy_(cam_host[v], non_blocking=True)
                 if not fwd_only:
-                    dL_dev[v].copy_(dL_host, non_blocking=True)
+                    dL_dev[v].copy_(dL_host[v], non_blocking=True)
                 color, _radii = GaussianRasterizer(settings_for(v))(
                     means3D=pv["means"], means2D=means2D, opacities=shared["opac"], shs=shared["shs"],
                     scales=shared["scales"], rotations=pv["rots"])

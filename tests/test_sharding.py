@@ -131,3 +131,24 @@ def test_sliced_bucket_layout():
     assert float(b.slice_flat(len(b.slices) - 1)[-28:].sum()) >= 9.0 * 28 - 1e-3 or True
     g = b.gather("xyz")
     assert g.shape == (P, 3) and float(g[0, 0]) == 1.0 and float(g[-1, 0]) == float(len(b.slices))
+
+
+def test_views_are_dealt_by_cost():
+    """shard_views_balanced: every rank gets views_per_rank views, together exactly the step's views, and the summed
+    costs are closer than with positional sharding; one rank takes the same views as positional sharding."""
+    import random
+
+    rnd = random.Random(3)
+    perm = list(range(50))
+    rnd.shuffle(perm)
+    costs = [1.4e6 + 4e5 * rnd.random() for _ in range(50)]
+    assert sorted(sharding.shard_views_balanced(perm, costs, 0, 0, 1, 8)) == sorted(sharding.shard_views(perm, 0, 0, 1, 8))
+    for world in (2, 4, 8):
+        got = [sharding.shard_views_balanced(perm, costs, 1, r, world, 8) for r in range(world)]
+        assert all(len(g) == 8 for g in got)
+        step_views = sorted(perm[(world * 8 + j) % 50] for j in range(world * 8))
+        assert sorted(v for g in got for v in g) == step_views
+        load = [sum(costs[v] for v in g) for g in got]
+        pos = [sum(costs[v] for v in sharding.shard_views(perm, 1, r, world, 8)) for r in range(world)]
+        assert max(load) / (sum(load) / world) <= max(pos) / (sum(pos) / world) + 1e-12
+        assert max(load) / (sum(load) / world) < 1.005
