@@ -329,13 +329,24 @@ def main():
 
         def make_bucket(ns):
             nonlocal reducer
-            b_ = sharding.SlicedGradBucket(P, widths, dev, ns, tail={"poses": (vps, 7)},
-                                           allocate=reducer.allocate if reducer is not None else None)
-            if reducer is not None and not reducer.available:
+            if reducer is not None:
+                try:
+                    b_ = sharding.SlicedGradBucket(P, widths, dev, ns, tail={"poses": (vps, 7)}, allocate=reducer.allocate)
+                    ok = reducer.available
+                except Exception as ex:  # symmetric-memory rendezvous refused on this box
+                    sys.stderr.write(f"[bench] symmetric memory rendezvous failed ({ex}); using NCCL\n")
+                    b_, ok = None, False
+                # every rank must take the same branch: the collective below would otherwise deadlock
+                flag = torch.tensor([1.0 if ok else 0.0], device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                if float(flag.item()) > 0.5:
+                    return b_
                 if args.allreduce == "nvls":
                     raise RuntimeError("no NVSwitch multicast support on this box")
                 reducer = None
-            return b_
+                if b_ is not None:
+                    return b_
+            return sharding.SlicedGradBucket(P, widths, dev, ns, tail={"poses": (vps, 7)})
 
         holder = {"bucket": make_bucket(n_slices)}
         bucket = holder["bucket"]
