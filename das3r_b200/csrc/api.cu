@@ -349,11 +349,22 @@ static int forward_finish(int n, const das3r_raster_fwd_view* const* views, int*
     for (int v = 0; v < n; v++)
         bin_fill_state(b.v[v], P, W, H, views[v]->state->geom, views[v]->state->image, views[v]->out->radii);
 
-    // The one host round trip of the forward (the reference has one per view, rasterizer_impl.cu:281).
-    uint32_t host_totals[RB_MAX_VIEWS][4];
+    // The one host round trip of the forward (the reference has one per view, rasterizer_impl.cu:281). The counters of
+    // all views land in a small page-locked buffer (one per host thread, allocated on first use and kept): copies into
+    // pageable memory would each block the host on their own.
+    static thread_local uint32_t(*pinned_totals)[4] = nullptr;
+    if (pinned_totals == nullptr) {
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, sizeof(uint32_t) * 4 * RB_MAX_VIEWS, cudaHostAllocDefault) == cudaSuccess)
+            pinned_totals = static_cast<uint32_t(*)[4]>(p);
+        else
+            (void)cudaGetLastError();  // fall back to the stack buffer below
+    }
+    uint32_t stack_totals[RB_MAX_VIEWS][4];
+    uint32_t(*host_totals)[4] = pinned_totals ? pinned_totals : stack_totals;
     cudaError_t e = cudaSuccess;
     for (int v = 0; v < n && e == cudaSuccess; v++)
-        e = cudaMemcpyAsync(host_totals[v], b.v[v].totals, sizeof(host_totals[v]), cudaMemcpyDeviceToHost, stream);
+        e = cudaMemcpyAsync(host_totals[v], b.v[v].totals, sizeof(uint32_t) * 4, cudaMemcpyDeviceToHost, stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) return fail(DAS3R_ECUDA, "read-back of num_rendered", e);
 
