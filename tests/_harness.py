@@ -244,7 +244,21 @@ def compare_forward(ours: dict, ref: dict, P: int, has_sh: bool = True) -> dict:
     return r
 
 
+def rel_err_elementwise(a, b, floor=0.1) -> float:
+    """max over the entries with |b| >= floor * max|b| of |a-b| / |b|: a true per-element relative error, restricted to
+    entries that are not the residue of a cancellation (for those only the tensor-wide metric above is meaningful)."""
+    a, b = np_(a).astype(np.float64), np_(b).astype(np.float64)
+    if a.size == 0:
+        return 0.0
+    big = np.abs(b) >= floor * max(np.abs(b).max(), 1e-30)
+    if not big.any():
+        return 0.0
+    return float((np.abs(a - b)[big] / np.abs(b)[big]).max())
+
+
 def compare_grads(ours: dict, ref: dict) -> dict:
+    """Per gradient tensor: max|a-b| / max|b| (key = the tensor's name) and the element-wise relative error of its
+    significant entries (key = name + ':elementwise'). Both are held to GRAD_RTOL by the callers."""
     r = {}
     for k, v in ours.items():
         if v is None or k not in ref or ref[k] is None:
@@ -253,4 +267,5 @@ def compare_grads(ours: dict, ref: dict) -> dict:
         if a.size == 0:
             continue
         r[k] = rel_err(a.reshape(b.shape), b)
+        r[k + ":elementwise"] = rel_err_elementwise(a.reshape(b.shape), b)
     return r
