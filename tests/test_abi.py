@@ -79,3 +79,40 @@ def test_bad_arguments_are_rejected_without_touching_the_gpu():
     assert lib.das3r_mark_visible(ctypes.c_int32(0), None, None, None, None, None) == 0
     assert lib.das3r_knn_dist2(ctypes.c_int32(0), None, None, None, ctypes.c_size_t(0), None) == 0
     assert lib.das3r_raster_backward_scratch_bytes(ctypes.c_int32(1000)) >= 48 * 1000
+
+
+def test_size_queries_and_argument_errors_need_no_gpu():
+    """Pure-host behaviour of the newer entry points: scratch-size queries, and argument validation that refuses a call
+    before any CUDA work is attempted (negative DAS3R_E* code + message)."""
+    import ctypes
+
+    lib = Hn.cabi()
+    for name in ("das3r_pointmap_scratch_bytes", "das3r_frontend_backward_scratch_bytes", "das3r_loss_state_bytes"):
+        getattr(lib, name).restype = ctypes.c_size_t
+    n = 50 * 288 * 512
+    assert lib.das3r_pointmap_scratch_bytes(ctypes.c_int64(n)) >= 4 * ((n + 1023) // 1024)
+    assert lib.das3r_pointmap_scratch_bytes(ctypes.c_int64(0)) > 0
+    assert lib.das3r_frontend_backward_scratch_bytes(ctypes.c_int32(1_000_000), ctypes.c_int32(8)) >= 3907 * 8 * 16 * 4
+    assert lib.das3r_raster_backward_scratch_bytes(ctypes.c_int32(1000)) >= 48 * 1000
+    assert lib.das3r_knn_scratch_bytes(ctypes.c_int32(1000)) > 0
+    assert lib.das3r_loss_state_bytes(ctypes.c_int32(512), ctypes.c_int32(288)) >= 15 * 512 * 288 * 4
+    EINVAL = -1
+    # in-switch all-reduce: null multicast pointer, bad rank, misaligned length
+    lib.das3r_nvls_allreduce_sum.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_int32,
+                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    assert lib.das3r_nvls_allreduce_sum(None, 0, 16, 0, 2, 0, None) == EINVAL
+    assert b"nvls_allreduce" in lib.das3r_last_error()
+    assert lib.das3r_nvls_allreduce_sum(ctypes.c_void_p(4096), 0, 16, 2, 2, 0, None) == EINVAL
+    assert lib.das3r_nvls_allreduce_sum(ctypes.c_void_p(4096), 0, 18, 0, 2, 0, None) == EINVAL
+    assert lib.das3r_nvls_allreduce_sum(ctypes.c_void_p(4096), 0, 0, 0, 2, 0, None) == 0  # nothing to do
+    # multi-view entry points: no views
+    assert lib.das3r_raster_backward_finish_ex(0, None, None, 0, 0, -1, 0, None) == EINVAL
+    assert lib.das3r_raster_backward_blend_batch(0, None, None) == EINVAL
+    assert lib.das3r_raster_forward_render_batch(0, None, None, None) == EINVAL
+    assert b"forward_render_batch" in lib.das3r_last_error()
+    # pointmap initialisation: null description
+    lib.das3r_pointmap_select.restype = ctypes.c_int64
+    assert lib.das3r_pointmap_select(None, None, None, None, ctypes.c_size_t(0), None) == EINVAL
+    assert lib.das3r_pointmap_init(None, None, ctypes.c_int64(0), None, None, ctypes.c_size_t(0), None, ctypes.c_size_t(0),
+                                   None) == EINVAL
+    assert lib.das3r_frontend_forward_ex(None, 1, None, None, None, None) == EINVAL
